@@ -1,0 +1,246 @@
+// bm_api.cu -- context, parameters, reference/read upload and measurement entry points of libbucketmap_b200.so.
+#include <cmath>
+#include <cstring>
+#include <new>
+
+#include <cub/device/device_scan.cuh>
+
+#include "bm_internal.cuh"
+
+extern "C" {
+
+int bm_version(void) { return 100; }
+
+int bm_ctx_create(int device, bm_ctx** out) {
+    if (!out) return BM_E_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0 || device < 0 || device >= n) return BM_E_CUDA;   // no CPU fallback
+    if (cudaSetDevice(device) != cudaSuccess) return BM_E_CUDA;
+    bm_ctx* c = new (std::nothrow) bm_ctx();
+    if (!c) return BM_E_NOMEM;
+    c->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&c->ev_a) != cudaSuccess || cudaEventCreate(&c->ev_b) != cudaSuccess) {
+        delete c;
+        return BM_E_CUDA;
+    }
+    *out = c;
+    return BM_OK;
+}
+
+void bm_ctx_destroy(bm_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf* bufs[] = {&c->d_packed, &c->d_bstart, &c->d_blen, &c->d_rows, &c->d_k2i, &c->d_zeros, &c->d_distok,
+                      &c->d_stage, &c->d_seq, &c->d_qual, &c->d_read_off, &c->d_seg_read, &c->d_seg_start,
+                      &c->d_seg_len, &c->d_rowidx, &c->d_segok, &c->d_cand_fixed, &c->d_cand_cnt, &c->d_cand_off,
+                      &c->d_cand, &c->d_stats, &c->d_scan_tmp, &c->d_lsamp_idx, &c->d_lsamp_hash, &c->d_cres_pos,
+                      &c->d_cres_votes, &c->d_cseg, &c->d_loc_cnt, &c->d_loc_off, &c->d_locs, &c->d_locs2,
+                      &c->d_loc_off2, &c->d_vote_scratch, &c->d_aln, &c->d_cigar_fixed, &c->d_cigar_cnt,
+                      &c->d_cigar_off, &c->d_cigar, &c->d_aln_scratch, &c->d_flush};
+    for (DevBuf* b : bufs) b->release();
+    for (auto& p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto e : c->ev_pool) cudaEventDestroy(e);
+    if (c->ev_a) cudaEventDestroy(c->ev_a);
+    if (c->ev_b) cudaEventDestroy(c->ev_b);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* bm_last_error(const bm_ctx* c) { return c ? c->err.c_str() : "null context / no CUDA device"; }
+
+// main.cpp:12-39 defaults; main.cpp:207 and bucket_locator.h:419-420 thresholds, computed in float like the reference
+void bm_params_derive(bm_params* p, uint32_t bucket_len, uint32_t read_len, uint32_t q, uint32_t k, uint32_t s,
+                      float d, uint32_t b, float e, float n, uint32_t pl, uint32_t u) {
+    p->bucket_len = bucket_len; p->read_len = read_len; p->q = q; p->k = k;
+    p->mapper_samples = s;
+    p->mapper_fault = (uint32_t)std::ceil(s * e);
+    p->distinguishability = d; p->avg_base_quality = b;
+    p->max_candidates = 30; p->num_segment_samples = 5;
+    p->locator_samples = pl;
+    p->allowed_mismatch = (uint32_t)(int)std::ceil(e * pl);
+    p->allowed_indel = (uint32_t)(int)std::ceil(n * read_len);
+    p->indel_rate = n; p->quality_threshold = u;
+}
+void bm_params_default(bm_params* p, uint32_t bucket_len) {
+    bm_params_derive(p, bucket_len, 300, 9, 12, 15, 0.5f, 25, 0.4f, 0.02f, 10, 40);
+}
+
+int bm_ref_upload(bm_ctx* c, const uint8_t* packed, uint64_t n_bases, const uint64_t* bstart, const uint32_t* blen,
+                  uint32_t n_emit, uint32_t NB) {
+    if (!c) return BM_E_ARG;
+    if (!packed || (n_emit && (!bstart || !blen)) || n_emit > NB) BM_FAIL(c, BM_E_ARG, "bm_ref_upload: bad arguments");
+    cudaSetDevice(c->device);
+    uint64_t nbytes = (n_bases + 3) / 4;
+    BM_CK(c, c->d_packed.ensure(nbytes + 64));
+    BM_CK(c, cudaMemsetAsync((uint8_t*)c->d_packed.p + nbytes, 0, 64, c->stream));   // kernels read whole words
+    BM_CK(c, cudaMemcpyAsync(c->d_packed.p, packed, nbytes, cudaMemcpyHostToDevice, c->stream));
+    BM_CK(c, c->d_bstart.ensure((size_t)(n_emit + 1) * 8));
+    BM_CK(c, c->d_blen.ensure((size_t)(n_emit + 1) * 4));
+    uint32_t mx = 0;
+    for (uint32_t i = 0; i < n_emit; i++) {
+        if (bstart[i] + blen[i] > n_bases) BM_FAIL(c, BM_E_ARG, "bm_ref_upload: bucket outside the genome");
+        if (blen[i] > mx) mx = blen[i];
+    }
+    if (n_emit) {
+        BM_CK(c, cudaMemcpyAsync(c->d_bstart.p, bstart, (size_t)n_emit * 8, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_blen.p, blen, (size_t)n_emit * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->n_bases = n_bases; c->n_emit = n_emit; c->NB = NB; c->max_blen = mx;
+    return BM_OK;
+}
+
+// utils.h:160-178 (Sampler).  The reference's early return (last_upper_bound is never updated, so it fires only
+// for upper_bound==0) leaves stale samples and then reads out of range; here upper_bound==0 gives n zeros.
+static void sample_det(uint32_t n, uint32_t ub, std::vector<uint32_t>& out) {
+    out.clear();
+    if (n == 0) return;
+    if (ub == 0) { out.assign(n, 0u); return; }
+    double delta = (n == 1) ? 0.0 : static_cast<double>(ub + 1u) / (double)(n - 1u);
+    for (uint32_t i = 0; i + 1 < n; i++) out.push_back((uint32_t)std::floor((double)(int)i * delta));
+    out.push_back(ub);
+}
+
+int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
+                    uint32_t n_reads) {
+    if (!c) return BM_E_ARG;
+    if (!p || !read_off || (n_reads && (!seq || !qual))) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad arguments");
+    if (p->read_len == 0 || p->num_segment_samples == 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad parameters");
+    cudaSetDevice(c->device);
+    c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
+    uint64_t nbytes = read_off[n_reads] - read_off[0];
+    if (read_off[0] != 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off[0] must be 0");
+    // segment table: q_gram_mapper.h:509-523 / bucket_locator.h:302-313
+    c->h_seg_read.clear(); c->h_seg_start.clear(); c->h_seg_len.clear();
+    std::vector<uint32_t> st;
+    uint32_t mx = 0;
+    for (uint32_t i = 0; i < n_reads; i++) {
+        if (read_off[i + 1] < read_off[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
+        uint64_t len64 = read_off[i + 1] - read_off[i];
+        if (len64 > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31");
+        uint32_t len = (uint32_t)len64;
+        if (len > 2 * p->read_len) sample_det(p->num_segment_samples, len - p->read_len - 1, st);
+        else st.assign(1, 0u);
+        for (uint32_t s : st) {
+            uint32_t e = s + p->read_len < len ? s + p->read_len : len;
+            c->h_seg_read.push_back(i); c->h_seg_start.push_back(s); c->h_seg_len.push_back(e - s);
+            if (e - s > mx) mx = e - s;
+        }
+    }
+    uint32_t n_seg = (uint32_t)c->h_seg_read.size();
+    BM_CK(c, c->d_seq.ensure(nbytes + 16));
+    BM_CK(c, c->d_qual.ensure(nbytes + 16));
+    BM_CK(c, c->d_read_off.ensure((size_t)(n_reads + 1) * 8));
+    BM_CK(c, c->d_seg_read.ensure((size_t)(n_seg + 1) * 4));
+    BM_CK(c, c->d_seg_start.ensure((size_t)(n_seg + 1) * 4));
+    BM_CK(c, c->d_seg_len.ensure((size_t)(n_seg + 1) * 4));
+    if (nbytes) {
+        BM_CK(c, cudaMemcpyAsync(c->d_seq.p, seq, nbytes, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_qual.p, qual, nbytes, cudaMemcpyHostToDevice, c->stream));
+    }
+    BM_CK(c, cudaMemcpyAsync(c->d_read_off.p, read_off, (size_t)(n_reads + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    if (n_seg) {
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_read.p, c->h_seg_read.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_start.p, c->h_seg_start.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_len.p, c->h_seg_len.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    BM_CK(c, cudaStreamSynchronize(c->stream));   // host vectors / caller buffers may be reused after return
+    c->n_reads = n_reads; c->n_seg = n_seg; c->max_seg_len = mx; c->n_read_bytes = nbytes;
+    c->have_reads = true;
+    return BM_OK;
+}
+
+int bm_reads_segments(bm_ctx* c, uint32_t* n_seg, uint32_t* seg_read, uint32_t* seg_start, uint32_t* seg_len) {
+    if (!c) return BM_E_ARG;
+    if (!c->have_reads) BM_FAIL(c, BM_E_ARG, "bm_reads_segments: no read batch resident");
+    if (n_seg) *n_seg = c->n_seg;
+    size_t b = (size_t)c->n_seg * 4;
+    if (seg_read && b) memcpy(seg_read, c->h_seg_read.data(), b);
+    if (seg_start && b) memcpy(seg_start, c->h_seg_start.data(), b);
+    if (seg_len && b) memcpy(seg_len, c->h_seg_len.data(), b);
+    return BM_OK;
+}
+
+// ---- measurement ------------------------------------------------------------------------------------------------
+int bm_timer_start(bm_ctx* c) {
+    if (!c) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    BM_CK(c, cudaEventRecord(c->ev_a, c->stream));
+    return BM_OK;
+}
+int bm_timer_stop(bm_ctx* c, float* ms) {
+    if (!c || !ms) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    BM_CK(c, cudaEventRecord(c->ev_b, c->stream));
+    BM_CK(c, cudaEventSynchronize(c->ev_b));
+    BM_CK(c, cudaEventElapsedTime(ms, c->ev_a, c->ev_b));
+    return BM_OK;
+}
+int bm_kernel_timing(bm_ctx* c, int enable) {
+    if (!c) return BM_E_ARG;
+    c->ktiming = enable != 0;
+    return BM_OK;
+}
+static int drain_pending(bm_ctx* c) {
+    if (c->pending.empty()) return BM_OK;
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    for (auto& p : c->pending) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) c->kstat[p.kid].ms += ms;
+        c->ev_pool.push_back(p.a); c->ev_pool.push_back(p.b);
+    }
+    c->pending.clear();
+    return BM_OK;
+}
+int bm_kernel_stats(bm_ctx* c, int kid, double* total_ms, uint64_t* launches) {
+    if (!c || kid < 0 || kid >= BM_K_COUNT) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    int r = drain_pending(c);
+    if (r) return r;
+    if (total_ms) *total_ms = c->kstat[kid].ms;
+    if (launches) *launches = c->kstat[kid].launches;
+    return BM_OK;
+}
+int bm_kernel_stats_reset(bm_ctx* c) {
+    if (!c) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    int r = drain_pending(c);
+    if (r) return r;
+    for (auto& k : c->kstat) k = KStat();
+    return BM_OK;
+}
+int bm_flush_l2(bm_ctx* c, uint64_t bytes) {
+    if (!c) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    BM_CK(c, c->d_flush.ensure(bytes));
+    BM_CK(c, cudaMemsetAsync(c->d_flush.p, 0x5a, bytes, c->stream));
+    return BM_OK;
+}
+int bm_sync(bm_ctx* c) {
+    if (!c) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    return BM_OK;
+}
+void* bm_host_alloc(uint64_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    return p;
+}
+void bm_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+}  // extern "C"
+
+int bm_internal_exclusive_scan(bm_ctx* c, const uint32_t* d_in, uint32_t* d_out, uint32_t n) {
+    size_t tmp = 0;
+    BM_CK(c, cub::DeviceScan::ExclusiveSum(nullptr, tmp, d_in, d_out, (int)n, c->stream));
+    BM_CK(c, c->d_scan_tmp.ensure(tmp));
+    BM_CK(c, cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.p, tmp, d_in, d_out, (int)n, c->stream));
+    return BM_OK;
+}

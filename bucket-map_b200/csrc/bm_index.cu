@@ -1,0 +1,222 @@
+// bm_index.cu -- q-gram bit matrix: build on device (K1), load/download in .qgram layout, row popcounts (K0).
+//
+// Device layout: n_rows rows of Wp bytes, Wp = roundup((NB+7)>>3, 64); bucket j of a row at byte j>>3 bit j&7 exactly
+// like the .qgram file (indexer/bucket_indexer.h:64-73), padding bytes zero.  64-B padded rows make every row start
+// on a DRAM burst boundary and keep the mapper's 16-B vector loads aligned.
+#include "bm_internal.cuh"
+
+namespace {
+
+// ---- K1: index build ---------------------------------------------------------------------------------------------
+// One CTA per emitted bucket (utils.h:82-96); each thread walks a contiguous slice of the bucket with a rolling
+// base-4 hash (seqan3 views::kmer_hash(ungapped{q}), first base most significant) and sets bit (row, bucket) for every
+// sampled q-gram (bucket_indexer.h:57-60).  Bits of 32 neighbouring buckets share a word, so the set is a RED.OR.
+// Consecutive CTAs touch the same 32-B sector column of the matrix, which keeps the read-modify-write traffic in L2.
+__global__ void __launch_bounds__(256)
+k_index_build(const uint8_t* __restrict__ packed, const uint64_t* __restrict__ bstart, const uint32_t* __restrict__ blen,
+              const int32_t* __restrict__ k2i, uint32_t q, uint32_t* __restrict__ rows32, uint32_t Wp32) {
+    const uint32_t b = blockIdx.x;
+    const uint64_t start = bstart[b];
+    const uint32_t len = blen[b];
+    if (len < q) return;
+    const uint32_t npos = len - q + 1;
+    const uint32_t per = (npos + blockDim.x - 1) / blockDim.x;
+    uint32_t lo = threadIdx.x * per;
+    if (lo >= npos) return;
+    uint32_t hi = min(lo + per, npos);
+    const uint32_t mask = (q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * q)) - 1u);
+    const uint32_t word = b >> 5, bit = 1u << (b & 31);
+    uint32_t h = 0;
+    uint64_t g = start + lo;
+    for (uint32_t i = 0; i + 1 < q; i++) h = (h << 2) | bm_gbase(packed, g + i);
+    g += q - 1;
+    for (uint32_t pos = lo; pos < hi; pos++, g++) {
+        h = ((h << 2) | bm_gbase(packed, g)) & mask;
+        int idx = __ldg(k2i + h);
+        if (idx >= 0) atomicOr(rows32 + (size_t)idx * Wp32 + word, bit);
+    }
+}
+
+// ---- layout conversion between the unpadded .qgram image and the padded device rows ----------------------------------
+__global__ void k_pad_rows(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint32_t W, uint32_t Wp,
+                           uint64_t total /* n_rows*Wp */) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < total; i += stride) {
+        uint64_t r = i / Wp; uint32_t c = (uint32_t)(i - r * Wp);
+        dst[i] = (c < W) ? src[r * W + c] : (uint8_t)0;
+    }
+}
+__global__ void k_unpad_rows(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, uint32_t W, uint32_t Wp,
+                             uint64_t total /* n_rows*W */) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < total; i += stride) {
+        uint64_t r = i / W; uint32_t c = (uint32_t)(i - r * W);
+        dst[i] = src[r * Wp + c];
+    }
+}
+
+// ---- K0: zeros[row] = NB - popcount(row)  (distinguishability_filter::read, q_gram_mapper.h:171-184) ------------------
+__global__ void k_row_zeros(const uint4* __restrict__ rows, uint32_t n_rows, uint32_t Wp16, uint32_t NB, uint32_t thr,
+                            uint32_t* __restrict__ zeros, uint32_t* __restrict__ valid) {
+    uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_rows) return;
+    const uint4* r = rows + (size_t)warp * Wp16;
+    uint32_t ones = 0;
+    for (uint32_t c = lane; c < Wp16; c += 32) {
+        uint4 v = __ldg(r + c);
+        ones += __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
+    }
+    for (int o = 16; o; o >>= 1) ones += __shfl_xor_sync(0xFFFFFFFFu, ones, o);
+    if (lane == 0) {
+        zeros[warp] = NB - ones;                  // both branches of :178-183 give NB - ones
+        if (NB - ones > thr) atomicAdd(valid, 1u);   // the logged counter (:175-177)
+    }
+}
+
+// distok bit g = (kmer_to_index[g] >= 0 && zeros[idx] >= threshold): one q-gram's share of is_highly_distinguishable
+// (q_gram_mapper.h:189-196), folded into a 4^q-bit table the sampler kernel keeps hot in L1.
+__global__ void k_distok(const int32_t* __restrict__ k2i, const uint32_t* __restrict__ zeros, uint32_t n_codes,
+                         uint32_t thr, uint32_t* __restrict__ distok) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    bool ok = false;
+    if (g < n_codes) { int idx = k2i[g]; ok = idx >= 0 && zeros[idx] >= thr; }
+    uint32_t m = __ballot_sync(0xFFFFFFFFu, ok);
+    if ((threadIdx.x & 31) == 0 && g < n_codes) distok[g >> 5] = m;
+}
+
+int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t NB) {
+    if (q == 0 || q > 14) BM_FAIL(c, BM_E_LIMIT, "index seed length q must be in [1,14]");
+    if (NB == 0) BM_FAIL(c, BM_E_ARG, "NB must be > 0");
+    uint64_t n_codes = 1ull << (2 * q);
+    uint32_t cnt = 0;
+    for (uint64_t i = 0; i < n_codes; i++) {
+        if (k2i[i] >= 0) { if ((uint32_t)k2i[i] >= n_rows) BM_FAIL(c, BM_E_ARG, "kmer_to_index entry >= n_rows"); cnt++; }
+    }
+    (void)cnt;
+    c->have_index = false; c->zeros_for_d = -1.f;
+    c->q = q; c->n_rows = n_rows; c->NB = NB;
+    c->W = (NB + 7) >> 3; c->Wp = (c->W + 63u) & ~63u;
+    BM_CK(c, c->d_k2i.ensure(n_codes * 4));
+    BM_CK(c, cudaMemcpyAsync(c->d_k2i.p, k2i, n_codes * 4, cudaMemcpyHostToDevice, c->stream));
+    BM_CK(c, c->d_rows.ensure((size_t)n_rows * c->Wp + 64));
+    BM_CK(c, c->d_zeros.ensure((size_t)(n_rows + 1) * 4));
+    BM_CK(c, c->d_distok.ensure((size_t)((n_codes + 31) / 32) * 4 + 64));
+    return BM_OK;
+}
+
+}  // namespace
+
+int bm_internal_index_prepare(bm_ctx* c, float d) {
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "no index resident (bm_index_build / bm_index_load first)");
+    if (c->zeros_for_d == d) return BM_OK;
+    const uint32_t thr = (unsigned int)(d * c->NB);          // q_gram_mapper.h:163 (float * unsigned, truncated)
+    BM_CK(c, c->d_stats.ensure(64 * 8));
+    uint32_t* d_valid = c->d_stats.as<uint32_t>() + 100;     // scratch word well past the mapper's stats
+    BM_CK(c, cudaMemsetAsync(d_valid, 0, 4, c->stream));
+    if (c->n_rows) {
+        KScope ks(c, BM_K_ROWPOP);
+        uint32_t blocks = (c->n_rows + 7) / 8;
+        k_row_zeros<<<blocks, 256, 0, c->stream>>>(c->d_rows.as<uint4>(), c->n_rows, c->Wp / 16, c->NB, thr,
+                                                   c->d_zeros.as<uint32_t>(), d_valid);
+    }
+    uint32_t n_codes = 1u << (2 * c->q);
+    {
+        KScope ks(c, BM_K_AUX);
+        k_distok<<<(n_codes + 255) / 256, 256, 0, c->stream>>>(c->d_k2i.as<int32_t>(), c->d_zeros.as<uint32_t>(), n_codes,
+                                                               thr, c->d_distok.as<uint32_t>());
+    }
+    BM_CK(c, cudaGetLastError());
+    BM_CK(c, cudaMemcpyAsync(&c->dist_valid, d_valid, 4, cudaMemcpyDeviceToHost, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->dist_threshold = thr; c->zeros_for_d = d;
+    return BM_OK;
+}
+
+extern "C" {
+
+int bm_index_build(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint8_t* out_rows) {
+    if (!c) return BM_E_ARG;
+    if (!k2i) BM_FAIL(c, BM_E_ARG, "bm_index_build: kmer_to_index is null");
+    if (c->NB == 0 || !c->d_packed.p) BM_FAIL(c, BM_E_ARG, "bm_index_build: bm_ref_upload first");
+    cudaSetDevice(c->device);
+    int r = set_table(c, k2i, q, n_rows, c->NB);
+    if (r) return r;
+    BM_CK(c, cudaMemsetAsync(c->d_rows.p, 0, (size_t)n_rows * c->Wp + 64, c->stream));
+    if (c->n_emit && n_rows) {
+        KScope ks(c, BM_K_INDEX);
+        k_index_build<<<c->n_emit, 256, 0, c->stream>>>(c->d_packed.as<uint8_t>(), c->d_bstart.as<uint64_t>(),
+                                                        c->d_blen.as<uint32_t>(), c->d_k2i.as<int32_t>(), q,
+                                                        c->d_rows.as<uint32_t>(), c->Wp / 4);
+    }
+    BM_CK(c, cudaGetLastError());
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->have_index = true;
+    if (out_rows) return bm_index_download(c, out_rows);
+    return BM_OK;
+}
+
+int bm_index_load(bm_ctx* c, const int32_t* k2i, uint32_t q, const uint8_t* rows, uint32_t n_rows, uint32_t NB) {
+    if (!c) return BM_E_ARG;
+    if (!k2i || (n_rows && !rows)) BM_FAIL(c, BM_E_ARG, "bm_index_load: null argument");
+    cudaSetDevice(c->device);
+    if (c->d_packed.p && c->NB && c->NB != NB) BM_FAIL(c, BM_E_ARG, "bm_index_load: NB differs from the uploaded reference");
+    int r = set_table(c, k2i, q, n_rows, NB);
+    if (r) return r;
+    uint64_t raw = (uint64_t)n_rows * c->W, padded = (uint64_t)n_rows * c->Wp;
+    if (n_rows) {
+        BM_CK(c, c->d_stage.ensure(raw));
+        BM_CK(c, cudaMemcpyAsync(c->d_stage.p, rows, raw, cudaMemcpyHostToDevice, c->stream));
+        KScope ks(c, BM_K_AUX);
+        k_pad_rows<<<c->sm_count * 8, 256, 0, c->stream>>>(c->d_stage.as<uint8_t>(), c->d_rows.as<uint8_t>(), c->W, c->Wp, padded);
+    }
+    BM_CK(c, cudaMemsetAsync((uint8_t*)c->d_rows.p + padded, 0, 64, c->stream));
+    BM_CK(c, cudaGetLastError());
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->d_stage.release();
+    c->have_index = true;
+    return BM_OK;
+}
+
+int bm_index_download(bm_ctx* c, uint8_t* out_rows) {
+    if (!c) return BM_E_ARG;
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_index_download: no index resident");
+    if (!out_rows) BM_FAIL(c, BM_E_ARG, "bm_index_download: null output");
+    cudaSetDevice(c->device);
+    uint64_t raw = (uint64_t)c->n_rows * c->W;
+    if (!raw) return BM_OK;
+    BM_CK(c, c->d_stage.ensure(raw));
+    {
+        KScope ks(c, BM_K_AUX);
+        k_unpad_rows<<<c->sm_count * 8, 256, 0, c->stream>>>(c->d_rows.as<uint8_t>(), c->d_stage.as<uint8_t>(), c->W, c->Wp, raw);
+    }
+    BM_CK(c, cudaGetLastError());
+    BM_CK(c, cudaMemcpyAsync(out_rows, c->d_stage.p, raw, cudaMemcpyDeviceToHost, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->d_stage.release();
+    return BM_OK;
+}
+
+int bm_index_zeros(bm_ctx* c, float d, uint32_t* zeros_out, uint32_t* valid) {
+    if (!c) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    int r = bm_internal_index_prepare(c, d);
+    if (r) return r;
+    if (zeros_out && c->n_rows) {
+        BM_CK(c, cudaMemcpyAsync(zeros_out, c->d_zeros.p, (size_t)c->n_rows * 4, cudaMemcpyDeviceToHost, c->stream));
+        BM_CK(c, cudaStreamSynchronize(c->stream));
+    }
+    if (valid) *valid = c->dist_valid;
+    return BM_OK;
+}
+
+int bm_index_free(bm_ctx* c) {
+    if (!c) return BM_E_ARG;
+    cudaSetDevice(c->device);
+    c->d_rows.release(); c->d_zeros.release(); c->d_distok.release(); c->d_k2i.release(); c->d_stage.release();
+    c->have_index = false; c->zeros_for_d = -1.f; c->have_map = false;
+    return BM_OK;
+}
+
+}  // extern "C"

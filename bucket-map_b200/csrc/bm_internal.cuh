@@ -1,0 +1,151 @@
+// bm_internal.cuh -- context layout and small device helpers shared by the kernels of libbucketmap_b200.so.
+// Product code: nothing here (or in any file of csrc/) includes, links or calls oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/bucketmap_b200.h"
+
+// ---------------------------------------------------------------------------------------------------------------
+// growable device buffer
+struct DevBuf {
+    void*  p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + (bytes >> 3) + 256;   // slack so slowly growing batches do not realloc every call
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct KStat { double ms = 0; uint64_t launches = 0; };
+struct PendingEv { int kid; cudaEvent_t a, b; };
+
+struct bm_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // reference genome (2-bit) + bucket table
+    DevBuf d_packed, d_bstart, d_blen;
+    uint64_t n_bases = 0;
+    uint32_t n_emit = 0, NB = 0, max_blen = 0;
+
+    // q-gram bit matrix, rows padded to Wp bytes (multiple of 64 B: whole DRAM bursts, 16-B aligned vector loads)
+    DevBuf d_rows, d_k2i, d_zeros, d_distok, d_stage;
+    uint32_t q = 0, n_rows = 0, W = 0, Wp = 0;
+    bool have_index = false;
+    float zeros_for_d = -1.f;     // distinguishability the distok bitmap was built for (<0: none)
+    uint32_t dist_threshold = 0, dist_valid = 0;
+
+    // read batch
+    DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len;
+    std::vector<uint32_t> h_seg_read, h_seg_start, h_seg_len;
+    uint32_t n_reads = 0, n_seg = 0, max_seg_len = 0;
+    uint64_t n_read_bytes = 0;
+    bool have_reads = false;
+
+    // mapper results
+    DevBuf d_rowidx, d_segok, d_cand_fixed, d_cand_cnt, d_cand_off, d_cand, d_stats, d_scan_tmp;
+    uint32_t map_max_cand = 0;
+    uint64_t n_cand = 0;          // total candidates of the last bm_map_device (valid after bm_map_finish)
+    bool have_map = false;
+
+    // locator results
+    DevBuf d_lsamp_idx, d_lsamp_hash, d_cres_pos, d_cres_votes, d_cseg, d_loc_cnt, d_loc_off, d_locs, d_locs2,
+           d_loc_off2, d_vote_scratch;
+    uint64_t n_locs = 0;
+    bool have_locs = false, locs_filtered = false;
+
+    // alignment results
+    DevBuf d_aln, d_cigar_fixed, d_cigar_cnt, d_cigar_off, d_cigar, d_aln_scratch;
+    uint64_t n_aln = 0, n_cigar = 0;
+    bool have_aln = false;
+
+    // L2 flush scratch
+    DevBuf d_flush;
+
+    // measurement
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+    bool ktiming = false;
+    KStat kstat[BM_K_COUNT];
+    std::vector<PendingEv> pending;
+    std::vector<cudaEvent_t> ev_pool;
+};
+
+#define BM_CK(ctx, call)                                                                        \
+    do {                                                                                        \
+        cudaError_t _e = (call);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            char _b[512];                                                                       \
+            snprintf(_b, sizeof _b, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+            (ctx)->err = _b;                                                                    \
+            return (_e == cudaErrorMemoryAllocation) ? BM_E_NOMEM : BM_E_CUDA;                  \
+        }                                                                                       \
+    } while (0)
+
+#define BM_FAIL(ctx, code, msg) do { (ctx)->err = (msg); return (code); } while (0)
+
+// per-kernel timing scope: records events around a launch when ctx->ktiming is on
+struct KScope {
+    bm_ctx* c; int kid; cudaEvent_t a = nullptr, b = nullptr;
+    static cudaEvent_t get(bm_ctx* c) {
+        if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
+        cudaEvent_t e; cudaEventCreate(&e); return e;
+    }
+    KScope(bm_ctx* c_, int kid_) : c(c_), kid(kid_) {
+        c->kstat[kid].launches++;
+        if (c->ktiming) { a = get(c); b = get(c); cudaEventRecord(a, c->stream); }
+    }
+    ~KScope() {
+        if (a) { cudaEventRecord(b, c->stream); c->pending.push_back({kid, a, b}); }
+    }
+};
+
+int bm_internal_index_prepare(bm_ctx* ctx, float d);          // K0: zeros + distok bitmap for threshold d
+int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
+
+// ---------------------------------------------------------------------------------------------------------------
+// device helpers
+#ifdef __CUDACC__
+
+// seqan3 dna4 char->rank as used for FASTQ input (utils.h:192-204).  IUPAC codes map to their first base
+// (unpinned; synthetic inputs are ACGT only).
+__device__ __forceinline__ uint32_t bm_rank_dna4(uint32_t c) {
+    c &= 0xDFu;   // upper-case
+    uint32_t r = 0;
+    r = (c == 'C' || c == 'Y' || c == 'S' || c == 'B') ? 1u : r;
+    r = (c == 'G' || c == 'K') ? 2u : r;
+    r = (c == 'T' || c == 'U') ? 3u : r;
+    return r;
+}
+
+// utils.h:291-302: reverse the k base-4 digits and complement each
+__device__ __forceinline__ uint32_t bm_revcomp_hash(uint32_t h, uint32_t k) {
+    uint32_t x = ~h;
+    x = __brev(x);                                              // reverses bits; digits now reversed with swapped bit pairs
+    x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);    // restore bit order inside each digit
+    return (k >= 16) ? x : (x >> (32 - 2 * k));
+}
+
+// base i of the 2-bit packed genome
+__device__ __forceinline__ uint32_t bm_gbase(const uint8_t* __restrict__ p, uint64_t i) {
+    return (p[i >> 2] >> ((i & 3) << 1)) & 3u;
+}
+
+__device__ __forceinline__ uint4 bm_ldg_stream(const uint4* p) {
+    uint4 v;
+    asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+#endif

@@ -1,0 +1,166 @@
+/*
+ * bucketmap_b200.h -- C-ABI of the B200-native BucketMap hot path (libbucketmap_b200.so).
+ *
+ * The reference (GZHoffie/bucket-map) has no FFI: its hot path sits behind three C++ class interfaces that only
+ * main.cpp consumes.  Every entry point below names the reference member it replaces (paths relative to
+ * /root/reference/bucket_map/).  The host classes in bucket-map_b200/host/ (bm::bucket_hash_indexer,
+ * bm::q_gram_mapper, bm::bucket_locator) keep the reference signatures and call only these functions.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative bm_status; bm_last_error(ctx) gives the text.
+ *   - the caller owns every host buffer (pinned memory recommended); the library owns all device memory in bm_ctx.
+ *   - one bm_ctx per GPU, used by one host thread at a time; no global state; no exceptions cross the ABI.
+ *   - there is NO CPU fallback: without a usable CUDA device bm_ctx_create fails with BM_E_CUDA.
+ *
+ * Shared data conventions
+ *   - reference genome: all FASTA records concatenated, 2 bits per base (A0 C1 G2 T3), base i in byte i>>2 at
+ *     bits 2*(i&3).  Buckets are views: bucket b = bases [bucket_start[b], bucket_start[b]+bucket_len[b]).
+ *   - q-gram bit matrix ("rows"): the .qgram file layout of indexer/bucket_indexer.h:64-100 -- row-major, one row
+ *     per sampled q-gram, W=(NB+7)>>3 bytes per row, bucket j at byte j>>3 bit j&7, no header, no padding.
+ *   - reads: concatenated ASCII bases and ASCII phred+33 qualities; read i = [read_off[i], read_off[i+1]).
+ *   - candidate lists: cand_off[2*n_seg+1]; list 2*s = forward strand of segment s, 2*s+1 = reverse complement.
+ */
+#ifndef BUCKETMAP_B200_H
+#define BUCKETMAP_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bm_ctx bm_ctx;
+
+typedef enum bm_status {
+    BM_OK = 0,
+    BM_E_ARG = -1,      /* bad argument / call order (e.g. map before index load) */
+    BM_E_CUDA = -2,     /* CUDA runtime error, text in bm_last_error */
+    BM_E_NOMEM = -3,    /* device or host allocation failed */
+    BM_E_LIMIT = -4     /* parameter outside what the kernels support (k>16, samples>64, ...) */
+} bm_status;
+
+/* Run-time parameters: main.cpp:12-39 (cmd_arguments) + the integer thresholds main.cpp:207 and
+ * locator/bucket_locator.h:419-420 derive from them in float. */
+typedef struct bm_params {
+    uint32_t bucket_len;          /* BM_BUCKET_LEN (CMakeLists.txt:7-58) */
+    uint32_t read_len;            /* -r */
+    uint32_t q;                   /* -k index seed length */
+    uint32_t k;                   /* -l query seed length */
+    uint32_t mapper_samples;      /* -s */
+    uint32_t mapper_fault;        /* ceil(s*e), main.cpp:207 */
+    float    distinguishability;  /* -d */
+    uint32_t avg_base_quality;    /* -b */
+    uint32_t max_candidates;      /* 30, mapper/q_gram_mapper.h:285 */
+    uint32_t num_segment_samples; /* 5,  mapper/q_gram_mapper.h:286 */
+    uint32_t locator_samples;     /* -p */
+    uint32_t allowed_mismatch;    /* ceil(e*p), locator/bucket_locator.h:419 */
+    uint32_t allowed_indel;       /* ceil(n*r), locator/bucket_locator.h:420 */
+    float    indel_rate;          /* -n */
+    uint32_t quality_threshold;   /* -u */
+} bm_params;
+
+/* locate_t of locator/bucket_locator.h:143-148 */
+typedef struct bm_loc {
+    uint32_t bucket;
+    int32_t  offset;       /* read start inside the bucket */
+    uint32_t seg_offset;   /* segment start inside the read (0 after the best-location merge) */
+    uint32_t votes;
+    uint32_t is_original;  /* 1 = forward strand, 0 = reverse complement */
+} bm_loc;
+
+/* result of one bucketmap_align verification, locator/bucket_locator.h:560-589 */
+typedef struct bm_aln {
+    int32_t  score;        /* -(edit distance) */
+    uint32_t begin;        /* sequence1_begin_position inside the (possibly reverse-complemented) text window */
+    uint32_t map_qual;     /* 60u + score with 32-bit wrap (:570) */
+    uint32_t kept;         /* map_qual >= quality_threshold (:571) */
+    uint32_t cigar_off;    /* first op in the cigar array */
+    uint32_t cigar_len;    /* number of run-length ops; op = (len<<4)|code, code M=0 I=1 D=2 */
+} bm_aln;
+
+/* kernel ids for bm_kernel_stats */
+enum { BM_K_ROWPOP = 0, BM_K_INDEX = 1, BM_K_SAMPLE = 2, BM_K_MAP = 3, BM_K_LOCSAMPLE = 4, BM_K_LOCATE = 5,
+       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_COUNT = 9 };
+
+/* ---- context -------------------------------------------------------------------------------------------------- */
+int  bm_ctx_create(int device, bm_ctx** out);
+void bm_ctx_destroy(bm_ctx* ctx);
+const char* bm_last_error(const bm_ctx* ctx);
+int  bm_version(void);
+
+/* main.cpp:12-39,207 + bucket_locator.h:419-420: defaults and float-derived thresholds */
+void bm_params_derive(bm_params* p, uint32_t bucket_len, uint32_t read_len, uint32_t q, uint32_t k, uint32_t s,
+                      float d, uint32_t b, float e, float n, uint32_t pl, uint32_t u);
+void bm_params_default(bm_params* p, uint32_t bucket_len);
+
+/* ---- reference genome (replaces the two FASTA passes: utils.h:60-102 called from bucket_indexer.h:198 and
+ *      bucket_locator.h:151-160) ---------------------------------------------------------------------------------- */
+int bm_ref_upload(bm_ctx* ctx, const uint8_t* packed2bit, uint64_t n_bases, const uint64_t* bucket_start,
+                  const uint32_t* bucket_len, uint32_t n_emitted, uint32_t NB);
+
+/* ---- indexer (replaces bucket_indexer::_insert_into_bucket/_store_q_gram_index, bucket_indexer.h:49-100,171-216) - */
+/* K1: builds the bit matrix on the device from the uploaded reference; leaves it resident (ready for bm_map_*);
+ * if out_rows != NULL also writes the .qgram byte image (n_rows * W bytes) to host memory. */
+int bm_index_build(bm_ctx* ctx, const int32_t* kmer_to_index, uint32_t q, uint32_t n_rows, uint8_t* out_rows);
+/* replaces q_gram_mapper::load (q_gram_mapper.h:318-372): .qgram bytes + .kmers_index table -> device */
+int bm_index_load(bm_ctx* ctx, const int32_t* kmer_to_index, uint32_t q, const uint8_t* rows, uint32_t n_rows,
+                  uint32_t NB);
+/* copies the resident matrix back in .qgram layout */
+int bm_index_download(bm_ctx* ctx, uint8_t* out_rows);
+/* distinguishability_filter::read (q_gram_mapper.h:171-187): zeros[] per row; *valid = the logged counter */
+int bm_index_zeros(bm_ctx* ctx, float distinguishability, uint32_t* zeros_out /* n_rows or NULL */, uint32_t* valid);
+/* mapper::reset (q_gram_mapper.h) */
+int bm_index_free(bm_ctx* ctx);
+
+/* ---- reads ---------------------------------------------------------------------------------------------------- */
+/* H2D of one read batch + segment table (q_gram_mapper.h:509-523 / bucket_locator.h:302-313). */
+int bm_reads_upload(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
+                    const uint64_t* read_off, uint32_t n_reads);
+int bm_reads_segments(bm_ctx* ctx, uint32_t* n_seg, uint32_t* seg_read, uint32_t* seg_start, uint32_t* seg_len);
+
+/* ---- mapper (replaces q_gram_mapper::query_sequence/query + fault_tolerate_filter, q_gram_mapper.h:39-102,380-480) */
+/* K2a+K2 on the resident batch; results stay on the device. */
+int bm_map_device(bm_ctx* ctx, const bm_params* p);
+/* cand_off: 2*n_seg+1 entries; cand: capacity cand_cap entries (2*max_candidates*n_seg always suffices).
+ * stats[0]=segments with >=1 candidate, [1]=sum forward, [2]=sum reverse, [3]=rows gathered (R of the roofline). */
+int bm_map_download(bm_ctx* ctx, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats);
+/* host-buffer form: upload + device + download (what q_gram_mapper::map does per FASTQ batch) */
+int bm_map_reads(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
+                 uint32_t n_reads, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats);
+
+/* ---- locator (replaces bucket_locator::_prepare_read_query/_create_kmer_index/_find_offset/_locate/
+ *      _filter_best_locations, bucket_locator.h:162-405,613-705) ------------------------------------------------- */
+/* K3a+K3 (+K3b when filter_best != 0) on the resident batch and the candidates of the last bm_map_device. */
+int bm_locate_device(bm_ctx* ctx, const bm_params* p, int filter_best);
+/* loc_off: n_reads+1; locs: capacity loc_cap (cand_off[2*n_seg] always suffices) */
+int bm_locate_download(bm_ctx* ctx, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap);
+/* host-buffer form of the whole alignment-free path: reads in, merged best locations out */
+int bm_map_locate(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
+                  const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs,
+                  uint64_t loc_cap, uint64_t* stats);
+
+/* ---- bucketmap_align verification (replaces seqan3::align_pairwise + cigar_from_alignment at
+ *      bucket_locator.h:520-528,560-589) -------------------------------------------------------------------------- */
+/* K4 on the (unmerged) locations of the last bm_locate_device(filter_best=0). */
+int bm_align_device(bm_ctx* ctx, const bm_params* p);
+/* aln: one per location; cigar: capacity cigar_cap ops; *cigar_used = ops needed */
+int bm_align_download(bm_ctx* ctx, bm_aln* aln, uint32_t* cigar, uint64_t cigar_cap, uint64_t* cigar_used);
+
+/* ---- measurement ----------------------------------------------------------------------------------------------- */
+/* CUDA events on the library's stream around whatever is enqueued between start and stop. */
+int bm_timer_start(bm_ctx* ctx);
+int bm_timer_stop(bm_ctx* ctx, float* ms);
+/* accumulated per-kernel device time (CUDA events around each launch) and launch counts since the last reset;
+ * timing each launch costs two event records, so it is off unless enabled. */
+int bm_kernel_timing(bm_ctx* ctx, int enable);
+int bm_kernel_stats(bm_ctx* ctx, int kernel_id, double* total_ms, uint64_t* launches);
+int bm_kernel_stats_reset(bm_ctx* ctx);
+/* writes `bytes` bytes of device scratch (L2 flush between timed iterations) */
+int bm_flush_l2(bm_ctx* ctx, uint64_t bytes);
+int bm_sync(bm_ctx* ctx);
+/* pinned host memory for the caller's batches */
+void* bm_host_alloc(uint64_t bytes);
+void  bm_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
