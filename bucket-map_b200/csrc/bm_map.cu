@@ -1,0 +1,404 @@
+// bm_map.cu -- the mapper: k-mer filtering + sampling (K2a) and the gather / miss-count vote (K2).
+//
+// Replaces q_gram_mapper::query_sequence / query and fault_tolerate_filter (mapper/q_gram_mapper.h:39-102,380-480).
+//
+// Closed form of the reference's cascade (q_gram_mapper.h:75-102): after all S samples, filters[F-1-j] holds the
+// buckets with <= j missed samples, and best_results() returns the set bits of the highest non-empty level.  That is
+// "all buckets whose miss count equals the minimum miss count m*, if m* <= F-1, else nothing".  K2 therefore keeps
+// one saturating bit-sliced miss counter per bucket (NP bit planes, 128 buckets per lane) instead of F full bitsets.
+//
+// K2 work split: one warp per (segment, strand).  A warp walks the row in 512-B column tiles (32 lanes x 16 B); per
+// tile every lane issues the S*(k-q+1) independent 128-bit loads of its column, B samples at a time, ANDs the rows of
+// one sample, and adds the complement to its counters.  Everything after the loads is register-only; cross-lane work
+// is one ballot per tile (is any bucket still under F misses?) plus, for the rare tiles that hold a contender, a
+// warp min / prefix sum.  No shared-memory traffic on the critical path, no block-level barrier.
+#include <cub/device/device_scan.cuh>
+
+#include "bm_internal.cuh"
+
+namespace {
+
+constexpr int kWarpsPerCta = 4;
+
+// ---------------------------------------------------------------------------------------------------------------------
+// shared by K2a and K3a: stage one segment in shared memory and evaluate its k-mers
+struct SegStage {
+    uint8_t* base;    // 2-bit ranks, one per byte
+    uint8_t* qual;    // phred ranks (char - 33)
+    uint32_t* mask;   // one ballot word per chunk of 32 k-mer positions
+};
+
+__device__ __forceinline__ uint32_t kmer_hash_at(const uint8_t* sb, uint32_t j, uint32_t k) {
+    uint32_t h = 0;   // seqan3 views::kmer_hash(ungapped{k}): first base most significant
+    for (uint32_t t = 0; t < k; t++) h = (h << 2) | sb[j + t];
+    return h;
+}
+__device__ __forceinline__ uint32_t kmer_qual_at(const uint8_t* sq, uint32_t j, uint32_t k) {
+    uint32_t s = 0;   // views::kmer_quality (quality_filter.h:531-534): window sum of phred ranks
+    for (uint32_t t = 0; t < k; t++) s += sq[j + t];
+    return s;
+}
+
+// utils.h:160-178 with upper_bound = G-1 (see bm_api.cu sample_det for the ub==0 convention)
+__device__ __forceinline__ uint32_t sample_index(uint32_t i, uint32_t n, uint32_t G) {
+    if (G <= 1) return 0;
+    if (i + 1 == n) return G - 1;
+    double delta = __ddiv_rn((double)G, (double)(n - 1));
+    return (uint32_t)floor(__dmul_rn((double)(int)i, delta));
+}
+
+// position of the x-th (0-based) set bit over the chunk masks
+__device__ __forceinline__ uint32_t select_good(const uint32_t* mask, uint32_t nchunk, uint32_t x) {
+    uint32_t c = 0;
+    for (; c + 1 < nchunk; c++) {
+        uint32_t n = __popc(mask[c]);
+        if (x < n) break;
+        x -= n;
+    }
+    return c * 32 + __fns(mask[c], 0, (int)x + 1);
+}
+
+__device__ __forceinline__ void stage_segment(const SegStage& st, const uint8_t* __restrict__ seq,
+                                              const uint8_t* __restrict__ qual, uint64_t off, uint32_t n, uint32_t lane) {
+    for (uint32_t i = lane; i < n; i += 32) {
+        st.base[i] = (uint8_t)bm_rank_dna4(seq[off + i]);
+        st.qual[i] = (uint8_t)(qual[off + i] - 33);
+    }
+    __syncwarp();
+}
+
+// ---- K2a: good k-mers -> S samples -> row ids of both strands ------------------------------------------------------------
+// q_gram_mapper.h:431-469.  rowidx[((2*seg+strand)*S + s)*NQ + i] = kmer_to_index[(h_s >> 2i) & Q]  (or -1)
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_map_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, const uint64_t* __restrict__ read_off,
+             const uint32_t* __restrict__ seg_read, const uint32_t* __restrict__ seg_start,
+             const uint32_t* __restrict__ seg_len, uint32_t n_seg, uint32_t max_seg_len,
+             const int32_t* __restrict__ k2i, const uint32_t* __restrict__ distok, uint32_t k, uint32_t q, uint32_t S,
+             uint32_t minq, uint32_t min_good, int32_t* __restrict__ rowidx, uint8_t* __restrict__ segok,
+             unsigned long long* __restrict__ stats) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t seg = blockIdx.x * kWarpsPerCta + warp;
+    if (seg >= n_seg) return;
+    const uint32_t nchunk_max = (max_seg_len + 31) / 32 + 1;
+    const uint32_t per_warp = ((2 * max_seg_len + 3) & ~3u) + nchunk_max * 4;
+    SegStage st;
+    st.base = smem + (size_t)warp * per_warp;
+    st.qual = st.base + max_seg_len;
+    st.mask = reinterpret_cast<uint32_t*>(st.base + ((2 * max_seg_len + 3) & ~3u));
+
+    const uint32_t n = seg_len[seg];
+    const uint64_t off = read_off[seg_read[seg]] + seg_start[seg];
+    stage_segment(st, seq, qual, off, n, lane);
+
+    const uint32_t NQ = k - q + 1, Q = (1u << (2 * q)) - 1u;
+    const uint32_t nk = (n >= k) ? n - k + 1 : 0;
+    const uint32_t nchunk = (nk + 31) / 32;
+    uint32_t G = 0;
+    for (uint32_t c = 0; c < nchunk; c++) {
+        uint32_t j = c * 32 + lane;
+        bool good = false;
+        if (j < nk) {
+            uint32_t h = kmer_hash_at(st.base, j, k);
+            bool dist = false;                                    // q_gram_mapper.h:189-196
+            for (uint32_t i = 0; i < NQ; i++) {
+                uint32_t g = (h >> (2 * i)) & Q;
+                dist |= (__ldg(distok + (g >> 5)) >> (g & 31)) & 1u;
+            }
+            good = dist && kmer_qual_at(st.qual, j, k) >= minq;   // :437-442
+        }
+        uint32_t m = __ballot_sync(0xFFFFFFFFu, good);
+        if (lane == 0) st.mask[c] = m;
+        G += __popc(m);
+    }
+    __syncwarp();
+    const bool ok = G >= min_good && G > 0;                        // :445-447
+    if (lane == 0) segok[seg] = ok ? 1 : 0;
+    if (!ok) return;
+    uint32_t gathered = 0;
+    for (uint32_t s = lane; s < S; s += 32) {
+        uint32_t pos = select_good(st.mask, nchunk, sample_index(s, S, G));   // :457-460
+        uint32_t h = kmer_hash_at(st.base, pos, k);
+        uint32_t hr = bm_revcomp_hash(h, k);                                  // :465-468
+        int32_t* o0 = rowidx + ((size_t)(2 * seg) * S + s) * NQ;
+        int32_t* o1 = rowidx + ((size_t)(2 * seg + 1) * S + s) * NQ;
+        for (uint32_t i = 0; i < NQ; i++) {
+            int32_t a = __ldg(k2i + ((h >> (2 * i)) & Q)), b = __ldg(k2i + ((hr >> (2 * i)) & Q));
+            o0[i] = a; o1[i] = b;
+            gathered += (a >= 0) + (b >= 0);
+        }
+    }
+    for (int o = 16; o; o >>= 1) gathered += __shfl_xor_sync(0xFFFFFFFFu, gathered, o);
+    if (lane == 0 && gathered) atomicAdd(stats + 3, (unsigned long long)gathered);
+}
+
+// ---- K2: gather + vote --------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 and4(uint4 a, uint4 b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); }
+__device__ __forceinline__ uint4 or4(uint4 a, uint4 b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); }
+__device__ __forceinline__ uint4 xor4(uint4 a, uint4 b) { return make_uint4(a.x ^ b.x, a.y ^ b.y, a.z ^ b.z, a.w ^ b.w); }
+__device__ __forceinline__ uint4 andn4(uint4 a, uint4 b) { return make_uint4(a.x & ~b.x, a.y & ~b.y, a.z & ~b.z, a.w & ~b.w); }
+__device__ __forceinline__ uint4 not4(uint4 a) { return make_uint4(~a.x, ~a.y, ~a.z, ~a.w); }
+__device__ __forceinline__ bool any4(uint4 a) { return (a.x | a.y | a.z | a.w) != 0u; }
+__device__ __forceinline__ uint32_t popc4(uint4 a) { return __popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w); }
+
+// bits of column `col` (128 buckets) that are real buckets (< NB)
+__device__ __forceinline__ uint4 valid_bits(uint32_t col, uint32_t NB) {
+    uint32_t lo = col * 128u;
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint32_t b = lo + 32u * i;
+        w[i] = (b >= NB) ? 0u : (NB - b >= 32u ? 0xFFFFFFFFu : ((1u << (NB - b)) - 1u));
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+template <int NQ, int NP>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ rowidx,
+           const uint8_t* __restrict__ segok, uint32_t n_lists, uint32_t S, uint32_t F, uint32_t max_cand,
+           uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt) {
+    constexpr int B = (NQ >= 8) ? 1 : (8 / NQ);           // samples in flight per lane: B*NQ 128-bit loads
+    extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * Spad*NQ row ids
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t list = blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand
+    if (list >= n_lists) return;
+    if (!segok[list >> 1]) {                              // q_gram_mapper.h:445-447: too few good k-mers
+        if (lane == 0) cand_cnt[list] = 0;
+        return;
+    }
+    const uint32_t Spad = (S + B - 1) / B * B;
+    int32_t* my_idx = s_idx + (size_t)warp * Spad * NQ;
+    for (uint32_t t = lane; t < Spad * NQ; t += 32)
+        my_idx[t] = (t < S * NQ) ? rowidx[(size_t)list * S * NQ + t] : -2;   // -2: padding sample, contributes nothing
+    __syncwarp();
+
+    const uint4 ONES = make_uint4(~0u, ~0u, ~0u, ~0u), ZERO = make_uint4(0, 0, 0, 0);
+    uint32_t best = 0xFFFFFFFFu, count = 0;
+    uint32_t* out = cand_fixed + (size_t)list * max_cand;
+    const uint32_t ntile = (Wp16 + 31) / 32;
+    for (uint32_t tile = 0; tile < ntile; tile++) {
+        const uint32_t col = tile * 32 + lane;
+        const bool active = col < Wp16;
+        const uint4* colp = rows + (active ? col : 0);
+        uint4 p[NP];
+#pragma unroll
+        for (int i = 0; i < NP; i++) p[i] = ZERO;
+        for (uint32_t s = 0; s < Spad; s += B) {
+            uint4 v[B][NQ];
+#pragma unroll
+            for (int b = 0; b < B; b++)
+#pragma unroll
+                for (int i = 0; i < NQ; i++) {
+                    int32_t idx = my_idx[(s + b) * NQ + i];
+                    v[b][i] = ONES;                       // un-sampled q-gram: skipped in the AND (:404-405)
+                    if (idx >= 0 && active) v[b][i] = bm_ldg_stream(colp + (size_t)idx * Wp16);
+                }
+#pragma unroll
+            for (int b = 0; b < B; b++) {
+                uint4 bf = v[b][0];
+#pragma unroll
+                for (int i = 1; i < NQ; i++) bf = and4(bf, v[b][i]);
+                uint4 carry = not4(bf);                   // 1 = this sample misses the bucket
+                if (my_idx[(s + b) * NQ] == -2) carry = ZERO;
+#pragma unroll
+                for (int i = 0; i < NP; i++) { uint4 t = and4(p[i], carry); p[i] = xor4(p[i], carry); carry = t; }
+#pragma unroll
+                for (int i = 0; i < NP; i++) p[i] = or4(p[i], carry);   // saturate at 2^NP-1 (>= F by dispatch)
+            }
+        }
+        // buckets with miss count < F
+        uint4 lt = ZERO, eq = ONES;
+#pragma unroll
+        for (int i = NP - 1; i >= 0; i--) {
+            if ((F >> i) & 1u) { lt = or4(lt, andn4(eq, p[i])); eq = and4(eq, p[i]); }
+            else eq = andn4(eq, p[i]);
+        }
+        uint4 alive = active ? and4(lt, valid_bits(col, NB)) : ZERO;
+        if (!__any_sync(0xFFFFFFFFu, any4(alive))) continue;
+        // minimum miss count inside this lane's 128 buckets, and the buckets attaining it
+        uint32_t lvl = 0xFFFFu;
+        uint4 cand = alive;
+        if (any4(alive)) {
+            lvl = 0;
+#pragma unroll
+            for (int i = NP - 1; i >= 0; i--) {
+                uint4 t = andn4(cand, p[i]);
+                if (any4(t)) cand = t; else lvl |= 1u << i;
+            }
+        }
+        const uint32_t tmin = __reduce_min_sync(0xFFFFFFFFu, lvl);
+        if (tmin < best) { best = tmin; count = 0; }
+        if (tmin == best) {
+            uint32_t n = (lvl == best) ? popc4(cand) : 0u;
+            uint32_t incl = n;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= o) incl += t; }
+            uint32_t pos = count + incl - n;
+            if (n) {
+                uint32_t w[4] = {cand.x, cand.y, cand.z, cand.w};
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    uint32_t x = w[i];
+                    while (x) {
+                        uint32_t bit = __ffs(x) - 1; x &= x - 1;
+                        if (pos < max_cand) out[pos] = col * 128u + 32u * i + bit;   // ascending, like _Find_next
+                        pos++;
+                    }
+                }
+            }
+            count += __shfl_sync(0xFFFFFFFFu, incl, 31);
+        }
+    }
+    // :471-476: a list longer than the cap is emptied, not truncated
+    if (lane == 0) cand_cnt[list] = (best < F && count <= max_cand) ? count : 0u;
+}
+
+// ---- compaction of the fixed-slot lists into cand_off / cand ---------------------------------------------------------------
+__global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const uint32_t* __restrict__ cand_cnt,
+                               const uint32_t* __restrict__ cand_off, uint32_t n_lists, uint32_t max_cand,
+                               uint32_t* __restrict__ cand, uint32_t* __restrict__ cand_list,
+                               unsigned long long* __restrict__ stats) {
+    uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x;
+    if (2 * seg >= n_lists) return;
+    uint32_t tot = 0;
+    for (uint32_t d = 0; d < 2; d++) {
+        uint32_t l = 2 * seg + d, n = cand_cnt[l], o = cand_off[l];
+        for (uint32_t i = 0; i < n; i++) { cand[o + i] = cand_fixed[(size_t)l * max_cand + i]; cand_list[o + i] = l; }
+        if (n) atomicAdd(stats + 1 + d, (unsigned long long)n);
+        tot += n;
+    }
+    if (tot) atomicAdd(stats + 0, 1ull);
+}
+
+template <int NQ>
+cudaError_t launch_vote_np(bm_ctx* c, const bm_params* p, uint32_t NP, uint32_t n_lists, uint32_t blocks, size_t smem) {
+#define BM_VOTE(NPv)                                                                                               \
+    k_map_vote<NQ, NPv><<<blocks, kWarpsPerCta * 32, smem, c->stream>>>(                                           \
+        c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), n_lists,    \
+        p->mapper_samples, p->mapper_fault, p->max_candidates, c->d_cand_fixed.as<uint32_t>(),                     \
+        c->d_cand_cnt.as<uint32_t>())
+    if (NP == 3) BM_VOTE(3); else if (NP == 4) BM_VOTE(4); else BM_VOTE(6);
+#undef BM_VOTE
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" {
+
+int bm_map_device(bm_ctx* c, const bm_params* p) {
+    if (!c) return BM_E_ARG;
+    if (!p) BM_FAIL(c, BM_E_ARG, "bm_map_device: null parameters");
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_map_device: no index resident (the q-gram index is empty)");
+    if (!c->have_reads) BM_FAIL(c, BM_E_ARG, "bm_map_device: no read batch resident");
+    if (p->q != c->q) BM_FAIL(c, BM_E_ARG, "bm_map_device: index seed length differs from the resident index");
+    if (p->k < p->q || p->k > 16) BM_FAIL(c, BM_E_LIMIT, "query seed length must satisfy q <= k <= 16");
+    const uint32_t NQ = p->k - p->q + 1, S = p->mapper_samples, F = p->mapper_fault;
+    if (NQ > 8) BM_FAIL(c, BM_E_LIMIT, "k - q must be <= 7");
+    if (S == 0 || S > 256) BM_FAIL(c, BM_E_LIMIT, "mapper samples must be in [1,256]");
+    if (F == 0 || F > 63) BM_FAIL(c, BM_E_LIMIT, "mapper fault-tolerance levels must be in [1,63]");
+    if (p->max_candidates == 0 || p->max_candidates > 1024) BM_FAIL(c, BM_E_LIMIT, "max candidates must be in [1,1024]");
+    if (c->max_seg_len > 8192) BM_FAIL(c, BM_E_LIMIT, "segments longer than 8192 bases are not supported (-r)");
+    cudaSetDevice(c->device);
+    c->have_map = false; c->have_locs = false; c->have_aln = false;
+    int r = bm_internal_index_prepare(c, p->distinguishability);
+    if (r) return r;
+
+    const uint32_t n_seg = c->n_seg, n_lists = 2 * n_seg;
+    BM_CK(c, c->d_rowidx.ensure((size_t)n_lists * S * NQ * 4 + 16));
+    BM_CK(c, c->d_segok.ensure((size_t)n_seg + 16));
+    BM_CK(c, c->d_cand_fixed.ensure((size_t)n_lists * p->max_candidates * 4 + 16));
+    BM_CK(c, c->d_cand_cnt.ensure((size_t)(n_lists + 1) * 4));
+    BM_CK(c, c->d_cand_off.ensure((size_t)(n_lists + 1) * 4));
+    BM_CK(c, c->d_stats.ensure(128 * 8));
+    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 4 * 8, c->stream));
+    c->map_max_cand = p->max_candidates;
+    c->n_cand = 0;
+    if (n_seg) {
+        // smallest G with !(G < 0.2*S), the comparison of q_gram_mapper.h:445 in double
+        uint32_t min_good = 0;
+        while ((double)min_good < 0.2 * (double)S) min_good++;
+        const uint32_t msl = c->max_seg_len ? c->max_seg_len : 1;
+        size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
+        const uint32_t blocks_a = (n_seg + kWarpsPerCta - 1) / kWarpsPerCta;
+        if (smem_a > 48 * 1024)
+            BM_CK(c, cudaFuncSetAttribute(k_map_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a));
+        {
+            KScope ks(c, BM_K_SAMPLE);
+            k_map_sample<<<blocks_a, kWarpsPerCta * 32, smem_a, c->stream>>>(
+                c->d_seq.as<uint8_t>(), c->d_qual.as<uint8_t>(), c->d_read_off.as<uint64_t>(),
+                c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), n_seg, msl,
+                c->d_k2i.as<int32_t>(), c->d_distok.as<uint32_t>(), p->k, p->q, S, p->avg_base_quality * p->k, min_good,
+                c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
+        }
+        BM_CK(c, cudaGetLastError());
+        const uint32_t NP = (F <= 7) ? 3 : (F <= 15 ? 4 : 6);
+        const uint32_t Bs = (NQ >= 8) ? 1 : (8 / NQ);
+        const uint32_t Spad = (S + Bs - 1) / Bs * Bs;
+        size_t smem_v = (size_t)kWarpsPerCta * Spad * NQ * 4;
+        const uint32_t blocks_v = (n_lists + kWarpsPerCta - 1) / kWarpsPerCta;
+        cudaError_t e = cudaSuccess;
+        {
+            KScope ks(c, BM_K_MAP);
+            switch (NQ) {
+                case 1: e = launch_vote_np<1>(c, p, NP, n_lists, blocks_v, smem_v); break;
+                case 2: e = launch_vote_np<2>(c, p, NP, n_lists, blocks_v, smem_v); break;
+                case 3: e = launch_vote_np<3>(c, p, NP, n_lists, blocks_v, smem_v); break;
+                case 4: e = launch_vote_np<4>(c, p, NP, n_lists, blocks_v, smem_v); break;
+                case 5: e = launch_vote_np<5>(c, p, NP, n_lists, blocks_v, smem_v); break;
+                case 6: e = launch_vote_np<6>(c, p, NP, n_lists, blocks_v, smem_v); break;
+                case 7: e = launch_vote_np<7>(c, p, NP, n_lists, blocks_v, smem_v); break;
+                default: e = launch_vote_np<8>(c, p, NP, n_lists, blocks_v, smem_v); break;
+            }
+        }
+        BM_CK(c, e);
+        r = bm_internal_exclusive_scan(c, c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists + 1);
+        if (r) return r;
+        // the compacted arrays are at most max_candidates per list, but sizing them exactly needs the total
+        uint32_t total = 0;
+        BM_CK(c, cudaMemcpyAsync(&total, c->d_cand_off.as<uint32_t>() + n_lists, 4, cudaMemcpyDeviceToHost, c->stream));
+        BM_CK(c, cudaStreamSynchronize(c->stream));
+        c->n_cand = total;
+        BM_CK(c, c->d_cand.ensure((size_t)total * 4 + 16));
+        BM_CK(c, c->d_cseg.ensure((size_t)total * 4 + 16));
+        {
+            KScope ks(c, BM_K_AUX);
+            k_cand_compact<<<(n_seg + 255) / 256, 256, 0, c->stream>>>(
+                c->d_cand_fixed.as<uint32_t>(), c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists,
+                p->max_candidates, c->d_cand.as<uint32_t>(), c->d_cseg.as<uint32_t>(),
+                c->d_stats.as<unsigned long long>());
+        }
+        BM_CK(c, cudaGetLastError());
+    } else {
+        BM_CK(c, cudaMemsetAsync(c->d_cand_off.p, 0, 4, c->stream));
+    }
+    c->have_map = true;
+    return BM_OK;
+}
+
+int bm_map_download(bm_ctx* c, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats) {
+    if (!c) return BM_E_ARG;
+    if (!c->have_map) BM_FAIL(c, BM_E_ARG, "bm_map_download: bm_map_device first");
+    cudaSetDevice(c->device);
+    const uint32_t n_lists = 2 * c->n_seg;
+    if (cand_off) BM_CK(c, cudaMemcpyAsync(cand_off, c->d_cand_off.p, (size_t)(n_lists + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (cand && c->n_cand) {
+        if (cand_cap < c->n_cand) BM_FAIL(c, BM_E_ARG, "bm_map_download: candidate buffer too small");
+        BM_CK(c, cudaMemcpyAsync(cand, c->d_cand.p, (size_t)c->n_cand * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (stats) BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 4 * 8, cudaMemcpyDeviceToHost, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    return BM_OK;
+}
+
+int bm_map_reads(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
+                 uint32_t n_reads, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats) {
+    int r = bm_reads_upload(c, p, seq, qual, read_off, n_reads);
+    if (r) return r;
+    r = bm_map_device(c, p);
+    if (r) return r;
+    return bm_map_download(c, cand_off, cand, cand_cap, stats);
+}
+
+}  // extern "C"
