@@ -1,0 +1,381 @@
+#!/usr/bin/env python
+"""bench.py -- reads/sec mapped through the candidate-bucket hot path (BASELINE.json metric) on N B200s.
+
+A step is one pass of the hot path (mapper K2a+K2, locator K3a+K3+gather, best-location merge K3b) over one batch of
+synthetic reads.  Workload at any N: BASELINE config 1 of `configs` ("synthetic 1.7 Gbp reference, BUCKET_LEN=65536,
+1M x 300bp reads, 0.2% sub, 0.025% ins/del") per GPU -- reads are sharded, the index is replicated (weak scaling).
+
+  value     whole-job reads/s with the read batch resident in HBM (CUDA events on the library's stream, max over ranks)
+  e2e       the same through bm_map_locate() with pinned HOST buffers: H2D of bases/qualities/offsets and D2H of the
+            location records inside the timed region
+  roofline  the mapper vote kernel (k_map_vote): algorithmic bytes = rows gathered x W, time = CUDA events around each
+            launch inside the timed region
+  cpu_baseline / --impl reference: the CPU restatement of the reference (oracle/, "port") on the host cores, on a
+            bounded sample of the same workload
+
+The reference itself (SeqAn3-based, single-threaded) cannot be built here; `--impl reference` times
+oracle/_ref when it exists, else the oracle port with all host threads.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: (genome bases, bucket_len, read_len, sub, indel, frac)
+    "c1": dict(n_bases=4_600_000, L=65536, read_len=150, sub=0.002, indel=0.00025, frac=1.0,
+               desc="4.6 Mbp synthetic reference, L=65536, 150bp reads"),
+    "c2": dict(n_bases=1_700_000_000, L=65536, read_len=300, sub=0.002, indel=0.00025, frac=1.0,
+               desc="1.7 Gbp synthetic reference, L=65536, 300bp reads (0.2% sub, 0.025% ins/del), -f 1"),
+    "c3": dict(n_bases=3_100_000_000, L=65536, read_len=150, sub=0.002, indel=0.00025, frac=1.0,
+               desc="3.1 Gbp synthetic reference, L=65536, 150bp reads"),
+}
+FMH_X, FMH_Y = 40503, 7919
+GENOME_SEED, READ_SEED = 3, 4
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
+    ap.add_argument("--reads", type=int, default=1_000_000, help="reads per GPU per step")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock and throttle reasons of one GPU while the timed region runs (pynvml)"""
+
+    def __init__(self, index, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.sm, self.reasons, self.sm_max = [], set(), None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def stop(self):
+        self._stop.set()
+        if self.is_alive():
+            self.join()
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons)}
+
+
+def make_workload(cfg, n_reads, seed, region=None):
+    """genome (packed) + buckets + simulated reads.  region=(lo,hi): reads start inside that genome range."""
+    from bucketmap_b200 import datagen
+    packed = datagen.random_genome_packed(cfg["n_bases"], GENOME_SEED)
+    NB, b_start, b_len, _ = datagen.bucketize(np.array([cfg["n_bases"]], np.uint64), cfg["L"], 300)
+    return packed, NB, b_start, b_len
+
+
+def simulate(cfg, packed, n_reads, seed, n_span=None):
+    from bucketmap_b200 import datagen
+    return datagen.simulate_reads(packed, n_span or cfg["n_bases"], n_reads, cfg["read_len"], cfg["sub"],
+                                  cfg["indel"], cfg["indel"], seed)[:3]
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(workload_key):
+    """per-launch DRAM bytes of k_map_vote from the committed ncu --set full capture, if it was taken on this workload"""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            if d.get("workload") == workload_key:
+                return d.get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    return None
+
+
+# ------------------------------------------------------------------------------------------------- CPU (oracle) leg
+def cpu_leg(cfg, packed, NB, b_start, b_len, k2i, rows, n_sample, full_reads, threads):
+    """times the CPU restatement (map + locate + best-location merge) on a bounded sample of the workload.
+    The sample reads start inside the first n_sample/full_reads of the genome, so the number of reads per bucket (the
+    amortisation of the reference's per-bucket k-mer index build) matches the full workload."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import bm_oracle
+    bm_oracle.build()
+    o = bm_oracle.Oracle(threads)
+    P = o.params(cfg["L"])
+    span = max(int(cfg["n_bases"] * n_sample / full_reads), 4 * cfg["L"])
+    span = min(span, cfg["n_bases"])
+    seq, qual, off = simulate(cfg, packed, n_sample, READ_SEED + 1000, n_span=span)
+    segs = o.segments(P, off)
+    ix = o.index_open(P, NB, k2i, rows)
+    t0 = time.perf_counter()
+    coff, cand, stats = o.map_segments_h(ix, P, seq, qual, off, segs)
+    t1 = time.perf_counter()
+    loff, locs = o.locate(P, packed, b_start, b_len, seq, qual, off, segs, coff, cand)
+    foff, best = o.filter_best(P, off, loff, locs)
+    t2 = time.perf_counter()
+    o.index_close(ix)
+    return {"reads": n_sample, "seconds": t2 - t0, "map_s": t1 - t0, "locate_s": t2 - t1,
+            "reads_per_s": n_sample / (t2 - t0), "threads": o.threads, "n_locs": int(len(best)),
+            "span": span}
+
+
+def main():
+    a = parse()
+    cfg = CONFIGS[a.config]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    workload = f"{a.config}: {cfg['desc']}; {a.reads} reads per GPU per step"
+    metric, unit = "reads/sec mapped", "reads/s"
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        run_reference(a, cfg, workload, metric, unit)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    import bucketmap_b200 as bm
+    from bucketmap_b200 import dist as bmd
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = bm.Context(local)
+    P = bm.default_params(ctx.lib, cfg["L"])
+    q = 9
+
+    # ---- reference + index: every rank uploads the (seeded) genome; rank 0 builds the matrix, NCCL replicates it
+    t0 = time.perf_counter()
+    packed, NB, b_start, b_len = make_workload(cfg, a.reads, GENOME_SEED)
+    k2i, n_rows = fracminhash(q, FMH_X, FMH_Y, cfg["frac"])
+    ctx.ref_upload(packed, cfg["n_bases"], b_start, b_len, NB)
+    ctx.kernel_timing(True)
+    if rank == 0:
+        ctx.index_build(k2i, q, n_rows, download=False)
+        ctx.sync()
+    index_ms = ctx.kernel_stats()["index_build"][0]
+    bcast_ms = None
+    if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        tb = time.perf_counter()
+        nbytes = bmd.broadcast_index(ctx, k2i, q, n_rows, NB, local)
+        dist.barrier()
+        bcast_ms = (time.perf_counter() - tb) * 1e3
+    W = (NB + 7) >> 3
+
+    # ---- reads of this rank (its contiguous shard of the job's N*reads reads)
+    seq, qual, off = simulate(cfg, packed, a.reads, READ_SEED + rank)
+    n_reads = len(off) - 1
+    setup_s = time.perf_counter() - t0
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def gather():
+        if world > 1:
+            counts, locs = bmd.device_results(ctx, local)
+            return bmd.gather_locations(counts, locs)
+        return None
+
+    # ---- device-resident steps ------------------------------------------------------------------------------------
+    ctx.reads_upload(P, seq, qual, off)
+
+    def step_resident():
+        ctx.map_device(P)
+        ctx.locate_device(P, True)
+        gather()
+
+    for _ in range(a.warmup):
+        step_resident()
+    ctx.kernel_stats_reset()
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    ctx.timer_start()
+    for _ in range(a.steps):
+        step_resident()
+    ms = ctx.timer_stop()
+    barrier()
+    clk = clocks.stop()
+    kst = ctx.kernel_stats()
+    _, _, mstats = ctx.map_download()
+    tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms_max = float(tms.item())
+    value = world * n_reads * a.steps / (ms_max * 1e-3)
+
+    # ---- end to end: pinned host buffers -> bm_map_locate -> host records --------------------------------------------
+    hseq = ctx.pinned(len(seq), np.uint8); hseq[:] = seq
+    hqual = ctx.pinned(len(qual), np.uint8); hqual[:] = qual
+    hoff = ctx.pinned(len(off), np.uint64); hoff[:] = off
+    d2h = 0
+    for _ in range(max(1, min(a.warmup, 2))):
+        ooff, olocs, _ = ctx.map_locate(P, hseq, hqual, hoff, True)
+    barrier()
+    te = time.perf_counter()
+    for _ in range(a.steps):
+        ooff, olocs, _ = ctx.map_locate(P, hseq, hqual, hoff, True)
+        d2h = ooff.nbytes + olocs.nbytes + 32
+        gather()
+    barrier()
+    e2e_s = time.perf_counter() - te
+    t2 = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    e2e_value = world * n_reads * a.steps / float(t2.item())
+    h2d = hseq.nbytes + hqual.nbytes + hoff.nbytes
+
+    # ---- roofline of the dominant kernel -------------------------------------------------------------------------------
+    vote_ms, vote_n = kst["map_vote"]
+    rows_gathered = int(mstats[3])
+    alg_bytes = rows_gathered * W
+    peak, peak_src = measured_peak()
+    achieved = alg_bytes / (vote_ms / vote_n * 1e-3) / 1e9 if vote_n else None
+    traffic = ncu_traffic(f"{a.config}/{a.reads}")
+    launches = int(sum(v[1] for v in kst.values()))
+    out = {
+        "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u32 bitwise", "data": "synthetic",
+        "config": {"workload": workload, "genome_bases": cfg["n_bases"], "bucket_len": cfg["L"], "NB": NB,
+                   "row_bytes": W, "matrix_bytes": int(n_rows) * W, "reads_per_gpu_per_step": n_reads,
+                   "read_len": cfg["read_len"], "flags": "-k 9 -l 12 -s 15 -e 0.4 -p 10 -f %g" % cfg["frac"],
+                   "parallelism": f"reads sharded x{world}, index replicated",
+                   "l2": "inputs larger than L2 (bit matrix %d MB vs 126 MB L2)" % (n_rows * W >> 20),
+                   "step": "bm_map_device + bm_locate_device(filter_best=1)" + (" + NCCL gather" if world > 1 else "")},
+        "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "api": "bm_map_locate (pinned host buffers in, host records out)"},
+        "gpu_launches": launches,
+        "clocks": clk,
+        "roofline": {"kernel": "k_map_vote", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+                     "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes,
+                     "ms_per_launch": vote_ms / vote_n if vote_n else None,
+                     "rows_gathered_per_read": rows_gathered / max(1, n_reads)},
+        "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
+        "index_build_ms": index_ms, "index_bcast_ms": bcast_ms, "setup_s": setup_s,
+        "mapped": {"reads_with_candidate": int(mstats[0]), "cand_fwd": int(mstats[1]), "cand_rev": int(mstats[2])},
+    }
+    if rank == 0 and world == 1 and not a.no_cpu:
+        rows = ctx.index_download()
+        ncores = os.cpu_count() or 1
+        n_sample = a.cpu_sample or max(2000, min(50_000, 600 * ncores))
+        c = cpu_leg(cfg, packed, NB, b_start, b_len, k2i, rows, n_sample, a.reads, ncores)
+        out["cpu_baseline"] = {"value": c["reads_per_s"], "unit": unit, "cores": c["threads"], "kind": "port",
+                               "sample": f"{c['reads']} reads drawn from the first {c['span']} bases (same reads per "
+                                         f"bucket as the full batch), full index; map {c['map_s']:.2f}s + locate/merge "
+                                         f"{c['locate_s']:.2f}s"}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+    return 0
+
+
+def fracminhash(q, x, y, frac):
+    """tools/hash_function_generator.h:95-117 + indexer/bucket_indexer.h:147-159 (host logic of the product)"""
+    from bucketmap_b200 import hostlogic
+    return hostlogic.fracminhash(q, x, y, frac)
+
+
+def run_reference(a, cfg, workload, metric, unit):
+    """reference arm: the reference's CPU implementation of the path on the host cores (oracle port; all threads)"""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import bm_oracle
+    bm_oracle.build()
+    ncores = os.cpu_count() or 1
+    o = bm_oracle.Oracle(ncores)
+    packed, NB, b_start, b_len = make_workload(cfg, a.reads, GENOME_SEED)
+    k2i, n_rows = o.fracminhash(9, FMH_X, FMH_Y, cfg["frac"])
+    rows = o.index_build(packed, b_start, b_len, NB, 9, k2i, n_rows)
+    P = o.params(cfg["L"])
+    n_sample = a.cpu_sample or max(2000, min(50_000, 600 * ncores))
+    span = min(max(int(cfg["n_bases"] * n_sample / a.reads), 4 * cfg["L"]), cfg["n_bases"])
+    seq, qual, off = simulate(cfg, packed, n_sample, READ_SEED + 1000, n_span=span)
+    segs = o.segments(P, off)
+    ix = o.index_open(P, NB, k2i, rows)
+
+    def step():
+        coff, cand, _ = o.map_segments_h(ix, P, seq, qual, off, segs)
+        loff, locs = o.locate(P, packed, b_start, b_len, seq, qual, off, segs, coff, cand)
+        return o.filter_best(P, off, loff, locs)
+
+    for _ in range(min(a.warmup, 1)):
+        step()
+    steps = max(1, min(a.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    v = n_sample * steps / dt
+    sample = (f"{n_sample} reads per step drawn from the first {span} bases (same reads per bucket as the full "
+              f"batch), full index, {steps} timed steps")
+    print(json.dumps({
+        "impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": a.gpus, "steps": steps,
+        "warmup": min(a.warmup, 1), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64 bitwise", "data": "synthetic",
+        "config": {"workload": workload, "NB": NB, "note": "CPU restatement of the reference (oracle/), all host threads"},
+        "cpu_baseline": {"value": v, "unit": unit, "cores": o.threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -49,6 +49,7 @@ SIGNATURES = {
     "bm_index_download": (C.c_int, [_vp, _vp]),
     "bm_index_zeros": (C.c_int, [_vp, C.c_float, _vp, C.POINTER(C.c_uint32)]),
     "bm_index_free": (C.c_int, [_vp]),
+    "bm_index_alloc": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32]),
     "bm_index_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
     "bm_ref_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
     "bm_reads_upload": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, C.c_uint32]),
@@ -59,6 +60,7 @@ SIGNATURES = {
     "bm_locate_device": (C.c_int, [_vp, C.POINTER(Params), C.c_int]),
     "bm_locate_download": (C.c_int, [_vp, _vp, _vp, C.c_uint64]),
     "bm_locate_count": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "bm_locate_device_buffers": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_uint64)]),
     "bm_map_locate": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, C.c_uint32, C.c_int, _vp, _vp, C.c_uint64,
                                 _vp]),
     "bm_align_device": (C.c_int, [_vp, C.POINTER(Params)]),
@@ -85,7 +87,7 @@ def load_library(path=LIB_PATH):
         raise BucketMapError(f"{path} is missing: run `make lib` (python -c 'import __graft_entry__ as g; g.build()')")
     lib = C.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
-        fn = getattr(lib, name)
+        fn = getattr(lib, name)   # AttributeError here = stale library: rebuild with `make lib`
         fn.restype, fn.argtypes = res, args
     return lib
 
@@ -236,6 +238,18 @@ class Context:
         locs = np.empty(n.value, LOC_DTYPE)
         self._ck(self.lib.bm_locate_download(self.h, _ptr(off), _ptr(locs), n.value), "bm_locate_download")
         return off, locs
+
+    def locate_device_buffers(self):
+        """(loc_off device pointer, locs device pointer, n_locs) of the last locate_device"""
+        a, b, n = _vp(), _vp(), C.c_uint64()
+        self._ck(self.lib.bm_locate_device_buffers(self.h, C.byref(a), C.byref(b), C.byref(n)),
+                 "bm_locate_device_buffers")
+        return a.value, b.value, n.value
+
+    def index_alloc(self, k2i, q, n_rows, NB):
+        k2i = np.ascontiguousarray(k2i, np.int32)
+        self._ck(self.lib.bm_index_alloc(self.h, _ptr(k2i), q, n_rows, NB), "bm_index_alloc")
+        self.NB, self.n_rows = NB, n_rows
 
     def map_locate(self, P, seq, qual, read_off, filter_best=True):
         n = len(read_off) - 1

@@ -1,0 +1,336 @@
+// bm_align.cu -- bucketmap_align's verification (K4): semi-global unit-cost edit distance of the whole read against the
+// text window of every located candidate, with begin position and CIGAR.
+//
+// Replaces seqan3::align_pairwise(edit_scheme, free end gaps in sequence1=text) + cigar_from_alignment at
+// locator/bucket_locator.h:520-528,548-589.
+//
+// One thread per alignment.  Forward pass: Myers' bit-vector recurrence in its block form (64 query rows per word, NW
+// words in registers, horizontal carry between words), one text column per step; after each column the thread stores
+// the vertical delta vectors (Pv, Mv) and the score at every word boundary to a column-major scratch record, so the
+// warp's stores are contiguous.  The best end column is the LAST column attaining the minimum of the bottom row.
+// Traceback: any cell value is boundary score + popcount of the masked deltas of ONE word, so the thread walks back
+// from (m, end) reading two records per step and prefers diagonal, then up (query base consumed: I), then left (text
+// base consumed: D) -- the conventions of the oracle (oracle/bm_oracle.cpp align_semi_global; seqan3's own tie-breaks
+// are not available in this environment).
+#include <algorithm>
+
+#include "bm_internal.cuh"
+
+namespace {
+
+constexpr int kAlnThreads = 128;
+constexpr uint32_t kCigTmp = 16;       // ops kept per alignment in the first pass
+
+struct AlignArgs {
+    const uint8_t* packed; const uint64_t* bstart; const uint32_t* blen;
+    const uint8_t* seq; const uint64_t* read_off; uint32_t n_reads;
+    const uint32_t* loc_off; const bm_loc* locs;
+    float indel_rate; uint32_t quality_threshold;
+    unsigned long long* scratch; uint32_t chunk_n;
+    bm_aln* aln; uint32_t* cig_tmp; uint32_t* cig_cnt;
+    const uint32_t* cig_off; uint32_t* cigar; const uint32_t* over_list;
+};
+
+template <int NW> struct Rec { static constexpr int kWords = (2 * NW + (NW + 3) / 4 + 1) & ~1; };
+
+__device__ __forceinline__ uint32_t read_of_loc(const uint32_t* loc_off, uint32_t n_reads, uint32_t id) {
+    uint32_t lo = 0, hi = n_reads;            // last r with loc_off[r] <= id
+    while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (loc_off[mid] <= id) lo = mid; else hi = mid; }
+    return lo;
+}
+
+template <int NW>
+struct Tracer {
+    const unsigned long long* scratch; size_t stride; uint32_t slot;
+    __device__ __forceinline__ unsigned long long word(uint32_t col, uint32_t w) const {
+        return scratch[((size_t)col * stride + slot) * Rec<NW>::kWords + w];
+    }
+    // D[i][col]
+    __device__ __forceinline__ int cell(uint32_t col, uint32_t i) const {
+        if (i == 0) return 0;
+        const uint32_t w = (i - 1) >> 6, nb = i - 64 * w;
+        const unsigned long long mask = nb == 64 ? ~0ull : ((1ull << nb) - 1ull);
+        const unsigned long long pv = word(col, w), mv = word(col, NW + w);
+        const int bs = (int)((word(col, 2 * NW + (w >> 2)) >> (16 * (w & 3))) & 0xFFFFull);
+        return bs + __popcll(pv & mask) - __popcll(mv & mask);
+    }
+    // D[i][col] - D[i-1][col], i >= 1
+    __device__ __forceinline__ int vdelta(uint32_t col, uint32_t i) const {
+        const uint32_t w = (i - 1) >> 6, b = (i - 1) & 63;
+        return (int)((word(col, w) >> b) & 1ull) - (int)((word(col, NW + w) >> b) & 1ull);
+    }
+};
+
+// MODE 0: first pass (score, begin, op count, first kCigTmp ops reversed); MODE 1: overflow list, ops written in place
+template <int NW, int MODE>
+__global__ void __launch_bounds__(kAlnThreads)
+k_align(AlignArgs a, uint32_t first, uint32_t count) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const uint32_t id = MODE ? a.over_list[first + t] : first + t;
+    const bm_loc l = a.locs[id];
+    const uint32_t r = read_of_loc(a.loc_off, a.n_reads, id);
+    const uint8_t* q = a.seq + a.read_off[r];
+    const uint32_t m = (uint32_t)(a.read_off[r + 1] - a.read_off[r]);
+    const uint32_t blen = a.blen[l.bucket];
+    bm_aln out;
+    out.score = 0; out.begin = 0; out.map_qual = 0; out.kept = 0; out.cigar_off = 0; out.cigar_len = 0;
+    // a negative or out-of-bucket offset makes the reference slice its bucket out of range (undefined there):
+    // such a location is reported as not kept with an empty alignment
+    if (l.offset < 0 || (uint32_t)l.offset >= blen || m == 0 || m > 64u * NW) {
+        if (!MODE) { a.aln[id] = out; a.cig_cnt[id] = 0; }
+        return;
+    }
+    // :550  width = min(|query| + 1 + (size_t)(rate * |read|), |bucket| - offset)
+    const uint32_t extra = (uint32_t)(unsigned long long)__fmul_rn(a.indel_rate, (float)m);
+    const uint32_t n = min(m + 1u + extra, blen - (uint32_t)l.offset);
+    const uint64_t tbase = a.bstart[l.bucket] + (uint32_t)l.offset;
+    const bool rev = l.is_original == 0;
+
+    unsigned long long P0[NW], P1[NW], P2[NW], P3[NW];
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+        unsigned long long p0 = 0, p1 = 0, p2 = 0, p3 = 0;
+        const uint32_t lim = (m > 64u * w) ? min(64u, m - 64u * w) : 0u;
+        for (uint32_t b = 0; b < lim; b++) {
+            const uint32_t c = bm_rank_dna4(q[64 * w + b]);
+            const unsigned long long bit = 1ull << b;
+            p0 |= (c == 0) ? bit : 0ull; p1 |= (c == 1) ? bit : 0ull;
+            p2 |= (c == 2) ? bit : 0ull; p3 |= (c == 3) ? bit : 0ull;
+        }
+        P0[w] = p0; P1[w] = p1; P2[w] = p2; P3[w] = p3;
+    }
+    unsigned long long Pv[NW], Mv[NW];
+    int bs[NW];
+#pragma unroll
+    for (int w = 0; w < NW; w++) { Pv[w] = ~0ull; Mv[w] = 0ull; bs[w] = 64 * w; }
+    const uint32_t lastw = (m - 1) >> 6, lastb = (m - 1) & 63;
+    const size_t stride = a.chunk_n;
+    unsigned long long* rec0 = a.scratch + (size_t)t * Rec<NW>::kWords;
+    auto store = [&](uint32_t col) {
+        unsigned long long rec[Rec<NW>::kWords];
+#pragma unroll
+        for (int w = 0; w < Rec<NW>::kWords; w++) rec[w] = 0ull;
+#pragma unroll
+        for (int w = 0; w < NW; w++) {
+            rec[w] = Pv[w]; rec[NW + w] = Mv[w];
+            rec[2 * NW + (w >> 2)] |= (unsigned long long)(bs[w] & 0xFFFF) << (16 * (w & 3));
+        }
+        ulonglong2* dst = reinterpret_cast<ulonglong2*>(rec0 + (size_t)col * stride * Rec<NW>::kWords);
+#pragma unroll
+        for (int w = 0; w < Rec<NW>::kWords / 2; w++) dst[w] = make_ulonglong2(rec[2 * w], rec[2 * w + 1]);
+    };
+    store(0);
+    int score = (int)m, best = (int)m;
+    uint32_t bj = 0;
+    for (uint32_t j = 1; j <= n; j++) {
+        const uint32_t tc = rev ? 3u - bm_gbase(a.packed, tbase + (n - j)) : bm_gbase(a.packed, tbase + (j - 1));   // :563-567
+        int hin = 0;
+#pragma unroll
+        for (int w = 0; w < NW; w++) {
+            unsigned long long Eq = tc == 0 ? P0[w] : (tc == 1 ? P1[w] : (tc == 2 ? P2[w] : P3[w]));
+            const unsigned long long hneg = hin < 0 ? 1ull : 0ull, hpos = hin > 0 ? 1ull : 0ull;
+            const unsigned long long Xv = Eq | Mv[w];
+            Eq |= hneg;
+            const unsigned long long Xh = (((Eq & Pv[w]) + Pv[w]) ^ Pv[w]) | Eq;
+            unsigned long long Ph = Mv[w] | ~(Xh | Pv[w]);
+            unsigned long long Mh = Pv[w] & Xh;
+            if (w == (int)lastw) score += (int)((Ph >> lastb) & 1ull) - (int)((Mh >> lastb) & 1ull);
+            const int hout = (int)(Ph >> 63) - (int)(Mh >> 63);
+            Ph = (Ph << 1) | hpos;
+            Mh = (Mh << 1) | hneg;
+            Pv[w] = Mh | ~(Xv | Ph);
+            Mv[w] = Ph & Xv;
+            if (w + 1 < NW) bs[w + 1] += hout;
+            hin = hout;
+        }
+        store(j);
+        if (score <= best) { best = score; bj = j; }        // last column attaining the minimum
+    }
+    // traceback from (m, bj)
+    Tracer<NW> tr{a.scratch, stride, t};
+    uint32_t i = m, j = bj, nops = 0, cur_op = 3, cur_len = 0;
+    int cur = best;
+    uint32_t* tmp = a.cig_tmp + (size_t)id * kCigTmp;
+    uint32_t wpos = 0;
+    if (MODE) wpos = a.cig_off[id] + a.aln[id].cigar_len;    // ops are produced last-to-first: fill backwards
+    auto flush = [&]() {
+        if (cur_len) {
+            const uint32_t op = (cur_len << 4) | cur_op;
+            if (MODE) a.cigar[--wpos] = op;
+            else if (nops < kCigTmp) tmp[nops] = op;
+            nops++;
+        }
+    };
+    while (i > 0) {
+        uint32_t op;
+        int nxt;
+        const int dg = (j > 0) ? tr.cell(j - 1, i - 1) : 0;
+        bool mism = true;
+        if (j > 0) {
+            const uint32_t tc = rev ? 3u - bm_gbase(a.packed, tbase + (n - j)) : bm_gbase(a.packed, tbase + (j - 1));
+            mism = bm_rank_dna4(q[i - 1]) != tc;
+        }
+        if (j > 0 && cur == dg + (mism ? 1 : 0)) { op = 0; nxt = dg; }
+        else {
+            const int up = cur - tr.vdelta(j, i);
+            if (cur == up + 1) { op = 1; nxt = up; }
+            else { op = 2; nxt = tr.cell(j - 1, i); }
+        }
+        if (op != cur_op) { flush(); cur_op = op; cur_len = 0; }
+        cur_len++;
+        cur = nxt;
+        if (op == 0) { i--; j--; } else if (op == 1) { i--; } else { j--; }
+    }
+    flush();
+    if (!MODE) {
+        out.score = -best;
+        out.begin = j;
+        out.map_qual = 60u + (uint32_t)out.score;                                    // :570, 32-bit wrap
+        out.kept = ((unsigned long long)out.map_qual >= (unsigned long long)a.quality_threshold) ? 1u : 0u;
+        out.cigar_len = nops;
+        a.aln[id] = out;
+        a.cig_cnt[id] = nops;
+    }
+}
+
+// final CIGAR arrays: reverse the first-pass ops into place; alignments with more ops than kCigTmp go to the overflow list
+__global__ void k_cigar_write(bm_aln* __restrict__ aln, const uint32_t* __restrict__ cig_off,
+                              const uint32_t* __restrict__ cig_tmp, uint32_t n, uint32_t* __restrict__ cigar,
+                              uint32_t* __restrict__ over_list, uint32_t* __restrict__ n_over) {
+    uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n) return;
+    const uint32_t len = aln[id].cigar_len, off = cig_off[id];
+    aln[id].cigar_off = off;
+    if (len > kCigTmp) { over_list[atomicAdd(n_over, 1u)] = id; return; }
+    for (uint32_t t = 0; t < len; t++) cigar[off + t] = cig_tmp[(size_t)id * kCigTmp + (len - 1 - t)];
+}
+
+template <int NW>
+cudaError_t run_align(bm_ctx* c, AlignArgs& a, uint32_t n_aln, uint32_t max_cols) {
+    // first pass in chunks sized by the scratch budget
+    const size_t rec = (size_t)Rec<NW>::kWords * 8;
+    size_t free_b = 0, total_b = 0;
+    cudaError_t e = cudaMemGetInfo(&free_b, &total_b);
+    if (e != cudaSuccess) return e;
+    size_t budget = free_b / 2 + c->d_aln_scratch.cap;
+    if (budget > ((size_t)16 << 30)) budget = (size_t)16 << 30;
+    size_t per = rec * max_cols;
+    uint32_t chunk = (uint32_t)std::min<size_t>(n_aln, std::max<size_t>(budget / per, kAlnThreads));
+    chunk = (chunk + kAlnThreads - 1) / kAlnThreads * kAlnThreads;
+    e = c->d_aln_scratch.ensure((size_t)chunk * per);
+    if (e != cudaSuccess) return e;
+    a.scratch = c->d_aln_scratch.as<unsigned long long>();
+    a.chunk_n = chunk;
+    for (uint32_t first = 0; first < n_aln; first += chunk) {
+        const uint32_t cnt = std::min(chunk, n_aln - first);
+        KScope ks(c, BM_K_ALIGN);
+        k_align<NW, 0><<<(cnt + kAlnThreads - 1) / kAlnThreads, kAlnThreads, 0, c->stream>>>(a, first, cnt);
+    }
+    return cudaGetLastError();
+}
+
+template <int NW>
+cudaError_t run_align_over(bm_ctx* c, AlignArgs& a, uint32_t n_over) {
+    for (uint32_t first = 0; first < n_over; first += a.chunk_n) {
+        const uint32_t cnt = std::min(a.chunk_n, n_over - first);
+        KScope ks(c, BM_K_ALIGN);
+        k_align<NW, 1><<<(cnt + kAlnThreads - 1) / kAlnThreads, kAlnThreads, 0, c->stream>>>(a, first, cnt);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" {
+
+int bm_align_device(bm_ctx* c, const bm_params* p) {
+    if (!c) return BM_E_ARG;
+    if (!p) BM_FAIL(c, BM_E_ARG, "bm_align_device: null parameters");
+    if (!c->have_locs || c->locs_filtered)
+        BM_FAIL(c, BM_E_ARG, "bm_align_device: bm_locate_device(filter_best=0) first (bucketmap_align verifies every location)");
+    cudaSetDevice(c->device);
+    c->have_aln = false;
+    uint64_t n64 = 0;
+    int r = bm_locate_count(c, &n64);
+    if (r) return r;
+    const uint32_t n_aln = (uint32_t)n64;
+    c->n_aln = n_aln; c->n_cigar = 0;
+    BM_CK(c, c->d_aln.ensure((size_t)(n_aln + 1) * sizeof(bm_aln)));
+    BM_CK(c, c->d_cigar_cnt.ensure((size_t)(n_aln + 1) * 4));
+    BM_CK(c, c->d_cigar_off.ensure((size_t)(n_aln + 1) * 4));
+    if (n_aln == 0) { c->have_aln = true; return BM_OK; }
+    const uint32_t max_len = c->max_read_len;
+    if (max_len > 1024) BM_FAIL(c, BM_E_LIMIT, "bm_align_device: reads longer than 1024 bases are not supported by the verifier");
+    const uint32_t max_cols = max_len + 2 + (uint32_t)(p->indel_rate * (float)max_len) + 1;
+    BM_CK(c, c->d_cigar_fixed.ensure((size_t)n_aln * kCigTmp * 4));
+    BM_CK(c, cudaMemsetAsync((uint32_t*)c->d_cigar_cnt.p + n_aln, 0, 4, c->stream));
+    AlignArgs a;
+    a.packed = c->d_packed.as<uint8_t>(); a.bstart = c->d_bstart.as<uint64_t>(); a.blen = c->d_blen.as<uint32_t>();
+    a.seq = c->d_seq.as<uint8_t>(); a.read_off = c->d_read_off.as<uint64_t>(); a.n_reads = c->n_reads;
+    a.loc_off = c->d_loc_off.as<uint32_t>(); a.locs = c->d_locs.as<bm_loc>();
+    a.indel_rate = p->indel_rate; a.quality_threshold = p->quality_threshold;
+    a.scratch = nullptr; a.chunk_n = 0;
+    a.aln = c->d_aln.as<bm_aln>(); a.cig_tmp = c->d_cigar_fixed.as<uint32_t>(); a.cig_cnt = c->d_cigar_cnt.as<uint32_t>();
+    a.cig_off = c->d_cigar_off.as<uint32_t>(); a.cigar = nullptr; a.over_list = nullptr;
+    const uint32_t nw = (max_len + 63) / 64;
+    cudaError_t e;
+    if (nw <= 1) e = run_align<1>(c, a, n_aln, max_cols);
+    else if (nw <= 2) e = run_align<2>(c, a, n_aln, max_cols);
+    else if (nw <= 3) e = run_align<3>(c, a, n_aln, max_cols);
+    else if (nw <= 4) e = run_align<4>(c, a, n_aln, max_cols);
+    else if (nw <= 5) e = run_align<5>(c, a, n_aln, max_cols);
+    else if (nw <= 8) e = run_align<8>(c, a, n_aln, max_cols);
+    else e = run_align<16>(c, a, n_aln, max_cols);
+    BM_CK(c, e);
+    r = bm_internal_exclusive_scan(c, c->d_cigar_cnt.as<uint32_t>(), c->d_cigar_off.as<uint32_t>(), n_aln + 1);
+    if (r) return r;
+    uint32_t total = 0;
+    BM_CK(c, cudaMemcpyAsync(&total, c->d_cigar_off.as<uint32_t>() + n_aln, 4, cudaMemcpyDeviceToHost, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->n_cigar = total;
+    BM_CK(c, c->d_cigar.ensure((size_t)total * 4 + 16));
+    BM_CK(c, c->d_vote_scratch.ensure((size_t)(n_aln + 2) * 4));
+    uint32_t* over_list = c->d_vote_scratch.as<uint32_t>();
+    uint32_t* n_over = over_list + n_aln;
+    BM_CK(c, cudaMemsetAsync(n_over, 0, 4, c->stream));
+    a.cigar = c->d_cigar.as<uint32_t>(); a.over_list = over_list;
+    {
+        KScope ks(c, BM_K_AUX);
+        k_cigar_write<<<(n_aln + 255) / 256, 256, 0, c->stream>>>(c->d_aln.as<bm_aln>(), c->d_cigar_off.as<uint32_t>(),
+                                                                   c->d_cigar_fixed.as<uint32_t>(), n_aln,
+                                                                   c->d_cigar.as<uint32_t>(), over_list, n_over);
+    }
+    BM_CK(c, cudaGetLastError());
+    uint32_t h_over = 0;
+    BM_CK(c, cudaMemcpyAsync(&h_over, n_over, 4, cudaMemcpyDeviceToHost, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    if (h_over) {
+        if (nw <= 1) e = run_align_over<1>(c, a, h_over);
+        else if (nw <= 2) e = run_align_over<2>(c, a, h_over);
+        else if (nw <= 3) e = run_align_over<3>(c, a, h_over);
+        else if (nw <= 4) e = run_align_over<4>(c, a, h_over);
+        else if (nw <= 5) e = run_align_over<5>(c, a, h_over);
+        else if (nw <= 8) e = run_align_over<8>(c, a, h_over);
+        else e = run_align_over<16>(c, a, h_over);
+        BM_CK(c, e);
+    }
+    c->have_aln = true;
+    return BM_OK;
+}
+
+int bm_align_download(bm_ctx* c, bm_aln* aln, uint32_t* cigar, uint64_t cigar_cap, uint64_t* cigar_used) {
+    if (!c) return BM_E_ARG;
+    if (!c->have_aln) BM_FAIL(c, BM_E_ARG, "bm_align_download: bm_align_device first");
+    cudaSetDevice(c->device);
+    if (cigar_used) *cigar_used = c->n_cigar;
+    if (aln && c->n_aln) BM_CK(c, cudaMemcpyAsync(aln, c->d_aln.p, (size_t)c->n_aln * sizeof(bm_aln), cudaMemcpyDeviceToHost, c->stream));
+    if (cigar && c->n_cigar) {
+        if (cigar_cap < c->n_cigar) BM_FAIL(c, BM_E_ARG, "bm_align_download: cigar buffer too small");
+        BM_CK(c, cudaMemcpyAsync(cigar, c->d_cigar.p, (size_t)c->n_cigar * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    return BM_OK;
+}
+
+}  // extern "C"

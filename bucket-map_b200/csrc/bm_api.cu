@@ -41,7 +41,7 @@ void bm_ctx_destroy(bm_ctx* c) {
                       &c->d_seg_len, &c->d_rowidx, &c->d_segok, &c->d_cand_fixed, &c->d_cand_cnt, &c->d_cand_off,
                       &c->d_cand, &c->d_stats, &c->d_scan_tmp, &c->d_lsamp_idx, &c->d_lsamp_hash, &c->d_cres_pos,
                       &c->d_cres_votes, &c->d_cseg, &c->d_loc_cnt, &c->d_loc_off, &c->d_locs, &c->d_locs2,
-                      &c->d_loc_off2, &c->d_vote_scratch, &c->d_aln, &c->d_cigar_fixed, &c->d_cigar_cnt,
+                      &c->d_loc_off2, &c->d_vote_scratch, &c->d_locs3, &c->d_loc_pool, &c->d_loc_flags, &c->d_read_seg0, &c->d_aln, &c->d_cigar_fixed, &c->d_cigar_cnt,
                       &c->d_cigar_off, &c->d_cigar, &c->d_aln_scratch, &c->d_flush};
     for (DevBuf* b : bufs) b->release();
     for (auto& p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
@@ -117,14 +117,16 @@ int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uin
     uint64_t nbytes = read_off[n_reads] - read_off[0];
     if (read_off[0] != 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off[0] must be 0");
     // segment table: q_gram_mapper.h:509-523 / bucket_locator.h:302-313
-    c->h_seg_read.clear(); c->h_seg_start.clear(); c->h_seg_len.clear();
+    c->h_seg_read.clear(); c->h_seg_start.clear(); c->h_seg_len.clear(); c->h_read_seg0.clear();
     std::vector<uint32_t> st;
-    uint32_t mx = 0;
+    uint32_t mx = 0, mxr = 0;
     for (uint32_t i = 0; i < n_reads; i++) {
         if (read_off[i + 1] < read_off[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
         uint64_t len64 = read_off[i + 1] - read_off[i];
         if (len64 > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31");
         uint32_t len = (uint32_t)len64;
+        if (len > mxr) mxr = len;
+        c->h_read_seg0.push_back((uint32_t)c->h_seg_read.size());
         if (len > 2 * p->read_len) sample_det(p->num_segment_samples, len - p->read_len - 1, st);
         else st.assign(1, 0u);
         for (uint32_t s : st) {
@@ -134,6 +136,9 @@ int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uin
         }
     }
     uint32_t n_seg = (uint32_t)c->h_seg_read.size();
+    c->h_read_seg0.push_back(n_seg);
+    BM_CK(c, c->d_read_seg0.ensure((size_t)(n_reads + 1) * 4));
+    BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.p, c->h_read_seg0.data(), (size_t)(n_reads + 1) * 4, cudaMemcpyHostToDevice, c->stream));
     BM_CK(c, c->d_seq.ensure(nbytes + 16));
     BM_CK(c, c->d_qual.ensure(nbytes + 16));
     BM_CK(c, c->d_read_off.ensure((size_t)(n_reads + 1) * 8));
@@ -151,7 +156,7 @@ int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uin
         BM_CK(c, cudaMemcpyAsync(c->d_seg_len.p, c->h_seg_len.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
     }
     BM_CK(c, cudaStreamSynchronize(c->stream));   // host vectors / caller buffers may be reused after return
-    c->n_reads = n_reads; c->n_seg = n_seg; c->max_seg_len = mx; c->n_read_bytes = nbytes;
+    c->n_reads = n_reads; c->n_seg = n_seg; c->max_seg_len = mx; c->max_read_len = mxr; c->n_read_bytes = nbytes;
     c->have_reads = true;
     return BM_OK;
 }

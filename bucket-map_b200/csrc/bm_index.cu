@@ -211,6 +211,35 @@ int bm_index_zeros(bm_ctx* c, float d, uint32_t* zeros_out, uint32_t* valid) {
     return BM_OK;
 }
 
+int bm_index_alloc(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t NB) {
+    if (!c) return BM_E_ARG;
+    if (!k2i) BM_FAIL(c, BM_E_ARG, "bm_index_alloc: kmer_to_index is null");
+    cudaSetDevice(c->device);
+    int r = set_table(c, k2i, q, n_rows, NB);
+    if (r) return r;
+    BM_CK(c, cudaMemsetAsync(c->d_rows.p, 0, (size_t)n_rows * c->Wp + 64, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->have_index = true;
+    return BM_OK;
+}
+
+int bm_index_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
+    if (!c) return BM_E_ARG;
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_index_device: no index resident");
+    c->zeros_for_d = -1.f;                       // the caller may overwrite the rows: recompute zeros on next use
+    if (dptr) *dptr = c->d_rows.p;
+    if (bytes) *bytes = (uint64_t)c->n_rows * c->Wp;
+    return BM_OK;
+}
+
+int bm_ref_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
+    if (!c) return BM_E_ARG;
+    if (!c->d_packed.p) BM_FAIL(c, BM_E_ARG, "bm_ref_device: bm_ref_upload first");
+    if (dptr) *dptr = c->d_packed.p;
+    if (bytes) *bytes = (c->n_bases + 3) / 4;
+    return BM_OK;
+}
+
 int bm_index_free(bm_ctx* c) {
     if (!c) return BM_E_ARG;
     cudaSetDevice(c->device);

@@ -48,9 +48,10 @@ struct bm_ctx {
     uint32_t dist_threshold = 0, dist_valid = 0;
 
     // read batch
-    DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len;
+    DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len, d_read_seg0;
+    std::vector<uint32_t> h_read_seg0;
     std::vector<uint32_t> h_seg_read, h_seg_start, h_seg_len;
-    uint32_t n_reads = 0, n_seg = 0, max_seg_len = 0;
+    uint32_t n_reads = 0, n_seg = 0, max_seg_len = 0, max_read_len = 0;
     uint64_t n_read_bytes = 0;
     bool have_reads = false;
 
@@ -62,9 +63,9 @@ struct bm_ctx {
 
     // locator results
     DevBuf d_lsamp_idx, d_lsamp_hash, d_cres_pos, d_cres_votes, d_cseg, d_loc_cnt, d_loc_off, d_locs, d_locs2,
-           d_loc_off2, d_vote_scratch;
-    uint64_t n_locs = 0;
-    bool have_locs = false, locs_filtered = false;
+           d_loc_off2, d_vote_scratch, d_locs3, d_loc_pool, d_loc_flags;
+    uint64_t n_locs = 0, n_locs_best = 0;
+    bool have_locs = false, locs_filtered = false, n_locs_known = false;
 
     // alignment results
     DevBuf d_aln, d_cigar_fixed, d_cigar_cnt, d_cigar_off, d_cigar, d_aln_scratch;
@@ -102,8 +103,8 @@ struct KScope {
         if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
         cudaEvent_t e; cudaEventCreate(&e); return e;
     }
-    KScope(bm_ctx* c_, int kid_) : c(c_), kid(kid_) {
-        c->kstat[kid].launches++;
+    KScope(bm_ctx* c_, int kid_, int own_kernels = 1) : c(c_), kid(kid_) {
+        c->kstat[kid].launches += own_kernels;   // hand-written kernels launched inside the scope (library kernels not counted)
         if (c->ktiming) { a = get(c); b = get(c); cudaEventRecord(a, c->stream); }
     }
     ~KScope() {
@@ -140,6 +141,52 @@ __device__ __forceinline__ uint32_t bm_revcomp_hash(uint32_t h, uint32_t k) {
 // base i of the 2-bit packed genome
 __device__ __forceinline__ uint32_t bm_gbase(const uint8_t* __restrict__ p, uint64_t i) {
     return (p[i >> 2] >> ((i & 3) << 1)) & 3u;
+}
+
+// shared by K2a and K3a: stage one segment in shared memory and evaluate its k-mers
+struct SegStage {
+    uint8_t* base;    // 2-bit ranks, one per byte
+    uint8_t* qual;    // phred ranks (char - 33)
+    uint32_t* mask;   // one ballot word per chunk of 32 k-mer positions
+};
+
+__device__ __forceinline__ uint32_t kmer_hash_at(const uint8_t* sb, uint32_t j, uint32_t k) {
+    uint32_t h = 0;   // seqan3 views::kmer_hash(ungapped{k}): first base most significant
+    for (uint32_t t = 0; t < k; t++) h = (h << 2) | sb[j + t];
+    return h;
+}
+__device__ __forceinline__ uint32_t kmer_qual_at(const uint8_t* sq, uint32_t j, uint32_t k) {
+    uint32_t s = 0;   // views::kmer_quality (quality_filter.h:531-534): window sum of phred ranks
+    for (uint32_t t = 0; t < k; t++) s += sq[j + t];
+    return s;
+}
+
+// utils.h:160-178 with upper_bound = G-1 (see bm_api.cu sample_det for the ub==0 convention)
+__device__ __forceinline__ uint32_t sample_index(uint32_t i, uint32_t n, uint32_t G) {
+    if (G <= 1) return 0;
+    if (i + 1 == n) return G - 1;
+    double delta = __ddiv_rn((double)G, (double)(n - 1));
+    return (uint32_t)floor(__dmul_rn((double)(int)i, delta));
+}
+
+// position of the x-th (0-based) set bit over the chunk masks
+__device__ __forceinline__ uint32_t select_good(const uint32_t* mask, uint32_t nchunk, uint32_t x) {
+    uint32_t c = 0;
+    for (; c + 1 < nchunk; c++) {
+        uint32_t n = __popc(mask[c]);
+        if (x < n) break;
+        x -= n;
+    }
+    return c * 32 + __fns(mask[c], 0, (int)x + 1);
+}
+
+__device__ __forceinline__ void stage_segment(const SegStage& st, const uint8_t* __restrict__ seq,
+                                              const uint8_t* __restrict__ qual, uint64_t off, uint32_t n, uint32_t lane) {
+    for (uint32_t i = lane; i < n; i += 32) {
+        st.base[i] = (uint8_t)bm_rank_dna4(seq[off + i]);
+        st.qual[i] = (uint8_t)(qual[off + i] - 33);
+    }
+    __syncwarp();
 }
 
 __device__ __forceinline__ uint4 bm_ldg_stream(const uint4* p) {

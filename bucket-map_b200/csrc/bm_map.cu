@@ -20,53 +20,6 @@ namespace {
 
 constexpr int kWarpsPerCta = 4;
 
-// ---------------------------------------------------------------------------------------------------------------------
-// shared by K2a and K3a: stage one segment in shared memory and evaluate its k-mers
-struct SegStage {
-    uint8_t* base;    // 2-bit ranks, one per byte
-    uint8_t* qual;    // phred ranks (char - 33)
-    uint32_t* mask;   // one ballot word per chunk of 32 k-mer positions
-};
-
-__device__ __forceinline__ uint32_t kmer_hash_at(const uint8_t* sb, uint32_t j, uint32_t k) {
-    uint32_t h = 0;   // seqan3 views::kmer_hash(ungapped{k}): first base most significant
-    for (uint32_t t = 0; t < k; t++) h = (h << 2) | sb[j + t];
-    return h;
-}
-__device__ __forceinline__ uint32_t kmer_qual_at(const uint8_t* sq, uint32_t j, uint32_t k) {
-    uint32_t s = 0;   // views::kmer_quality (quality_filter.h:531-534): window sum of phred ranks
-    for (uint32_t t = 0; t < k; t++) s += sq[j + t];
-    return s;
-}
-
-// utils.h:160-178 with upper_bound = G-1 (see bm_api.cu sample_det for the ub==0 convention)
-__device__ __forceinline__ uint32_t sample_index(uint32_t i, uint32_t n, uint32_t G) {
-    if (G <= 1) return 0;
-    if (i + 1 == n) return G - 1;
-    double delta = __ddiv_rn((double)G, (double)(n - 1));
-    return (uint32_t)floor(__dmul_rn((double)(int)i, delta));
-}
-
-// position of the x-th (0-based) set bit over the chunk masks
-__device__ __forceinline__ uint32_t select_good(const uint32_t* mask, uint32_t nchunk, uint32_t x) {
-    uint32_t c = 0;
-    for (; c + 1 < nchunk; c++) {
-        uint32_t n = __popc(mask[c]);
-        if (x < n) break;
-        x -= n;
-    }
-    return c * 32 + __fns(mask[c], 0, (int)x + 1);
-}
-
-__device__ __forceinline__ void stage_segment(const SegStage& st, const uint8_t* __restrict__ seq,
-                                              const uint8_t* __restrict__ qual, uint64_t off, uint32_t n, uint32_t lane) {
-    for (uint32_t i = lane; i < n; i += 32) {
-        st.base[i] = (uint8_t)bm_rank_dna4(seq[off + i]);
-        st.qual[i] = (uint8_t)(qual[off + i] - 33);
-    }
-    __syncwarp();
-}
-
 // ---- K2a: good k-mers -> S samples -> row ids of both strands ------------------------------------------------------------
 // q_gram_mapper.h:431-469.  rowidx[((2*seg+strand)*S + s)*NQ + i] = kmer_to_index[(h_s >> 2i) & Q]  (or -1)
 __global__ void __launch_bounds__(kWarpsPerCta * 32)

@@ -65,10 +65,13 @@ def bucketize(rec_len, L, r):
     return NB, np.array(b_start, np.uint64), np.array(b_len, np.uint32), np.array(b_rec, np.uint32)
 
 
-def simulate_reads(packed, n_bases, n_reads, read_len, sub_rate, ins_rate, del_rate, seed, chunk=65536):
+def simulate_reads(packed, n_bases, n_reads, read_len, sub_rate, ins_rate, del_rate, seed, chunk=65536, hot=None):
     """returns (seq ASCII uint8, qual ASCII uint8, read_off uint64[n+1], truth_start int64[n], truth_rev bool[n])"""
     rng = np.random.default_rng(seed)
     starts = rng.integers(0, n_bases - read_len - 1, n_reads, dtype=np.int64)
+    if hot is not None:   # every 8th read starts inside [hot[0], hot[1])
+        sel = np.arange(0, n_reads, 8)
+        starts[sel] = rng.integers(max(0, hot[0]), min(hot[1], n_bases - read_len - 1), len(sel), dtype=np.int64)
     n_del = rng.poisson(del_rate * read_len, n_reads)
     n_ins = rng.poisson(ins_rate * read_len, n_reads)
     n_sub = rng.poisson(sub_rate * read_len, n_reads)

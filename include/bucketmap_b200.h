@@ -107,8 +107,14 @@ int bm_index_load(bm_ctx* ctx, const int32_t* kmer_to_index, uint32_t q, const u
 int bm_index_download(bm_ctx* ctx, uint8_t* out_rows);
 /* distinguishability_filter::read (q_gram_mapper.h:171-187): zeros[] per row; *valid = the logged counter */
 int bm_index_zeros(bm_ctx* ctx, float distinguishability, uint32_t* zeros_out /* n_rows or NULL */, uint32_t* valid);
-/* mapper::reset (q_gram_mapper.h) */
+/* mapper::reset (q_gram_mapper.h:374-378) */
 int bm_index_free(bm_ctx* ctx);
+/* multi-GPU replication (no reference counterpart: the reference is one process).  bm_index_alloc sizes an empty
+ * resident matrix for the given table; bm_index_device / bm_ref_device expose the device buffers (padded rows:
+ * n_rows * Wp bytes, Wp = roundup(W,64); packed genome) so the caller can ncclBroadcast into / out of them. */
+int bm_index_alloc(bm_ctx* ctx, const int32_t* kmer_to_index, uint32_t q, uint32_t n_rows, uint32_t NB);
+int bm_index_device(bm_ctx* ctx, void** dptr, uint64_t* bytes);
+int bm_ref_device(bm_ctx* ctx, void** dptr, uint64_t* bytes);
 
 /* ---- reads ---------------------------------------------------------------------------------------------------- */
 /* H2D of one read batch + segment table (q_gram_mapper.h:509-523 / bucket_locator.h:302-313). */
@@ -132,6 +138,11 @@ int bm_map_reads(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint
 int bm_locate_device(bm_ctx* ctx, const bm_params* p, int filter_best);
 /* loc_off: n_reads+1; locs: capacity loc_cap (cand_off[2*n_seg] always suffices) */
 int bm_locate_download(bm_ctx* ctx, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap);
+/* number of locations the last bm_locate_device produced */
+int bm_locate_count(bm_ctx* ctx, uint64_t* n_locs);
+/* device-resident results (loc_off: n_reads+1 uint32; locs: n_locs bm_loc) for a device-side gather over NCCL;
+ * valid until the next bm_locate_device / bm_reads_upload on this context */
+int bm_locate_device_buffers(bm_ctx* ctx, void** loc_off, void** locs, uint64_t* n_locs);
 /* host-buffer form of the whole alignment-free path: reads in, merged best locations out */
 int bm_map_locate(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
                   const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs,

@@ -464,19 +464,33 @@ void orc_sample(uint32_t n, uint32_t ub, uint32_t* out) {
     std::copy(v.begin(), v.end(), out);
 }
 
-void orc_map_segments(const orc_params* p, uint32_t NB, const int32_t* k2i, const uint8_t* rows, uint32_t n_rows,
-                      const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off, const uint32_t* seg_read,
-                      const uint32_t* seg_start, const uint32_t* seg_len, uint32_t n_seg, uint32_t* cand_off,
-                      uint32_t* cand, uint64_t* stats, uint32_t threads) {
-    Matrix M; M.load(rows, n_rows, NB);
-    std::vector<uint32_t> zeros(n_rows);
-    orc_zeros(rows, n_rows, NB, p->distinguishability, zeros.data());
-    const uint32_t thr = dist_threshold(p->distinguishability, NB);
+struct orc_index {                 /* what q_gram_mapper::load leaves in memory (q_gram_mapper.h:318-372) */
+    Matrix M;
+    std::vector<uint32_t> zeros;
+    std::vector<int32_t> k2i;
+    uint32_t thr = 0;
+};
+
+orc_index* orc_index_open(const orc_params* p, uint32_t NB, const int32_t* k2i, const uint8_t* rows, uint32_t n_rows) {
+    orc_index* ix = new orc_index();
+    ix->M.load(rows, n_rows, NB);
+    ix->zeros.resize(n_rows);
+    orc_zeros(rows, n_rows, NB, p->distinguishability, ix->zeros.data());
+    ix->thr = dist_threshold(p->distinguishability, NB);
+    ix->k2i.assign(k2i, k2i + (1ull << (2 * p->q)));
+    return ix;
+}
+void orc_index_close(orc_index* ix) { delete ix; }
+
+void orc_map_segments_h(const orc_index* ix, const orc_params* p, const uint8_t* seq, const uint8_t* qual,
+                        const uint64_t* read_off, const uint32_t* seg_read, const uint32_t* seg_start,
+                        const uint32_t* seg_len, uint32_t n_seg, uint32_t* cand_off, uint32_t* cand, uint64_t* stats,
+                        uint32_t threads) {
     std::vector<std::vector<uint32_t>> lists((size_t)2 * n_seg);
     if (threads == 0) threads = 1;
     std::vector<uint64_t> anded(threads, 0);
     parallel_for(n_seg, threads, [&](uint64_t lo, uint64_t hi, uint32_t t) {
-        MapperState st(p, &M, k2i, zeros.data(), thr);
+        MapperState st(p, &ix->M, ix->k2i.data(), ix->zeros.data(), ix->thr);
         for (uint64_t s = lo; s < hi; s++) {
             uint64_t o = read_off[seg_read[s]] + seg_start[s];
             SegView v{seq + o, qual + o, seg_len[s]};
@@ -495,6 +509,15 @@ void orc_map_segments(const orc_params* p, uint32_t NB, const int32_t* k2i, cons
     cand_off[2 * n_seg] = pos;
     for (uint64_t a : anded) tot += a;
     if (stats) { stats[0] = mapped; stats[1] = so; stats[2] = sr; stats[3] = tot; }
+}
+
+void orc_map_segments(const orc_params* p, uint32_t NB, const int32_t* k2i, const uint8_t* rows, uint32_t n_rows,
+                      const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off, const uint32_t* seg_read,
+                      const uint32_t* seg_start, const uint32_t* seg_len, uint32_t n_seg, uint32_t* cand_off,
+                      uint32_t* cand, uint64_t* stats, uint32_t threads) {
+    orc_index* ix = orc_index_open(p, NB, k2i, rows, n_rows);
+    orc_map_segments_h(ix, p, seq, qual, read_off, seg_read, seg_start, seg_len, n_seg, cand_off, cand, stats, threads);
+    orc_index_close(ix);
 }
 
 void orc_prepare_query(const orc_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,

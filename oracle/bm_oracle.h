@@ -92,6 +92,17 @@ void orc_map_segments(const orc_params* p, uint32_t NB, const int32_t* kmer_to_i
                       const uint32_t* seg_read, const uint32_t* seg_start, const uint32_t* seg_len, uint32_t n_seg,
                       uint32_t* cand_off, uint32_t* cand, uint64_t* stats, uint32_t threads);
 
+/* the same with the loaded index kept between calls (what q_gram_mapper::load leaves in memory), so a timed
+ * mapping pass does not include the index load */
+typedef struct orc_index orc_index;
+orc_index* orc_index_open(const orc_params* p, uint32_t NB, const int32_t* kmer_to_index, const uint8_t* rows,
+                          uint32_t n_rows);
+void orc_index_close(orc_index* ix);
+void orc_map_segments_h(const orc_index* ix, const orc_params* p, const uint8_t* seq, const uint8_t* qual,
+                        const uint64_t* read_off, const uint32_t* seg_read, const uint32_t* seg_start,
+                        const uint32_t* seg_len, uint32_t n_seg, uint32_t* cand_off, uint32_t* cand, uint64_t* stats,
+                        uint32_t threads);
+
 /* locator/bucket_locator.h:292-347: P (index,hash) pairs per segment */
 void orc_prepare_query(const orc_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
                        const uint32_t* seg_read, const uint32_t* seg_start, const uint32_t* seg_len, uint32_t n_seg,

@@ -65,6 +65,13 @@ class Oracle:
         L.orc_map_segments.restype = None
         L.orc_map_segments.argtypes = [C.POINTER(Params), C.c_uint32, _vp, _vp, C.c_uint32, _vp, _vp, _vp, _vp, _vp,
                                        _vp, C.c_uint32, _vp, _vp, _vp, C.c_uint32]
+        L.orc_index_open.restype = _vp
+        L.orc_index_open.argtypes = [C.POINTER(Params), C.c_uint32, _vp, _vp, C.c_uint32]
+        L.orc_index_close.restype = None
+        L.orc_index_close.argtypes = [_vp]
+        L.orc_map_segments_h.restype = None
+        L.orc_map_segments_h.argtypes = [_vp, C.POINTER(Params), _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint32, _vp, _vp,
+                                         _vp, C.c_uint32]
         L.orc_prepare_query.restype = None
         L.orc_prepare_query.argtypes = [C.POINTER(Params), _vp, _vp, _vp, _vp, _vp, _vp, C.c_uint32, _vp, _vp]
         L.orc_locate.restype = None
@@ -138,6 +145,22 @@ class Oracle:
         self.lib.orc_map_segments(C.byref(P), NB, _p(k2i), _p(rows), rows.shape[0], _p(seq), _p(qual), _p(read_off),
                                   _p(sr), _p(ss), _p(sl), n_seg, _p(off), _p(cand), _p(stats),
                                   threads or self.threads)
+        return off, cand[:int(off[-1])].copy(), stats
+
+    def index_open(self, P, NB, k2i, rows):
+        return self.lib.orc_index_open(C.byref(P), NB, _p(k2i), _p(rows), rows.shape[0])
+
+    def index_close(self, ix):
+        self.lib.orc_index_close(ix)
+
+    def map_segments_h(self, ix, P, seq, qual, read_off, segs, threads=None):
+        sr, ss, sl = segs
+        n_seg = len(sr)
+        off = np.empty(2 * n_seg + 1, np.uint32)
+        cand = np.empty(2 * n_seg * P.max_candidates + 1, np.uint32)
+        stats = np.zeros(4, np.uint64)
+        self.lib.orc_map_segments_h(ix, C.byref(P), _p(seq), _p(qual), _p(read_off), _p(sr), _p(ss), _p(sl), n_seg,
+                                    _p(off), _p(cand), _p(stats), threads or self.threads)
         return off, cand[:int(off[-1])].copy(), stats
 
     def prepare_query(self, P, seq, qual, read_off, segs):

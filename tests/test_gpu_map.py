@@ -29,6 +29,7 @@ def test_index_build_matches_oracle(oracle, bm, ctx, kw):
 def test_index_load_roundtrip(oracle, bm, ctx):
     d = dataset()
     k2i, n_rows, rows = _index(oracle, d)
+    ctx.ref_upload(d.packed, d.n_bases, d.b_start, d.b_len, d.NB)
     ctx.index_load(k2i, d.q, rows, d.NB)
     assert np.array_equal(ctx.index_download(), rows)
 
