@@ -61,7 +61,7 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.sm, self.reasons, self.sm_max = [], set(), None
-        self._stop = threading.Event()
+        self._halt = threading.Event()
         self.ok = False
         try:
             import pynvml
@@ -83,7 +83,7 @@ class ClockSampler(threading.Thread):
             getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
             getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
         }
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
@@ -92,10 +92,10 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(self.period)
+            self._halt.wait(self.period)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         if self.is_alive():
             self.join()
         return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
@@ -126,14 +126,16 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(workload_key):
-    """per-launch DRAM bytes of k_map_vote from the committed ncu --set full capture, if it was taken on this workload"""
+def ncu_traffic(config_name, n_reads):
+    """per-launch DRAM bytes (read+write) of k_map_vote from the committed ncu --set full capture of this workload,
+    scaled from the captured launch size to this launch's reads (traffic is linear in reads: no reuse across reads)"""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
             d = json.load(open(p))
-            if d.get("workload") == workload_key:
-                return d.get("dram_bytes_per_launch")
+            if d.get("workload") == config_name:
+                per = (d["dram_bytes_read_per_launch"] + d["dram_bytes_write_per_launch"]) / d["captured_reads_per_launch"]
+                return per * n_reads
         except Exception:
             pass
     return None
@@ -286,7 +288,7 @@ def main():
     alg_bytes = rows_gathered * W
     peak, peak_src = measured_peak()
     achieved = alg_bytes / (vote_ms / vote_n * 1e-3) / 1e9 if vote_n else None
-    traffic = ncu_traffic(f"{a.config}/{a.reads}")
+    traffic = ncu_traffic(a.config, n_reads)
     launches = int(sum(v[1] for v in kst.values()))
     out = {
         "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
