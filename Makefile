@@ -4,7 +4,9 @@
 #   make oracle   -> oracle/libbm_oracle.so                 (test infrastructure only)
 #   make ref      -> oracle/_ref/...                        (reference headers built against oracle/shim; needs /root/reference)
 NVCC      ?= nvcc
-CXX       ?= g++
+# the environment may point CXX at a wrapper whose libstdc++.so link is dangling (static libstdc++ in a .so crashes
+# inside a Python process that already holds the shared one): always use the g++ on PATH
+CXX       := g++
 PKG       := bucket-map_b200
 CSRC      := $(PKG)/csrc
 BUILD     := build
