@@ -1,0 +1,83 @@
+"""CPU, world_size 2 over gloo: the host-side multi-GPU plumbing (read sharding, variable-length gather of location
+records to rank 0 in global read order).  The index broadcast aliases device memory and is covered on the GPU box."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import bucketmap_b200 as bm
+from bucketmap_b200 import dist as bmd
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _fake_results(n_reads_total, rank, world, seed=5):
+    """deterministic per-read location lists; rank r owns the contiguous shard shard_bounds(n, r, world)"""
+    rng = np.random.default_rng(seed)
+    counts = rng.integers(0, 4, n_reads_total)
+    locs = np.zeros(int(counts.sum()), bm.LOC_DTYPE)
+    locs["bucket"] = rng.integers(0, 1000, len(locs))
+    locs["offset"] = rng.integers(-5, 65000, len(locs))
+    locs["votes"] = rng.integers(6, 12, len(locs))
+    locs["is_original"] = rng.integers(0, 2, len(locs))
+    off = np.concatenate([[0], np.cumsum(counts)])
+    lo, hi = bmd.shard_bounds(n_reads_total, rank, world)
+    return counts, locs, off, lo, hi
+
+
+def _worker(rank, world, port, n_reads, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    counts, locs, off, lo, hi = _fake_results(n_reads, rank, world)
+    my_counts = torch.from_numpy(counts[lo:hi].astype(np.int32))
+    my_locs = locs[off[lo]:off[hi]]
+    my_bytes = torch.from_numpy(my_locs.view(np.uint8).reshape(-1, bm.LOC_DTYPE.itemsize).copy())
+    res = bmd.gather_locations(my_counts, my_bytes, dst=0)
+    if rank == 0:
+        g_off, g_locs = res
+        np.save(os.path.join(out_dir, "off.npy"), g_off)
+        np.save(os.path.join(out_dir, "locs.npy"), g_locs)
+    else:
+        assert res is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_shard_bounds_cover_all_reads():
+    for n in (0, 1, 7, 1000, 1_000_003):
+        for world in (1, 2, 4, 8):
+            b = [bmd.shard_bounds(n, r, world) for r in range(world)]
+            assert b[0][0] == 0 and b[-1][1] == n
+            assert all(b[i][1] == b[i + 1][0] for i in range(world - 1))
+            sizes = [hi - lo for lo, hi in b]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_gather_locations_world2(tmp_path):
+    n_reads, world = 1001, 2
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, n_reads, str(tmp_path)), nprocs=world, join=True)
+    counts, locs, off, _, _ = _fake_results(n_reads, 0, world)
+    g_off = np.load(tmp_path / "off.npy")
+    g_locs = np.load(tmp_path / "locs.npy")
+    assert np.array_equal(g_off, off.astype(np.uint32))
+    assert np.array_equal(g_locs, locs)
+
+
+def test_gather_locations_with_an_empty_rank(tmp_path):
+    # 1 read over 2 ranks: rank 0's shard is empty
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, 1, str(tmp_path)), nprocs=2, join=True)
+    counts, locs, off, _, _ = _fake_results(1, 0, 2)
+    assert np.array_equal(np.load(tmp_path / "off.npy"), off.astype(np.uint32))
+    assert np.array_equal(np.load(tmp_path / "locs.npy"), locs)
