@@ -284,8 +284,9 @@ def main():
 
     # ---- roofline of the dominant kernel -------------------------------------------------------------------------------
     vote_ms, vote_n = kst["map_vote"]
-    rows_gathered = int(mstats[3])
-    alg_bytes = rows_gathered * W
+    rows_gathered = int(mstats[3])          # rows the reference's cascade ANDs (R of SURVEY 8d)
+    alg_bytes = int(mstats[4])              # bytes of those rows K2's algorithm needs: 16-B loads it issued, counted
+                                            # in the kernel (tiles whose buckets all reached F misses stop early)
     peak, peak_src = measured_peak()
     achieved = alg_bytes / (vote_ms / vote_n * 1e-3) / 1e9 if vote_n else None
     traffic = ncu_traffic(a.config, n_reads)
@@ -308,7 +309,11 @@ def main():
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                      "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes,
                      "ms_per_launch": vote_ms / vote_n if vote_n else None,
-                     "rows_gathered_per_read": rows_gathered / max(1, n_reads)},
+                     "rows_gathered_per_read": rows_gathered / max(1, n_reads),
+                     "reference_cascade_bytes_per_launch": rows_gathered * W,
+                     "alg_bytes_definition": "16-B row loads issued by k_map_vote (counted in-kernel): the q-gram rows of "
+                                             "every 512-B column tile until all 4096 buckets of the tile have missed F "
+                                             "samples; reference_cascade_bytes = all S*(k-q+1) rows of both strands x W"},
         "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
         "index_build_ms": index_ms, "index_bcast_ms": bcast_ms, "setup_s": setup_s,
         "mapped": {"reads_with_candidate": int(mstats[0]), "cand_fwd": int(mstats[1]), "cand_rev": int(mstats[2])},

@@ -205,7 +205,7 @@ class Context:
 
     def map_download(self, max_candidates=30):
         off = np.empty(2 * self.n_seg + 1, np.uint32)
-        stats = np.zeros(4, np.uint64)
+        stats = np.zeros(8, np.uint64)
         self._ck(self.lib.bm_map_download(self.h, _ptr(off), None, 0, _ptr(stats)), "bm_map_download")
         cand = np.empty(int(off[-1]), np.uint32)
         self._ck(self.lib.bm_map_download(self.h, None, _ptr(cand), len(cand), None), "bm_map_download")
@@ -217,7 +217,7 @@ class Context:
         nseg_max = n * max(1, P.num_segment_samples)
         off = np.empty(2 * nseg_max + 1, np.uint32)
         cand = np.empty(2 * nseg_max * P.max_candidates + 1, np.uint32)
-        stats = np.zeros(4, np.uint64)
+        stats = np.zeros(8, np.uint64)
         self._ck(self.lib.bm_map_reads(self.h, C.byref(P), _ptr(seq), _ptr(qual), _ptr(read_off), n, _ptr(off),
                                        _ptr(cand), len(cand), _ptr(stats)), "bm_map_reads")
         self.n_reads = n
@@ -257,7 +257,7 @@ class Context:
         cap = 2 * nseg_max * P.max_candidates + 1
         off = np.empty(n + 1, np.uint32)
         locs = np.empty(cap, LOC_DTYPE)
-        stats = np.zeros(4, np.uint64)
+        stats = np.zeros(8, np.uint64)
         self._ck(self.lib.bm_map_locate(self.h, C.byref(P), _ptr(seq), _ptr(qual), _ptr(read_off), n,
                                         int(filter_best), _ptr(off), _ptr(locs), cap, _ptr(stats)), "bm_map_locate")
         self.n_reads = n

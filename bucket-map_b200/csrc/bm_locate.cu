@@ -668,7 +668,7 @@ int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8
     r = bm_locate_device(c, p, filter_best);
     if (r) return r;
     if (stats) {
-        BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 4 * 8, cudaMemcpyDeviceToHost, c->stream));
+        BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 8 * 8, cudaMemcpyDeviceToHost, c->stream));
     }
     return bm_locate_download(c, loc_off, locs, loc_cap);
 }

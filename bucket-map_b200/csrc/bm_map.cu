@@ -106,13 +106,60 @@ __device__ __forceinline__ uint4 valid_bits(uint32_t col, uint32_t NB) {
     return make_uint4(w[0], w[1], w[2], w[3]);
 }
 
+// one group of BB samples: BB*NQ independent 128-bit loads per lane, then the bit-sliced miss counters are advanced
+template <int NQ, int NP, int BB>
+__device__ __forceinline__ uint32_t vote_group(const uint4* __restrict__ colp, uint32_t Wp16, const int32_t* idx, bool load_ok,
+                                               uint4 (&p)[NP]) {
+    const uint4 ONES = make_uint4(~0u, ~0u, ~0u, ~0u);
+    uint4 v[BB][NQ];
+    uint32_t nloads = 0;
+#pragma unroll
+    for (int b = 0; b < BB; b++)
+#pragma unroll
+        for (int i = 0; i < NQ; i++) {
+            const int32_t r = idx[b * NQ + i];
+            v[b][i] = ONES;                               // un-sampled q-gram: skipped in the AND (:404-405)
+            if (r >= 0 && load_ok) { v[b][i] = bm_ldg_stream(colp + (size_t)r * Wp16); nloads++; }
+        }
+#pragma unroll
+    for (int b = 0; b < BB; b++) {
+        uint4 bf = v[b][0];
+#pragma unroll
+        for (int i = 1; i < NQ; i++) bf = and4(bf, v[b][i]);
+        uint4 carry = not4(bf);                           // 1 = this sample misses the bucket
+#pragma unroll
+        for (int i = 0; i < NP; i++) { uint4 t = and4(p[i], carry); p[i] = xor4(p[i], carry); carry = t; }
+#pragma unroll
+        for (int i = 0; i < NP; i++) p[i] = or4(p[i], carry);   // saturate at 2^NP-1 (>= F by dispatch)
+    }
+    return nloads;
+}
+
+// buckets of this lane's column whose miss count is still < F
+template <int NP>
+__device__ __forceinline__ uint4 below_f(const uint4 (&p)[NP], uint32_t F) {
+    uint4 lt = make_uint4(0, 0, 0, 0), eq = make_uint4(~0u, ~0u, ~0u, ~0u);
+#pragma unroll
+    for (int i = NP - 1; i >= 0; i--) {
+        if ((F >> i) & 1u) { lt = or4(lt, andn4(eq, p[i])); eq = and4(eq, p[i]); }
+        else eq = andn4(eq, p[i]);
+    }
+    return lt;
+}
+
+// Dead-tile early exit.  A bucket that has missed F samples can never be reported (best_results() only looks at the F
+// cascade levels, q_gram_mapper.h:90-102) and miss counts only grow, so once every bucket of a 4096-bucket tile has
+// reached F misses the remaining samples' rows need not be gathered for that tile; inside a live tile, lanes whose 128
+// buckets are all dead stop loading too.  On a random genome a 12-mer hits a foreign bucket with probability ~0.2 %, so
+// almost every tile dies after F+1 or F+2 of the S samples: the kernel moves about half of the S*(k-q+1)*W bytes per
+// list that the reference's cascade touches, with identical results.
 template <int NQ, int NP>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ rowidx,
            const uint8_t* __restrict__ segok, uint32_t n_lists, uint32_t S, uint32_t F, uint32_t max_cand,
-           uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt) {
-    constexpr int B = (NQ >= 8) ? 1 : (8 / NQ);           // samples in flight per lane: B*NQ 128-bit loads
-    extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * Spad*NQ row ids
+           uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt, unsigned long long* __restrict__ stats) {
+    constexpr int B = (NQ >= 8) ? 1 : (8 / NQ);           // samples in flight per lane while no tile can be dead yet
+    extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * S*NQ row ids
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t list = blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand
     if (list >= n_lists) return;
@@ -120,16 +167,15 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
         if (lane == 0) cand_cnt[list] = 0;
         return;
     }
-    const uint32_t Spad = (S + B - 1) / B * B;
-    int32_t* my_idx = s_idx + (size_t)warp * Spad * NQ;
-    for (uint32_t t = lane; t < Spad * NQ; t += 32)
-        my_idx[t] = (t < S * NQ) ? rowidx[(size_t)list * S * NQ + t] : -2;   // -2: padding sample, contributes nothing
+    int32_t* my_idx = s_idx + (size_t)warp * S * NQ;
+    for (uint32_t t = lane; t < S * NQ; t += 32) my_idx[t] = rowidx[(size_t)list * S * NQ + t];
     __syncwarp();
 
-    const uint4 ONES = make_uint4(~0u, ~0u, ~0u, ~0u), ZERO = make_uint4(0, 0, 0, 0);
-    uint32_t best = 0xFFFFFFFFu, count = 0;
+    const uint4 ZERO = make_uint4(0, 0, 0, 0);
+    uint32_t best = 0xFFFFFFFFu, count = 0, nloads = 0;
     uint32_t* out = cand_fixed + (size_t)list * max_cand;
     const uint32_t ntile = (Wp16 + 31) / 32;
+    const uint32_t s_blind = (min(S, F) / B) * B;         // fewer than F samples seen: nothing can be dead
     for (uint32_t tile = 0; tile < ntile; tile++) {
         const uint32_t col = tile * 32 + lane;
         const bool active = col < Wp16;
@@ -137,36 +183,20 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
         uint4 p[NP];
 #pragma unroll
         for (int i = 0; i < NP; i++) p[i] = ZERO;
-        for (uint32_t s = 0; s < Spad; s += B) {
-            uint4 v[B][NQ];
-#pragma unroll
-            for (int b = 0; b < B; b++)
-#pragma unroll
-                for (int i = 0; i < NQ; i++) {
-                    int32_t idx = my_idx[(s + b) * NQ + i];
-                    v[b][i] = ONES;                       // un-sampled q-gram: skipped in the AND (:404-405)
-                    if (idx >= 0 && active) v[b][i] = bm_ldg_stream(colp + (size_t)idx * Wp16);
-                }
-#pragma unroll
-            for (int b = 0; b < B; b++) {
-                uint4 bf = v[b][0];
-#pragma unroll
-                for (int i = 1; i < NQ; i++) bf = and4(bf, v[b][i]);
-                uint4 carry = not4(bf);                   // 1 = this sample misses the bucket
-                if (my_idx[(s + b) * NQ] == -2) carry = ZERO;
-#pragma unroll
-                for (int i = 0; i < NP; i++) { uint4 t = and4(p[i], carry); p[i] = xor4(p[i], carry); carry = t; }
-#pragma unroll
-                for (int i = 0; i < NP; i++) p[i] = or4(p[i], carry);   // saturate at 2^NP-1 (>= F by dispatch)
+        uint32_t s = 0;
+        for (; s < s_blind; s += B) nloads += vote_group<NQ, NP, B>(colp, Wp16, my_idx + s * NQ, active, p);
+        bool tile_alive = true;
+        for (; s < S; s++) {
+            bool lane_alive = active;
+            if (s >= F) {
+                lane_alive = active && any4(below_f<NP>(p, F));
+                if (!__any_sync(0xFFFFFFFFu, lane_alive)) { tile_alive = false; break; }
             }
+            nloads += vote_group<NQ, NP, 1>(colp, Wp16, my_idx + s * NQ, lane_alive, p);
         }
+        if (!tile_alive) continue;
         // buckets with miss count < F
-        uint4 lt = ZERO, eq = ONES;
-#pragma unroll
-        for (int i = NP - 1; i >= 0; i--) {
-            if ((F >> i) & 1u) { lt = or4(lt, andn4(eq, p[i])); eq = and4(eq, p[i]); }
-            else eq = andn4(eq, p[i]);
-        }
+        const uint4 lt = below_f<NP>(p, F);
         uint4 alive = active ? and4(lt, valid_bits(col, NB)) : ZERO;
         if (!__any_sync(0xFFFFFFFFu, any4(alive))) continue;
         // minimum miss count inside this lane's 128 buckets, and the buckets attaining it
@@ -205,6 +235,8 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
     }
     // :471-476: a list longer than the cap is emptied, not truncated
     if (lane == 0) cand_cnt[list] = (best < F && count <= max_cand) ? count : 0u;
+    nloads = __reduce_add_sync(0xFFFFFFFFu, nloads);
+    if (lane == 0) atomicAdd(stats + 4, (unsigned long long)nloads * 16ull);   // bytes actually gathered
 }
 
 // ---- compaction of the fixed-slot lists into cand_off / cand ---------------------------------------------------------------
@@ -230,7 +262,7 @@ cudaError_t launch_vote_np(bm_ctx* c, const bm_params* p, uint32_t NP, uint32_t 
     k_map_vote<NQ, NPv><<<blocks, kWarpsPerCta * 32, smem, c->stream>>>(                                           \
         c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), n_lists,    \
         p->mapper_samples, p->mapper_fault, p->max_candidates, c->d_cand_fixed.as<uint32_t>(),                     \
-        c->d_cand_cnt.as<uint32_t>())
+        c->d_cand_cnt.as<uint32_t>(), c->d_stats.as<unsigned long long>())
     if (NP == 3) BM_VOTE(3); else if (NP == 4) BM_VOTE(4); else BM_VOTE(6);
 #undef BM_VOTE
     return cudaGetLastError();
@@ -265,7 +297,7 @@ int bm_map_device(bm_ctx* c, const bm_params* p) {
     BM_CK(c, c->d_cand_cnt.ensure((size_t)(n_lists + 1) * 4));
     BM_CK(c, c->d_cand_off.ensure((size_t)(n_lists + 1) * 4));
     BM_CK(c, c->d_stats.ensure(128 * 8));
-    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 4 * 8, c->stream));
+    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * 8, c->stream));
     c->map_max_cand = p->max_candidates;
     c->n_cand = 0;
     if (n_seg) {
@@ -287,9 +319,7 @@ int bm_map_device(bm_ctx* c, const bm_params* p) {
         }
         BM_CK(c, cudaGetLastError());
         const uint32_t NP = (F <= 7) ? 3 : (F <= 15 ? 4 : 6);
-        const uint32_t Bs = (NQ >= 8) ? 1 : (8 / NQ);
-        const uint32_t Spad = (S + Bs - 1) / Bs * Bs;
-        size_t smem_v = (size_t)kWarpsPerCta * Spad * NQ * 4;
+        size_t smem_v = (size_t)kWarpsPerCta * S * NQ * 4;
         const uint32_t blocks_v = (n_lists + kWarpsPerCta - 1) / kWarpsPerCta;
         cudaError_t e = cudaSuccess;
         {
@@ -340,7 +370,7 @@ int bm_map_download(bm_ctx* c, uint32_t* cand_off, uint32_t* cand, uint64_t cand
         if (cand_cap < c->n_cand) BM_FAIL(c, BM_E_ARG, "bm_map_download: candidate buffer too small");
         BM_CK(c, cudaMemcpyAsync(cand, c->d_cand.p, (size_t)c->n_cand * 4, cudaMemcpyDeviceToHost, c->stream));
     }
-    if (stats) BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 4 * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (stats) BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 8 * 8, cudaMemcpyDeviceToHost, c->stream));
     BM_CK(c, cudaStreamSynchronize(c->stream));
     return BM_OK;
 }

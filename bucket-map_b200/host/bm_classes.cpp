@@ -240,7 +240,7 @@ std::pair<segments_t, segments_t> q_gram_mapper::map(fs::path const& sequence_fi
         const size_t nseg_max = (size_t)n * (num_segment_samples_ ? num_segment_samples_ : 1);
         cand_off.resize(2 * nseg_max + 1);
         cand.resize(2 * nseg_max * allowed_max_candidate_buckets + 1);
-        uint64_t stats[4] = {0, 0, 0, 0};
+        uint64_t stats[8] = {0};
         int rc = bm_map_reads(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n, cand_off.data(), cand.data(),
                               cand.size(), stats);                                          // K2a + K2
         if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n"; break; }

@@ -142,7 +142,7 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
     while (fin.next(b, batch_reads_, (uint64_t)1 << 31)) {
         const uint32_t n = b.size();
         const double t0 = now_s();
-        uint64_t stats[4] = {0, 0, 0, 0};
+        uint64_t stats[8] = {0};
         uint64_t n_locs = 0;
         loc_off.resize((size_t)n + 1);
         if (!align_) {

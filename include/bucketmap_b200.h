@@ -126,7 +126,9 @@ int bm_reads_segments(bm_ctx* ctx, uint32_t* n_seg, uint32_t* seg_read, uint32_t
 /* K2a+K2 on the resident batch; results stay on the device. */
 int bm_map_device(bm_ctx* ctx, const bm_params* p);
 /* cand_off: 2*n_seg+1 entries; cand: capacity cand_cap entries (2*max_candidates*n_seg always suffices).
- * stats[0]=segments with >=1 candidate, [1]=sum forward, [2]=sum reverse, [3]=rows gathered (R of the roofline). */
+ * stats: 8 entries. [0]=segments with >=1 candidate, [1]=sum forward, [2]=sum reverse, [3]=rows the reference's
+ * cascade ANDs for this batch (indexed q-grams of both strands: R of SURVEY 8d), [4]=bytes K2 actually gathered
+ * (less than [3]*Wp: tiles whose buckets have all reached F misses are not gathered further), [5..7]=0. */
 int bm_map_download(bm_ctx* ctx, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats);
 /* host-buffer form: upload + device + download (what q_gram_mapper::map does per FASTQ batch) */
 int bm_map_reads(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,

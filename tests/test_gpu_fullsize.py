@@ -126,7 +126,14 @@ def test_full_error_free_reads_land_on_their_origin_and_align_perfectly(full):
     np.logical_or.at(found, read_of[exact], True)
     assert found[cnt > 0].all()
     # an exact location verifies with edit distance 0, begin 0 and a single 300M op
-    assert (aln["score"][exact] == 0).all() and (aln["begin"][exact] == 0).all()
+    assert (aln["score"][exact] == 0).all()
+    # forward strand: the read starts at column 0 of its text window; reverse strand: the window (read length + 1 +
+    # (size_t)(0.02 * 300) = 307 columns, clipped at the bucket end) is reverse-complemented, so the read sits at its end
+    fwd = exact & (locs["is_original"] == 1)
+    rv = exact & (locs["is_original"] == 0)
+    assert (aln["begin"][fwd] == 0).all()
+    width = np.minimum(307, full.b_len[locs["bucket"][rv]].astype(np.int64) - locs["offset"][rv])
+    assert np.array_equal(aln["begin"][rv].astype(np.int64), width - 300)
     assert (aln["kept"][exact] == 1).all() and (aln["map_qual"][exact] == 60).all()
     assert (aln["cigar_len"][exact] == 1).all()
     assert (cig[aln["cigar_off"][exact]] == ((300 << 4) | 0)).all()

@@ -68,7 +68,7 @@ def test_locator_samples_match_oracle(oracle, bm, ctx):
     segs = oracle.segments(Po, d.read_off)
     coff, cand, stats = oracle.map_segments(Po, d.NB, k2i, rows, d.seq, qual, d.read_off, segs)
     goff, gcand, gstats = ctx.map_reads(P, d.seq, qual, d.read_off)
-    assert np.array_equal(goff, coff) and np.array_equal(gcand, cand) and np.array_equal(gstats, stats)
+    assert np.array_equal(goff, coff) and np.array_equal(gcand, cand) and np.array_equal(gstats[:4], stats)
     loff, locs = oracle.locate(Po, d.packed, d.b_start, d.b_len, d.seq, qual, d.read_off, segs, coff, cand)
     ctx.locate_device(P, False)
     g2, gl = ctx.locate_download()

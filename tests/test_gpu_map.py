@@ -59,5 +59,5 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk):
         assert np.array_equal(a, b)
     assert np.array_equal(goff, coff)
     assert np.array_equal(gcand, cand)
-    assert np.array_equal(gstats, stats)
+    assert np.array_equal(gstats[:4], stats)
     assert stats[0] > 0.9 * len(segs[0]) or kw.get("read_len") == 800
