@@ -152,7 +152,8 @@ __device__ __forceinline__ uint4 below_f(const uint4 (&p)[NP], uint32_t F) {
 // reached F misses the remaining samples' rows need not be gathered for that tile; inside a live tile, lanes whose 128
 // buckets are all dead stop loading too.  On a random genome a 12-mer hits a foreign bucket with probability ~0.2 %, so
 // almost every tile dies after F+1 or F+2 of the S samples: the kernel moves about half of the S*(k-q+1)*W bytes per
-// list that the reference's cascade touches, with identical results.
+// list that the reference's cascade touches, with identical results.  Only the buckets attaining the MINIMUM miss count
+// are reported, so once a finished tile holds a bucket with `best` misses the bar for later tiles drops to best+1.
 template <int NQ, int NP>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ rowidx,
@@ -175,11 +176,14 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
     uint32_t best = 0xFFFFFFFFu, count = 0, nloads = 0;
     uint32_t* out = cand_fixed + (size_t)list * max_cand;
     const uint32_t ntile = (Wp16 + 31) / 32;
-    const uint32_t s_blind = (min(S, F) / B) * B;         // fewer than F samples seen: nothing can be dead
     for (uint32_t tile = 0; tile < ntile; tile++) {
         const uint32_t col = tile * 32 + lane;
         const bool active = col < Wp16;
         const uint4* colp = rows + (active ? col : 0);
+        // a bucket is out of the race once it has missed T samples: T = F, or best+1 once an earlier tile holds a
+        // bucket that finished with `best` misses (only buckets attaining the minimum are reported)
+        const uint32_t T = (best < F) ? best + 1u : F;
+        const uint32_t s_blind = (min(S, T) / B) * B;     // fewer than T samples seen: nothing can be out yet
         uint4 p[NP];
 #pragma unroll
         for (int i = 0; i < NP; i++) p[i] = ZERO;
@@ -188,15 +192,15 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
         bool tile_alive = true;
         for (; s < S; s++) {
             bool lane_alive = active;
-            if (s >= F) {
-                lane_alive = active && any4(below_f<NP>(p, F));
+            if (s >= T) {
+                lane_alive = active && any4(below_f<NP>(p, T));
                 if (!__any_sync(0xFFFFFFFFu, lane_alive)) { tile_alive = false; break; }
             }
             nloads += vote_group<NQ, NP, 1>(colp, Wp16, my_idx + s * NQ, lane_alive, p);
         }
         if (!tile_alive) continue;
-        // buckets with miss count < F
-        const uint4 lt = below_f<NP>(p, F);
+        // buckets with miss count < T
+        const uint4 lt = below_f<NP>(p, T);
         uint4 alive = active ? and4(lt, valid_bits(col, NB)) : ZERO;
         if (!__any_sync(0xFFFFFFFFu, any4(alive))) continue;
         // minimum miss count inside this lane's 128 buckets, and the buckets attaining it

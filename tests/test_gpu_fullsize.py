@@ -122,9 +122,14 @@ def test_full_error_free_reads_land_on_their_origin_and_align_perfectly(full):
     read_of = np.repeat(np.arange(n), cnt)
     pos = locs["bucket"].astype(np.int64) * L + locs["offset"]
     exact = (pos == start[read_of]) & (locs["is_original"] == (~rev[read_of]).astype(np.uint32))
+    # a read hanging over the end of a bucket is still located there (its first samples vote), but its text window is
+    # clipped at the bucket end (bucket_locator.h:550): only whole-read windows must verify perfectly
+    whole = locs["offset"].astype(np.int64) + 300 <= full.b_len[locs["bucket"]].astype(np.int64)
     found = np.zeros(n, bool)
     np.logical_or.at(found, read_of[exact], True)
     assert found[cnt > 0].all()
+    exact &= whole
+    assert exact.sum() >= (cnt > 0).sum()
     # an exact location verifies with edit distance 0, begin 0 and a single 300M op
     assert (aln["score"][exact] == 0).all()
     # forward strand: the read starts at column 0 of its text window; reverse strand: the window (read length + 1 +
