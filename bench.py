@@ -168,6 +168,83 @@ def cpu_leg(cfg, packed, NB, b_start, b_len, k2i, rows, n_sample, full_reads, th
             "span": span}
 
 
+# ----------------------------------------------------------------------------------- CPU (reference itself) leg
+def reference_leg(cfg, packed, NB, b_start, k2i, rows, n_per_proc, full_reads, procs):
+    """times oracle/_ref/bucketmap_<NB>_<L> -- the reference's own main.cpp built against oracle/shim -- on a bounded
+    sample of the workload: `procs` independent single-threaded processes (the reference has no threads), each mapping
+    its own n_per_proc reads drawn from its own genome span sized so that reads per bucket match the full batch.
+    Timed: the reference's own [BENCHMARK] phase timers for bucket mapping + per-bucket k-mer index builds + offset
+    finding (the scope of one bench step); FASTA/index loading and SAM output are outside, as they are for the GPU arm.
+    The index files are handed over ready-made (they are byte-identical to what `bucketmap -x` writes: tests/golden)."""
+    import shutil
+    import subprocess
+    import tempfile
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import bm_ref
+    from bucketmap_b200 import datagen
+    L, n_bases = cfg["L"], cfg["n_bases"]
+    work = tempfile.mkdtemp(prefix="bm_ref_bench_")
+    try:
+        fa = os.path.join(work, "genome.fa")
+        datagen.write_fasta_fast(fa, packed, n_bases, "chr1")
+        np.ascontiguousarray(rows).tofile(os.path.join(work, "idx.qgram"))
+        with open(os.path.join(work, "idx.kmers_index"), "wb") as f:
+            f.write(("\n".join(map(str, k2i.tolist())) + "\n").encode())
+        with open(os.path.join(work, "idx.bucket_id"), "w") as f:
+            f.write("chr1\n" * len(b_start))
+        span = max(int(n_bases * n_per_proc / full_reads), 4 * L)
+        span -= span % 4
+        procs = max(1, min(procs, n_bases // span))
+        runs = []
+        env = dict(os.environ, BM_GENOME=fa, BM_RAND=f"{FMH_X - 1},{FMH_Y}")
+        for pi in range(procs):
+            d = os.path.join(work, f"p{pi}")
+            os.makedirs(d)
+            for ext in ("qgram", "kmers_index", "bucket_id"):
+                os.symlink(os.path.join(work, "idx." + ext), os.path.join(d, "idx." + ext))
+            lo = (n_bases - span) // max(1, procs - 1) * pi if procs > 1 else 0
+            lo -= lo % 4
+            seq, qual, off = datagen.simulate_reads(packed[lo // 4:], span, n_per_proc, cfg["read_len"], cfg["sub"],
+                                                    cfg["indel"], cfg["indel"], READ_SEED + 1000 + pi)[:3]
+            fq = os.path.join(d, "reads.fq")
+            datagen.write_fastq_fast(fq, seq, qual, off)
+            cmd = [bm_ref.binary(NB, L), "-i", "idx", "-q", fq, "-o", os.path.join(d, "out.sam"), "-f", repr(float(cfg["frac"]))]
+            runs.append(subprocess.Popen(cmd, cwd=d, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True))
+        t0 = time.perf_counter()
+        logs = [r.communicate()[1] for r in runs]
+        wall = time.perf_counter() - t0
+        for r, lg in zip(runs, logs):
+            if r.returncode != 0:
+                raise RuntimeError("reference binary failed: " + lg[-1500:])
+        ph = [bm_ref.parse_log(lg) for lg in logs]
+        per = [x["map_s"] + x["kmer_index_s"] + x["find_offset_s"] for x in ph]
+        t = max(per)
+        return {"reads": procs * n_per_proc, "seconds": t, "procs": procs, "reads_per_s": procs * n_per_proc / t,
+                "map_s": max(x["map_s"] for x in ph), "kmer_index_s": max(x["kmer_index_s"] for x in ph),
+                "find_offset_s": max(x["find_offset_s"] for x in ph), "load_s": max(x["load_s"] for x in ph),
+                "wall_s": wall, "span": span, "n_locs": sum(x["locations"] for x in ph)}
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
+def ref_procs():
+    ncores = os.cpu_count() or 1
+    try:
+        import psutil
+        by_mem = int(psutil.virtual_memory().available // (6 << 30))      # ~4 GB peak per reference process at C2
+    except Exception:
+        by_mem = 8
+    return max(1, min(ncores, 16, by_mem))
+
+
+def ref_sample_text(c):
+    return (f"{c['procs']} single-threaded reference processes (oracle/_ref, the reference's own main.cpp) x "
+            f"{c['reads'] // c['procs']} reads, each drawn from its own {c['span']}-base span (same reads per bucket as "
+            f"the full batch), full index; slowest process: bucket mapping {c['map_s']:.2f}s + per-bucket k-mer index "
+            f"{c['kmer_index_s']:.2f}s + offset vote {c['find_offset_s']:.2f}s (its own [BENCHMARK] timers; index load "
+            f"{c['load_s']:.0f}s and FASTA parse not counted)")
+
+
 def main():
     a = parse()
     cfg = CONFIGS[a.config]
@@ -321,12 +398,19 @@ def main():
     if rank == 0 and world == 1 and not a.no_cpu:
         rows = ctx.index_download()
         ncores = os.cpu_count() or 1
-        n_sample = a.cpu_sample or max(2000, min(50_000, 600 * ncores))
-        c = cpu_leg(cfg, packed, NB, b_start, b_len, k2i, rows, n_sample, a.reads, ncores)
-        out["cpu_baseline"] = {"value": c["reads_per_s"], "unit": unit, "cores": c["threads"], "kind": "port",
-                               "sample": f"{c['reads']} reads drawn from the first {c['span']} bases (same reads per "
-                                         f"bucket as the full batch), full index; map {c['map_s']:.2f}s + locate/merge "
-                                         f"{c['locate_s']:.2f}s"}
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import bm_ref
+        if bm_ref.available(NB, cfg["L"]):
+            c = reference_leg(cfg, packed, NB, b_start, k2i, rows, a.cpu_sample or 12_000, a.reads, ref_procs())
+            out["cpu_baseline"] = {"value": c["reads_per_s"], "unit": unit, "cores": c["procs"], "kind": "reference",
+                                   "sample": ref_sample_text(c)}
+        else:
+            n_sample = a.cpu_sample or max(2000, min(50_000, 600 * ncores))
+            c = cpu_leg(cfg, packed, NB, b_start, b_len, k2i, rows, n_sample, a.reads, ncores)
+            out["cpu_baseline"] = {"value": c["reads_per_s"], "unit": unit, "cores": c["threads"], "kind": "port",
+                                   "sample": f"{c['reads']} reads drawn from the first {c['span']} bases (same reads per "
+                                             f"bucket as the full batch), full index; map {c['map_s']:.2f}s + locate/merge "
+                                             f"{c['locate_s']:.2f}s"}
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -343,15 +427,34 @@ def fracminhash(q, x, y, frac):
 
 
 def run_reference(a, cfg, workload, metric, unit):
-    """reference arm: the reference's CPU implementation of the path on the host cores (oracle port; all threads)"""
+    """reference arm: the reference's own CPU implementation of the path on the host cores.  oracle/_ref (the
+    reference's main.cpp built from /root/reference against oracle/shim) when the binary for this bucket count was
+    prebuilt, else the oracle port with all host threads."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import bm_oracle
+    import bm_ref
     bm_oracle.build()
     ncores = os.cpu_count() or 1
     o = bm_oracle.Oracle(ncores)
     packed, NB, b_start, b_len = make_workload(cfg, a.reads, GENOME_SEED)
     k2i, n_rows = o.fracminhash(9, FMH_X, FMH_Y, cfg["frac"])
-    rows = o.index_build(packed, b_start, b_len, NB, 9, k2i, n_rows)
+    rows = o.index_build(packed, b_start, b_len, NB, 9, k2i, n_rows)   # setup only: == `bucketmap -x` (tests/golden)
+    steps = max(1, a.steps)
+    if bm_ref.available(NB, cfg["L"]):
+        n_per = a.cpu_sample or max(2000, min(12_000, 36_000 // steps))
+        c = reference_leg(cfg, packed, NB, b_start, k2i, rows, n_per * steps, a.reads, ref_procs())
+        v = c["reads_per_s"]
+        print(json.dumps({
+            "impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": a.gpus, "steps": steps,
+            "warmup": a.warmup, "ms_per_step": c["seconds"] / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64 bitwise (std::bitset)", "data": "synthetic",
+            "config": {"workload": workload, "NB": NB,
+                       "note": "unmodified reference sources (oracle/_ref); a step = %d reads per process; one launch "
+                               "covers all steps, warm-up reads are not separable inside the reference process" % n_per},
+            "cpu_baseline": {"value": v, "unit": unit, "cores": c["procs"], "kind": "reference", "sample": ref_sample_text(c)},
+            "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }), flush=True)
+        return
     P = o.params(cfg["L"])
     n_sample = a.cpu_sample or max(2000, min(50_000, 600 * ncores))
     span = min(max(int(cfg["n_bases"] * n_sample / a.reads), 4 * cfg["L"]), cfg["n_bases"])

@@ -141,3 +141,44 @@ def write_fastq(path, seq, qual, off, names=None):
             a, b = int(off[i]), int(off[i + 1])
             nm = str(i) if names is None else names[i]
             f.write(b"@" + nm.encode() + b"\n" + seq[a:b].tobytes() + b"\n+\n" + qual[a:b].tobytes() + b"\n")
+
+
+def write_fasta_fast(path, packed, n_bases, name, width=60, chunk=1 << 26):
+    """single-record FASTA of a packed genome, vectorised (the per-line loop of write_fasta is too slow at Gbp scale)"""
+    lut = np.zeros((256, 4), np.uint8)
+    v = np.arange(256)
+    for j in range(4):
+        lut[:, j] = _ASCII[(v >> (2 * j)) & 3]
+    chunk -= chunk % (4 * width)
+    with open(path, "wb") as f:
+        f.write(b">" + name.encode() + b"\n")
+        for b0 in range(0, n_bases, chunk):
+            n = min(chunk, n_bases - b0)
+            s = lut[packed[b0 // 4:(b0 + n + 3) // 4]].reshape(-1)[:n]
+            full = n - n % width
+            if full:
+                lines = np.empty((full // width, width + 1), np.uint8)
+                lines[:, :width] = s[:full].reshape(-1, width)
+                lines[:, width] = 10
+                f.write(lines.tobytes())
+            if n % width:
+                f.write(s[full:].tobytes() + b"\n")
+
+
+def write_fastq_fast(path, seq, qual, off):
+    """FASTQ with numeric read names; vectorised for equal-length reads, per-read loop otherwise"""
+    n = len(off) - 1
+    lens = np.diff(off.astype(np.int64))
+    if n and (lens == lens[0]).all():
+        m = int(lens[0])
+        names = np.char.add(np.char.add("@", np.arange(n).astype(str)), "\n").astype("S")
+        body = np.empty((n, 2 * m + 4), np.uint8)
+        body[:, :m] = seq.reshape(n, m)
+        body[:, m] = 10; body[:, m + 1] = ord("+"); body[:, m + 2] = 10
+        body[:, m + 3:2 * m + 3] = qual.reshape(n, m)
+        body[:, 2 * m + 3] = 10
+        with open(path, "wb") as f:
+            for i in range(n):
+                f.write(names[i]); f.write(body[i].tobytes())
+        return
+    write_fastq(path, seq, qual, off)
