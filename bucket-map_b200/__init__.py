@@ -263,6 +263,17 @@ class Context:
         self.n_reads = n
         return off, locs[:int(off[-1])].copy(), stats
 
+    def map_locate_into(self, P, seq, qual, read_off, out_off, out_locs, filter_best=True):
+        """bm_map_locate with caller-provided (ideally pinned) output arrays: out_off uint32[n+1], out_locs LOC_DTYPE[cap].
+        Returns (n_locs, stats)."""
+        n = len(read_off) - 1
+        stats = np.zeros(8, np.uint64)
+        self._ck(self.lib.bm_map_locate(self.h, C.byref(P), _ptr(seq), _ptr(qual), _ptr(read_off), n,
+                                        int(filter_best), _ptr(out_off), _ptr(out_locs), len(out_locs), _ptr(stats)),
+                 "bm_map_locate")
+        self.n_reads = n
+        return int(out_off[n]), stats
+
     # ---- alignment -----------------------------------------------------------------------------------------------
     def align_device(self, P):
         self._ck(self.lib.bm_align_device(self.h, C.byref(P)), "bm_align_device")

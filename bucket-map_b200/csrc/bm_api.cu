@@ -34,6 +34,7 @@ int bm_ctx_create(int device, bm_ctx** out) {
 
 void bm_ctx_destroy(bm_ctx* c) {
     if (!c) return;
+    for (auto& l : c->lane) { if (l) bm_ctx_destroy(l); l = nullptr; }
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->d_packed, &c->d_bstart, &c->d_blen, &c->d_rows, &c->d_k2i, &c->d_zeros, &c->d_distok,
@@ -114,14 +115,17 @@ int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uin
     if (p->read_len == 0 || p->num_segment_samples == 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad parameters");
     cudaSetDevice(c->device);
     c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
-    uint64_t nbytes = read_off[n_reads] - read_off[0];
-    if (read_off[0] != 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off[0] must be 0");
+    // read i = seq[read_off[i], read_off[i+1]); read_off[0] may be non-zero (a slice of a larger batch)
+    const uint64_t base = read_off[0];
+    uint64_t nbytes = read_off[n_reads] - base;
+    c->h_off_rel.resize((size_t)n_reads + 1);
     // segment table: q_gram_mapper.h:509-523 / bucket_locator.h:302-313
     c->h_seg_read.clear(); c->h_seg_start.clear(); c->h_seg_len.clear(); c->h_read_seg0.clear();
     std::vector<uint32_t> st;
     uint32_t mx = 0, mxr = 0;
     for (uint32_t i = 0; i < n_reads; i++) {
         if (read_off[i + 1] < read_off[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
+        c->h_off_rel[i] = read_off[i] - base;
         uint64_t len64 = read_off[i + 1] - read_off[i];
         if (len64 > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31");
         uint32_t len = (uint32_t)len64;
@@ -136,6 +140,7 @@ int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uin
         }
     }
     uint32_t n_seg = (uint32_t)c->h_seg_read.size();
+    c->h_off_rel[n_reads] = nbytes;
     c->h_read_seg0.push_back(n_seg);
     BM_CK(c, c->d_read_seg0.ensure((size_t)(n_reads + 1) * 4));
     BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.p, c->h_read_seg0.data(), (size_t)(n_reads + 1) * 4, cudaMemcpyHostToDevice, c->stream));
@@ -146,10 +151,10 @@ int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uin
     BM_CK(c, c->d_seg_start.ensure((size_t)(n_seg + 1) * 4));
     BM_CK(c, c->d_seg_len.ensure((size_t)(n_seg + 1) * 4));
     if (nbytes) {
-        BM_CK(c, cudaMemcpyAsync(c->d_seq.p, seq, nbytes, cudaMemcpyHostToDevice, c->stream));
-        BM_CK(c, cudaMemcpyAsync(c->d_qual.p, qual, nbytes, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seq.p, seq + base, nbytes, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_qual.p, qual + base, nbytes, cudaMemcpyHostToDevice, c->stream));
     }
-    BM_CK(c, cudaMemcpyAsync(c->d_read_off.p, read_off, (size_t)(n_reads + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    BM_CK(c, cudaMemcpyAsync(c->d_read_off.p, c->h_off_rel.data(), (size_t)(n_reads + 1) * 8, cudaMemcpyHostToDevice, c->stream));
     if (n_seg) {
         BM_CK(c, cudaMemcpyAsync(c->d_seg_read.p, c->h_seg_read.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
         BM_CK(c, cudaMemcpyAsync(c->d_seg_start.p, c->h_seg_start.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));

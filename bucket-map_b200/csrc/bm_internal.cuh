@@ -14,15 +14,18 @@
 struct DevBuf {
     void*  p = nullptr;
     size_t cap = 0;
+    bool   owned = true;                 // false: a view of another context's buffer (pipeline lanes share the index)
+    void view_of(const DevBuf& o) { if (owned && p) cudaFree(p); p = o.p; cap = o.cap; owned = false; }
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
+        if (!owned) { p = nullptr; cap = 0; owned = true; }
         if (p) { cudaFree(p); p = nullptr; cap = 0; }
         size_t want = bytes + (bytes >> 3) + 256;   // slack so slowly growing batches do not realloc every call
         cudaError_t e = cudaMalloc(&p, want);
         if (e == cudaSuccess) cap = want;
         return e;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    void release() { if (p && owned) cudaFree(p); p = nullptr; cap = 0; owned = true; }
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
@@ -75,6 +78,11 @@ struct bm_ctx {
     // L2 flush scratch
     DevBuf d_flush;
 
+    // pipeline lanes of bm_map_locate: child contexts with their own stream and batch buffers that share (view) the
+    // parent's index and reference buffers
+    bm_ctx* lane[2] = {nullptr, nullptr};
+    std::vector<uint64_t> h_off_rel;
+
     // measurement
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     bool ktiming = false;
@@ -114,6 +122,9 @@ struct KScope {
 
 int bm_internal_index_prepare(bm_ctx* ctx, float d);          // K0: zeros + distok bitmap for threshold d
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
+int bm_internal_map_locate_serial(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
+                                  const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off,
+                                  bm_loc* locs, uint64_t loc_cap, uint64_t* stats);
 
 // ---------------------------------------------------------------------------------------------------------------
 // device helpers

@@ -659,8 +659,11 @@ int bm_locate_download(bm_ctx* c, uint32_t* loc_off, bm_loc* locs, uint64_t loc_
     return BM_OK;
 }
 
-int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
-                  uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats) {
+}  // extern "C"
+
+int bm_internal_map_locate_serial(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
+                                  const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off,
+                                  bm_loc* locs, uint64_t loc_cap, uint64_t* stats) {
     int r = bm_reads_upload(c, p, seq, qual, read_off, n_reads);
     if (r) return r;
     r = bm_map_device(c, p);
@@ -672,5 +675,3 @@ int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8
     }
     return bm_locate_download(c, loc_off, locs, loc_cap);
 }
-
-}  // extern "C"

@@ -73,3 +73,37 @@ def test_locator_samples_match_oracle(oracle, bm, ctx):
     ctx.locate_device(P, False)
     g2, gl = ctx.locate_download()
     assert np.array_equal(g2, loff) and np.array_equal(gl, locs)
+
+
+@pytest.mark.parametrize("filter_best", [True, False])
+def test_pipelined_map_locate_matches_oracle_and_serial_path(oracle, bm, ctx, filter_best):
+    """bm_map_locate cuts batches of >= 32768 reads into chunks over two lanes: same records, same order"""
+    d = dataset(n_bases=3_000_000, n_reads=70_001, read_len=150, repeats=20)
+    k2i, n_rows = oracle.fracminhash(d.q, X, Y, d.frac)
+    rows = oracle.index_build(d.packed, d.b_start, d.b_len, d.NB, d.q, k2i, n_rows)
+    Po = oracle.params(d.L)
+    P = bm.default_params(ctx.lib, d.L)
+    ctx.ref_upload(d.packed, d.n_bases, d.b_start, d.b_len, d.NB)
+    ctx.index_load(k2i, d.q, rows, d.NB)
+    segs = oracle.segments(Po, d.read_off)
+    coff, cand, ostats = oracle.map_segments(Po, d.NB, k2i, rows, d.seq, d.qual, d.read_off, segs)
+    loff, locs = oracle.locate(Po, d.packed, d.b_start, d.b_len, d.seq, d.qual, d.read_off, segs, coff, cand)
+    if filter_best:
+        loff, locs = oracle.filter_best(Po, d.read_off, loff, locs)
+    n = len(d.read_off) - 1
+    out_off = np.zeros(n + 1, np.uint32)
+    out_locs = np.zeros(len(cand) + 16, bm.LOC_DTYPE)
+    n_locs, stats = ctx.map_locate_into(P, d.seq, d.qual, d.read_off, out_off, out_locs, filter_best)
+    assert n_locs == len(locs)
+    assert np.array_equal(out_off, loff)
+    assert np.array_equal(out_locs[:n_locs], locs)
+    assert np.array_equal(stats[:4], ostats)
+    # serial device path
+    ctx.reads_upload(P, d.seq, d.qual, d.read_off)
+    ctx.map_device(P)
+    ctx.locate_device(P, filter_best)
+    soff, slocs = ctx.locate_download()
+    assert np.array_equal(soff, loff) and np.array_equal(slocs, locs)
+    # a too-small output buffer is an error, not a truncation
+    with pytest.raises(bm.BucketMapError):
+        ctx.map_locate_into(P, d.seq, d.qual, d.read_off, out_off, out_locs[:100], filter_best)
