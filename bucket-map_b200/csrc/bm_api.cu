@@ -34,7 +34,6 @@ int bm_ctx_create(int device, bm_ctx** out) {
 
 void bm_ctx_destroy(bm_ctx* c) {
     if (!c) return;
-    for (auto& l : c->lane) { if (l) bm_ctx_destroy(l); l = nullptr; }
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->d_packed, &c->d_bstart, &c->d_blen, &c->d_rows, &c->d_k2i, &c->d_zeros, &c->d_distok,
@@ -45,6 +44,9 @@ void bm_ctx_destroy(bm_ctx* c) {
                       &c->d_loc_off2, &c->d_vote_scratch, &c->d_locs3, &c->d_loc_pool, &c->d_loc_flags, &c->d_read_seg0, &c->d_aln, &c->d_cigar_fixed, &c->d_cigar_cnt,
                       &c->d_cigar_off, &c->d_cigar, &c->d_aln_scratch, &c->d_flush};
     for (DevBuf* b : bufs) b->release();
+    for (HostBuf* h : {&c->h_read_seg0, &c->h_seg_read, &c->h_seg_start, &c->h_seg_len, &c->h_off_rel}) h->release();
+    for (auto e : c->chunk_ev) cudaEventDestroy(e);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     for (auto& p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     if (c->ev_a) cudaEventDestroy(c->ev_a);
@@ -108,60 +110,101 @@ static void sample_det(uint32_t n, uint32_t ub, std::vector<uint32_t>& out) {
     out.push_back(ub);
 }
 
+}  // extern "C"
+
+// Sizes the host tables and the device buffers of a batch of n_reads reads (n_seg is bounded by
+// n_reads * num_segment_samples) and resets the per-batch state; the tables are filled by bm_internal_build_segments.
+int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads) {
+    if (p->read_len == 0 || p->num_segment_samples == 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad parameters");
+    c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
+    if (read_off[n_reads] < read_off[0]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
+    const uint64_t nbytes = read_off[n_reads] - read_off[0];
+    // long reads (> 2r) are cut into num_segment_samples segments; without one the table has one entry per read
+    // exact segment count: reads longer than 2r are cut into num_segment_samples segments (one cheap pass)
+    uint64_t n_long = 0;
+    const uint64_t two_r = 2ull * p->read_len;
+    for (uint32_t i = 0; i < n_reads; i++) n_long += (read_off[i + 1] - read_off[i]) > two_r;
+    const uint64_t seg_cap = n_reads + n_long * (p->num_segment_samples - 1);
+    if (seg_cap > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: too many segments in one batch");
+    BM_CK(c, c->h_off_rel.ensure((size_t)(n_reads + 1) * 8));
+    BM_CK(c, c->h_read_seg0.ensure((size_t)(n_reads + 1) * 4));
+    BM_CK(c, c->h_seg_read.ensure((size_t)(seg_cap + 1) * 4));
+    BM_CK(c, c->h_seg_start.ensure((size_t)(seg_cap + 1) * 4));
+    BM_CK(c, c->h_seg_len.ensure((size_t)(seg_cap + 1) * 4));
+    BM_CK(c, c->d_read_seg0.ensure((size_t)(n_reads + 1) * 4));
+    BM_CK(c, c->d_seq.ensure(nbytes + 16));
+    BM_CK(c, c->d_qual.ensure(nbytes + 16));
+    BM_CK(c, c->d_read_off.ensure((size_t)(n_reads + 1) * 8));
+    BM_CK(c, c->d_seg_read.ensure((size_t)(seg_cap + 1) * 4));
+    BM_CK(c, c->d_seg_start.ensure((size_t)(seg_cap + 1) * 4));
+    BM_CK(c, c->d_seg_len.ensure((size_t)(seg_cap + 1) * 4));
+    c->n_reads = n_reads; c->n_seg = 0; c->n_seg_total = (uint32_t)seg_cap; c->max_seg_len = 0; c->max_read_len = 0;
+    c->n_read_bytes = nbytes;
+    return BM_OK;
+}
+
+// segment table of reads [r0, r1): q_gram_mapper.h:509-523 / bucket_locator.h:302-313.  Reads must be appended in order.
+int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t r0, uint32_t r1) {
+    uint64_t* off_rel = c->h_off_rel.as<uint64_t>();
+    uint32_t* seg0 = c->h_read_seg0.as<uint32_t>();
+    uint32_t *sr = c->h_seg_read.as<uint32_t>(), *ss = c->h_seg_start.as<uint32_t>(), *sl = c->h_seg_len.as<uint32_t>();
+    const uint64_t base = read_off[0];
+    const uint32_t rl = p->read_len;
+    uint32_t n_seg = c->n_seg, mx = c->max_seg_len, mxr = c->max_read_len;
+    std::vector<uint32_t> st;
+    for (uint32_t i = r0; i < r1; i++) {
+        if (read_off[i + 1] < read_off[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
+        off_rel[i] = read_off[i] - base;
+        const uint64_t len64 = read_off[i + 1] - read_off[i];
+        if (len64 > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31");
+        const uint32_t len = (uint32_t)len64;
+        if (len > mxr) mxr = len;
+        seg0[i] = n_seg;
+        if (len > 2 * rl) {
+            sample_det(p->num_segment_samples, len - rl - 1, st);
+            for (uint32_t s : st) {
+                const uint32_t e = s + rl < len ? s + rl : len;
+                sr[n_seg] = i; ss[n_seg] = s; sl[n_seg] = e - s; n_seg++;
+                if (e - s > mx) mx = e - s;
+            }
+        } else {
+            const uint32_t e = rl < len ? rl : len;
+            sr[n_seg] = i; ss[n_seg] = 0; sl[n_seg] = e; n_seg++;
+            if (e > mx) mx = e;
+        }
+    }
+    off_rel[r1] = read_off[r1] - base;
+    seg0[r1] = n_seg;
+    c->n_seg = n_seg; c->max_seg_len = mx; c->max_read_len = mxr;
+    return BM_OK;
+}
+
+extern "C" {
+
 int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
                     uint32_t n_reads) {
     if (!c) return BM_E_ARG;
     if (!p || !read_off || (n_reads && (!seq || !qual))) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad arguments");
-    if (p->read_len == 0 || p->num_segment_samples == 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad parameters");
     cudaSetDevice(c->device);
-    c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
     // read i = seq[read_off[i], read_off[i+1]); read_off[0] may be non-zero (a slice of a larger batch)
-    const uint64_t base = read_off[0];
-    uint64_t nbytes = read_off[n_reads] - base;
-    c->h_off_rel.resize((size_t)n_reads + 1);
-    // segment table: q_gram_mapper.h:509-523 / bucket_locator.h:302-313
-    c->h_seg_read.clear(); c->h_seg_start.clear(); c->h_seg_len.clear(); c->h_read_seg0.clear();
-    std::vector<uint32_t> st;
-    uint32_t mx = 0, mxr = 0;
-    for (uint32_t i = 0; i < n_reads; i++) {
-        if (read_off[i + 1] < read_off[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
-        c->h_off_rel[i] = read_off[i] - base;
-        uint64_t len64 = read_off[i + 1] - read_off[i];
-        if (len64 > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31");
-        uint32_t len = (uint32_t)len64;
-        if (len > mxr) mxr = len;
-        c->h_read_seg0.push_back((uint32_t)c->h_seg_read.size());
-        if (len > 2 * p->read_len) sample_det(p->num_segment_samples, len - p->read_len - 1, st);
-        else st.assign(1, 0u);
-        for (uint32_t s : st) {
-            uint32_t e = s + p->read_len < len ? s + p->read_len : len;
-            c->h_seg_read.push_back(i); c->h_seg_start.push_back(s); c->h_seg_len.push_back(e - s);
-            if (e - s > mx) mx = e - s;
-        }
-    }
-    uint32_t n_seg = (uint32_t)c->h_seg_read.size();
-    c->h_off_rel[n_reads] = nbytes;
-    c->h_read_seg0.push_back(n_seg);
-    BM_CK(c, c->d_read_seg0.ensure((size_t)(n_reads + 1) * 4));
-    BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.p, c->h_read_seg0.data(), (size_t)(n_reads + 1) * 4, cudaMemcpyHostToDevice, c->stream));
-    BM_CK(c, c->d_seq.ensure(nbytes + 16));
-    BM_CK(c, c->d_qual.ensure(nbytes + 16));
-    BM_CK(c, c->d_read_off.ensure((size_t)(n_reads + 1) * 8));
-    BM_CK(c, c->d_seg_read.ensure((size_t)(n_seg + 1) * 4));
-    BM_CK(c, c->d_seg_start.ensure((size_t)(n_seg + 1) * 4));
-    BM_CK(c, c->d_seg_len.ensure((size_t)(n_seg + 1) * 4));
+    int r = bm_internal_reads_begin(c, p, read_off, n_reads);
+    if (r) return r;
+    r = bm_internal_build_segments(c, p, read_off, 0, n_reads);
+    if (r) return r;
+    const uint64_t base = read_off[0], nbytes = c->n_read_bytes;
+    const uint32_t n_seg = c->n_seg;
+    BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.p, c->h_read_seg0.p, (size_t)(n_reads + 1) * 4, cudaMemcpyHostToDevice, c->stream));
     if (nbytes) {
         BM_CK(c, cudaMemcpyAsync(c->d_seq.p, seq + base, nbytes, cudaMemcpyHostToDevice, c->stream));
         BM_CK(c, cudaMemcpyAsync(c->d_qual.p, qual + base, nbytes, cudaMemcpyHostToDevice, c->stream));
     }
-    BM_CK(c, cudaMemcpyAsync(c->d_read_off.p, c->h_off_rel.data(), (size_t)(n_reads + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    BM_CK(c, cudaMemcpyAsync(c->d_read_off.p, c->h_off_rel.p, (size_t)(n_reads + 1) * 8, cudaMemcpyHostToDevice, c->stream));
     if (n_seg) {
-        BM_CK(c, cudaMemcpyAsync(c->d_seg_read.p, c->h_seg_read.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
-        BM_CK(c, cudaMemcpyAsync(c->d_seg_start.p, c->h_seg_start.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
-        BM_CK(c, cudaMemcpyAsync(c->d_seg_len.p, c->h_seg_len.data(), (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_read.p, c->h_seg_read.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_start.p, c->h_seg_start.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_len.p, c->h_seg_len.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
     }
-    BM_CK(c, cudaStreamSynchronize(c->stream));   // host vectors / caller buffers may be reused after return
-    c->n_reads = n_reads; c->n_seg = n_seg; c->max_seg_len = mx; c->max_read_len = mxr; c->n_read_bytes = nbytes;
+    BM_CK(c, cudaStreamSynchronize(c->stream));   // the caller's buffers may be reused after return
     c->have_reads = true;
     return BM_OK;
 }
@@ -171,9 +214,9 @@ int bm_reads_segments(bm_ctx* c, uint32_t* n_seg, uint32_t* seg_read, uint32_t* 
     if (!c->have_reads) BM_FAIL(c, BM_E_ARG, "bm_reads_segments: no read batch resident");
     if (n_seg) *n_seg = c->n_seg;
     size_t b = (size_t)c->n_seg * 4;
-    if (seg_read && b) memcpy(seg_read, c->h_seg_read.data(), b);
-    if (seg_start && b) memcpy(seg_start, c->h_seg_start.data(), b);
-    if (seg_len && b) memcpy(seg_len, c->h_seg_len.data(), b);
+    if (seg_read && b) memcpy(seg_read, c->h_seg_read.p, b);
+    if (seg_start && b) memcpy(seg_start, c->h_seg_start.p, b);
+    if (seg_len && b) memcpy(seg_len, c->h_seg_len.p, b);
     return BM_OK;
 }
 

@@ -29,6 +29,24 @@ struct DevBuf {
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// growable pinned host buffer (staging tables the copy engine reads asynchronously)
+struct HostBuf {
+    void*  p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        void* np_ = nullptr;
+        size_t want = bytes + (bytes >> 3) + 256;
+        cudaError_t e = cudaMallocHost(&np_, want);
+        if (e != cudaSuccess) return e;
+        if (p) cudaFreeHost(p);
+        p = np_; cap = want;
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
 struct KStat { double ms = 0; uint64_t launches = 0; };
 struct PendingEv { int kid; cudaEvent_t a, b; };
 
@@ -52,9 +70,8 @@ struct bm_ctx {
 
     // read batch
     DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len, d_read_seg0;
-    std::vector<uint32_t> h_read_seg0;
-    std::vector<uint32_t> h_seg_read, h_seg_start, h_seg_len;
-    uint32_t n_reads = 0, n_seg = 0, max_seg_len = 0, max_read_len = 0;
+    HostBuf h_read_seg0, h_seg_read, h_seg_start, h_seg_len, h_off_rel;   // pinned; filled by bm_internal_build_segments
+    uint32_t n_reads = 0, n_seg = 0, n_seg_total = 0, max_seg_len = 0, max_read_len = 0;
     uint64_t n_read_bytes = 0;
     bool have_reads = false;
 
@@ -78,10 +95,9 @@ struct bm_ctx {
     // L2 flush scratch
     DevBuf d_flush;
 
-    // pipeline lanes of bm_map_locate: child contexts with their own stream and batch buffers that share (view) the
-    // parent's index and reference buffers
-    bm_ctx* lane[2] = {nullptr, nullptr};
-    std::vector<uint64_t> h_off_rel;
+    // bm_map_locate pipeline: copy stream + one event per chunk
+    cudaStream_t copy_stream = nullptr;
+    std::vector<cudaEvent_t> chunk_ev;
 
     // measurement
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
@@ -122,6 +138,13 @@ struct KScope {
 
 int bm_internal_index_prepare(bm_ctx* ctx, float d);          // K0: zeros + distok bitmap for threshold d
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
+// reads: size the batch buffers (host tables + device), then append the segment table of reads [r0, r1)
+int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads);
+int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t r0, uint32_t r1);
+// mapper in three steps so that K2a/K2 can run on a segment range as soon as its bytes are resident
+int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uint32_t max_seg_len);
+int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len);
+int bm_internal_map_finish(bm_ctx* c, const bm_params* p);
 int bm_internal_map_locate_serial(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
                                   const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off,
                                   bm_loc* locs, uint64_t loc_cap, uint64_t* stats);

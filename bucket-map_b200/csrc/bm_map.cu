@@ -25,13 +25,13 @@ constexpr int kWarpsPerCta = 4;
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 k_map_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, const uint64_t* __restrict__ read_off,
              const uint32_t* __restrict__ seg_read, const uint32_t* __restrict__ seg_start,
-             const uint32_t* __restrict__ seg_len, uint32_t n_seg, uint32_t max_seg_len,
+             const uint32_t* __restrict__ seg_len, uint32_t seg0, uint32_t n_seg, uint32_t max_seg_len,
              const int32_t* __restrict__ k2i, const uint32_t* __restrict__ distok, uint32_t k, uint32_t q, uint32_t S,
              uint32_t minq, uint32_t min_good, int32_t* __restrict__ rowidx, uint8_t* __restrict__ segok,
              unsigned long long* __restrict__ stats) {
     extern __shared__ __align__(16) uint8_t smem[];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t seg = blockIdx.x * kWarpsPerCta + warp;
+    const uint32_t seg = seg0 + blockIdx.x * kWarpsPerCta + warp;   // segments [seg0, n_seg) of the batch
     if (seg >= n_seg) return;
     const uint32_t nchunk_max = (max_seg_len + 31) / 32 + 1;
     const uint32_t per_warp = ((2 * max_seg_len + 3) & ~3u) + nchunk_max * 4;
@@ -157,12 +157,12 @@ __device__ __forceinline__ uint4 below_f(const uint4 (&p)[NP], uint32_t F) {
 template <int NQ, int NP>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ rowidx,
-           const uint8_t* __restrict__ segok, uint32_t n_lists, uint32_t S, uint32_t F, uint32_t max_cand,
+           const uint8_t* __restrict__ segok, uint32_t list0, uint32_t n_lists, uint32_t S, uint32_t F, uint32_t max_cand,
            uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt, unsigned long long* __restrict__ stats) {
     constexpr int B = (NQ >= 8) ? 1 : (8 / NQ);           // samples in flight per lane while no tile can be dead yet
     extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * S*NQ row ids
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t list = blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand
+    const uint32_t list = list0 + blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand; lists [list0, n_lists)
     if (list >= n_lists) return;
     if (!segok[list >> 1]) {                              // q_gram_mapper.h:445-447: too few good k-mers
         if (lane == 0) cand_cnt[list] = 0;
@@ -261,10 +261,10 @@ __global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const ui
 }
 
 template <int NQ>
-cudaError_t launch_vote_np(bm_ctx* c, const bm_params* p, uint32_t NP, uint32_t n_lists, uint32_t blocks, size_t smem) {
+cudaError_t launch_vote_np(bm_ctx* c, const bm_params* p, uint32_t NP, uint32_t list0, uint32_t n_lists, uint32_t blocks, size_t smem) {
 #define BM_VOTE(NPv)                                                                                               \
     k_map_vote<NQ, NPv><<<blocks, kWarpsPerCta * 32, smem, c->stream>>>(                                           \
-        c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), n_lists,    \
+        c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), list0, n_lists, \
         p->mapper_samples, p->mapper_fault, p->max_candidates, c->d_cand_fixed.as<uint32_t>(),                     \
         c->d_cand_cnt.as<uint32_t>(), c->d_stats.as<unsigned long long>())
     if (NP == 3) BM_VOTE(3); else if (NP == 4) BM_VOTE(4); else BM_VOTE(6);
@@ -279,89 +279,12 @@ extern "C" {
 int bm_map_device(bm_ctx* c, const bm_params* p) {
     if (!c) return BM_E_ARG;
     if (!p) BM_FAIL(c, BM_E_ARG, "bm_map_device: null parameters");
-    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_map_device: no index resident (the q-gram index is empty)");
     if (!c->have_reads) BM_FAIL(c, BM_E_ARG, "bm_map_device: no read batch resident");
-    if (p->q != c->q) BM_FAIL(c, BM_E_ARG, "bm_map_device: index seed length differs from the resident index");
-    if (p->k < p->q || p->k > 16) BM_FAIL(c, BM_E_LIMIT, "query seed length must satisfy q <= k <= 16");
-    const uint32_t NQ = p->k - p->q + 1, S = p->mapper_samples, F = p->mapper_fault;
-    if (NQ > 8) BM_FAIL(c, BM_E_LIMIT, "k - q must be <= 7");
-    if (S == 0 || S > 256) BM_FAIL(c, BM_E_LIMIT, "mapper samples must be in [1,256]");
-    if (F == 0 || F > 63) BM_FAIL(c, BM_E_LIMIT, "mapper fault-tolerance levels must be in [1,63]");
-    if (p->max_candidates == 0 || p->max_candidates > 1024) BM_FAIL(c, BM_E_LIMIT, "max candidates must be in [1,1024]");
-    if (c->max_seg_len > 8192) BM_FAIL(c, BM_E_LIMIT, "segments longer than 8192 bases are not supported (-r)");
-    cudaSetDevice(c->device);
-    c->have_map = false; c->have_locs = false; c->have_aln = false;
-    int r = bm_internal_index_prepare(c, p->distinguishability);
+    int r = bm_internal_map_begin(c, p, c->n_seg, c->max_seg_len);
     if (r) return r;
-
-    const uint32_t n_seg = c->n_seg, n_lists = 2 * n_seg;
-    BM_CK(c, c->d_rowidx.ensure((size_t)n_lists * S * NQ * 4 + 16));
-    BM_CK(c, c->d_segok.ensure((size_t)n_seg + 16));
-    BM_CK(c, c->d_cand_fixed.ensure((size_t)n_lists * p->max_candidates * 4 + 16));
-    BM_CK(c, c->d_cand_cnt.ensure((size_t)(n_lists + 1) * 4));
-    BM_CK(c, c->d_cand_off.ensure((size_t)(n_lists + 1) * 4));
-    BM_CK(c, c->d_stats.ensure(128 * 8));
-    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * 8, c->stream));
-    c->map_max_cand = p->max_candidates;
-    c->n_cand = 0;
-    if (n_seg) {
-        // smallest G with !(G < 0.2*S), the comparison of q_gram_mapper.h:445 in double
-        uint32_t min_good = 0;
-        while ((double)min_good < 0.2 * (double)S) min_good++;
-        const uint32_t msl = c->max_seg_len ? c->max_seg_len : 1;
-        size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
-        const uint32_t blocks_a = (n_seg + kWarpsPerCta - 1) / kWarpsPerCta;
-        if (smem_a > 48 * 1024)
-            BM_CK(c, cudaFuncSetAttribute(k_map_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a));
-        {
-            KScope ks(c, BM_K_SAMPLE);
-            k_map_sample<<<blocks_a, kWarpsPerCta * 32, smem_a, c->stream>>>(
-                c->d_seq.as<uint8_t>(), c->d_qual.as<uint8_t>(), c->d_read_off.as<uint64_t>(),
-                c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), n_seg, msl,
-                c->d_k2i.as<int32_t>(), c->d_distok.as<uint32_t>(), p->k, p->q, S, p->avg_base_quality * p->k, min_good,
-                c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
-        }
-        BM_CK(c, cudaGetLastError());
-        const uint32_t NP = (F <= 7) ? 3 : (F <= 15 ? 4 : 6);
-        size_t smem_v = (size_t)kWarpsPerCta * S * NQ * 4;
-        const uint32_t blocks_v = (n_lists + kWarpsPerCta - 1) / kWarpsPerCta;
-        cudaError_t e = cudaSuccess;
-        {
-            KScope ks(c, BM_K_MAP);
-            switch (NQ) {
-                case 1: e = launch_vote_np<1>(c, p, NP, n_lists, blocks_v, smem_v); break;
-                case 2: e = launch_vote_np<2>(c, p, NP, n_lists, blocks_v, smem_v); break;
-                case 3: e = launch_vote_np<3>(c, p, NP, n_lists, blocks_v, smem_v); break;
-                case 4: e = launch_vote_np<4>(c, p, NP, n_lists, blocks_v, smem_v); break;
-                case 5: e = launch_vote_np<5>(c, p, NP, n_lists, blocks_v, smem_v); break;
-                case 6: e = launch_vote_np<6>(c, p, NP, n_lists, blocks_v, smem_v); break;
-                case 7: e = launch_vote_np<7>(c, p, NP, n_lists, blocks_v, smem_v); break;
-                default: e = launch_vote_np<8>(c, p, NP, n_lists, blocks_v, smem_v); break;
-            }
-        }
-        BM_CK(c, e);
-        r = bm_internal_exclusive_scan(c, c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists + 1);
-        if (r) return r;
-        // the compacted arrays are at most max_candidates per list, but sizing them exactly needs the total
-        uint32_t total = 0;
-        BM_CK(c, cudaMemcpyAsync(&total, c->d_cand_off.as<uint32_t>() + n_lists, 4, cudaMemcpyDeviceToHost, c->stream));
-        BM_CK(c, cudaStreamSynchronize(c->stream));
-        c->n_cand = total;
-        BM_CK(c, c->d_cand.ensure((size_t)total * 4 + 16));
-        BM_CK(c, c->d_cseg.ensure((size_t)total * 4 + 16));
-        {
-            KScope ks(c, BM_K_AUX);
-            k_cand_compact<<<(n_seg + 255) / 256, 256, 0, c->stream>>>(
-                c->d_cand_fixed.as<uint32_t>(), c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists,
-                p->max_candidates, c->d_cand.as<uint32_t>(), c->d_cseg.as<uint32_t>(),
-                c->d_stats.as<unsigned long long>());
-        }
-        BM_CK(c, cudaGetLastError());
-    } else {
-        BM_CK(c, cudaMemsetAsync(c->d_cand_off.p, 0, 4, c->stream));
-    }
-    c->have_map = true;
-    return BM_OK;
+    r = bm_internal_map_range(c, p, 0, c->n_seg, c->max_seg_len);
+    if (r) return r;
+    return bm_internal_map_finish(c, p);
 }
 
 int bm_map_download(bm_ctx* c, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats) {
@@ -389,3 +312,104 @@ int bm_map_reads(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
 }
 
 }  // extern "C"
+
+// ---- the mapper in three steps ---------------------------------------------------------------------------------------------
+int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uint32_t max_seg_len) {
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_map_device: no index resident (the q-gram index is empty)");
+    if (p->q != c->q) BM_FAIL(c, BM_E_ARG, "bm_map_device: index seed length differs from the resident index");
+    if (p->k < p->q || p->k > 16) BM_FAIL(c, BM_E_LIMIT, "query seed length must satisfy q <= k <= 16");
+    const uint32_t NQ = p->k - p->q + 1, S = p->mapper_samples, F = p->mapper_fault;
+    if (NQ > 8) BM_FAIL(c, BM_E_LIMIT, "k - q must be <= 7");
+    if (S == 0 || S > 256) BM_FAIL(c, BM_E_LIMIT, "mapper samples must be in [1,256]");
+    if (F == 0 || F > 63) BM_FAIL(c, BM_E_LIMIT, "mapper fault-tolerance levels must be in [1,63]");
+    if (p->max_candidates == 0 || p->max_candidates > 1024) BM_FAIL(c, BM_E_LIMIT, "max candidates must be in [1,1024]");
+    if (max_seg_len > 8192) BM_FAIL(c, BM_E_LIMIT, "segments longer than 8192 bases are not supported (-r)");
+    cudaSetDevice(c->device);
+    c->have_map = false; c->have_locs = false; c->have_aln = false;
+    int r = bm_internal_index_prepare(c, p->distinguishability);
+    if (r) return r;
+    const size_t n_lists = 2 * (size_t)n_seg_cap;
+    BM_CK(c, c->d_rowidx.ensure(n_lists * S * NQ * 4 + 16));
+    BM_CK(c, c->d_segok.ensure((size_t)n_seg_cap + 16));
+    BM_CK(c, c->d_cand_fixed.ensure(n_lists * p->max_candidates * 4 + 16));
+    BM_CK(c, c->d_cand_cnt.ensure((n_lists + 1) * 4));
+    BM_CK(c, c->d_cand_off.ensure((n_lists + 1) * 4));
+    BM_CK(c, c->d_stats.ensure(128 * 8));
+    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * 8, c->stream));
+    c->map_max_cand = p->max_candidates;
+    c->n_cand = 0;
+    const uint32_t msl = max_seg_len ? max_seg_len : 1;
+    size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
+    if (smem_a > 48 * 1024)
+        BM_CK(c, cudaFuncSetAttribute(k_map_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a));
+    return BM_OK;
+}
+
+// K2a + K2 over segments [seg0, seg1); everything they read must already be resident (or ordered before on c->stream)
+int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len) {
+    if (seg1 <= seg0) return BM_OK;
+    const uint32_t NQ = p->k - p->q + 1, S = p->mapper_samples, F = p->mapper_fault;
+    // smallest G with !(G < 0.2*S), the comparison of q_gram_mapper.h:445 in double
+    uint32_t min_good = 0;
+    while ((double)min_good < 0.2 * (double)S) min_good++;
+    const uint32_t msl = max_seg_len ? max_seg_len : 1;
+    size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
+    const uint32_t blocks_a = (seg1 - seg0 + kWarpsPerCta - 1) / kWarpsPerCta;
+    {
+        KScope ks(c, BM_K_SAMPLE);
+        k_map_sample<<<blocks_a, kWarpsPerCta * 32, smem_a, c->stream>>>(
+            c->d_seq.as<uint8_t>(), c->d_qual.as<uint8_t>(), c->d_read_off.as<uint64_t>(),
+            c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), seg0, seg1, msl,
+            c->d_k2i.as<int32_t>(), c->d_distok.as<uint32_t>(), p->k, p->q, S, p->avg_base_quality * p->k, min_good,
+            c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
+    }
+    BM_CK(c, cudaGetLastError());
+    const uint32_t NP = (F <= 7) ? 3 : (F <= 15 ? 4 : 6);
+    size_t smem_v = (size_t)kWarpsPerCta * S * NQ * 4;
+    const uint32_t list0 = 2 * seg0, list1 = 2 * seg1;
+    const uint32_t blocks_v = (list1 - list0 + kWarpsPerCta - 1) / kWarpsPerCta;
+    cudaError_t e = cudaSuccess;
+    {
+        KScope ks(c, BM_K_MAP);
+        switch (NQ) {
+            case 1: e = launch_vote_np<1>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+            case 2: e = launch_vote_np<2>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+            case 3: e = launch_vote_np<3>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+            case 4: e = launch_vote_np<4>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+            case 5: e = launch_vote_np<5>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+            case 6: e = launch_vote_np<6>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+            case 7: e = launch_vote_np<7>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+            default: e = launch_vote_np<8>(c, p, NP, list0, list1, blocks_v, smem_v); break;
+        }
+    }
+    BM_CK(c, e);
+    return BM_OK;
+}
+
+// fixed-slot lists of all c->n_seg segments -> cand_off / cand
+int bm_internal_map_finish(bm_ctx* c, const bm_params* p) {
+    const uint32_t n_seg = c->n_seg, n_lists = 2 * n_seg;
+    if (n_seg) {
+        int r = bm_internal_exclusive_scan(c, c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists + 1);
+        if (r) return r;
+        // the compacted arrays are at most max_candidates per list, but sizing them exactly needs the total
+        uint32_t total = 0;
+        BM_CK(c, cudaMemcpyAsync(&total, c->d_cand_off.as<uint32_t>() + n_lists, 4, cudaMemcpyDeviceToHost, c->stream));
+        BM_CK(c, cudaStreamSynchronize(c->stream));
+        c->n_cand = total;
+        BM_CK(c, c->d_cand.ensure((size_t)total * 4 + 16));
+        BM_CK(c, c->d_cseg.ensure((size_t)total * 4 + 16));
+        {
+            KScope ks(c, BM_K_AUX);
+            k_cand_compact<<<(n_seg + 255) / 256, 256, 0, c->stream>>>(
+                c->d_cand_fixed.as<uint32_t>(), c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists,
+                p->max_candidates, c->d_cand.as<uint32_t>(), c->d_cseg.as<uint32_t>(),
+                c->d_stats.as<unsigned long long>());
+        }
+        BM_CK(c, cudaGetLastError());
+    } else {
+        BM_CK(c, cudaMemsetAsync(c->d_cand_off.p, 0, 4, c->stream));
+    }
+    c->have_map = true;
+    return BM_OK;
+}
