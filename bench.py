@@ -390,7 +390,7 @@ def main():
                    "l2": "inputs larger than L2 (bit matrix %d MB vs 126 MB L2)" % (n_rows * W >> 20),
                    "step": "bm_map_device + bm_locate_device(filter_best=1)" + (" + NCCL gather" if world > 1 else "")},
         "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "api": "bm_map_locate (pinned host buffers in, host records out; two pipelined lanes inside the call)"},
+                "api": "bm_map_locate (pinned host buffers in, host records out; H2D chunks pipelined against the mapper inside the call)"},
         "gpu_launches": launches,
         "clocks": clk,
         "roofline": {"kernel": "k_map_vote", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
