@@ -51,6 +51,9 @@ def parse():
     ap.add_argument("--reads", type=int, default=1_000_000, help="reads per GPU per step")
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--ktable", type=int, default=1, choices=[0, 1],
+                    help="1: mapper gathers one precomputed k-mer row per sample (table derived on the device when "
+                         "4^k rows fit); 0: gathers the k-q+1 q-gram rows per sample")
     return ap.parse_args()
 
 
@@ -126,14 +129,14 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(config_name, n_reads):
+def ncu_traffic(config_name, n_reads, ktable):
     """per-launch DRAM bytes (read+write) of k_map_vote from the committed ncu --set full capture of this workload,
     scaled from the captured launch size to this launch's reads (traffic is linear in reads: no reuse across reads)"""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
             d = json.load(open(p))
-            if d.get("workload") == config_name:
+            if d.get("workload") == config_name and bool(d.get("kmer_table", False)) == bool(ktable):
                 per = (d["dram_bytes_read_per_launch"] + d["dram_bytes_write_per_launch"]) / d["captured_reads_per_launch"]
                 return per * n_reads
         except Exception:
@@ -273,6 +276,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = bm.Context(local)
+    ctx.index_kmer_table(a.ktable)
     P = bm.default_params(ctx.lib, cfg["L"])
     q = 9
 
@@ -326,6 +330,9 @@ def main():
 
     for _ in range(a.warmup):
         step_resident()
+    ctx.sync()
+    ktable_ms = ctx.kernel_stats()["kmer_table"][0]     # one-off, inside the first (untimed) mapper call
+    ktable_k, ktable_bytes = ctx.index_kmer_table_info()
     ctx.kernel_stats_reset()
     barrier()
     clocks = ClockSampler(local)
@@ -395,14 +402,19 @@ def main():
                                             # in the kernel (tiles whose buckets all reached F misses stop early)
     peak, peak_src = measured_peak()
     achieved = alg_bytes / (vote_ms / vote_n * 1e-3) / 1e9 if vote_n else None
-    traffic = ncu_traffic(a.config, n_reads)
+    traffic = ncu_traffic(a.config, n_reads, ktable_k)
+    rows_per_sample = 1 if ktable_k else 4
     launches = int(sum(v[1] for v in kst.values()))
     out = {
         "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u32 bitwise", "data": "synthetic",
         "config": {"workload": workload, "genome_bases": cfg["n_bases"], "bucket_len": cfg["L"], "NB": NB,
-                   "row_bytes": W, "matrix_bytes": int(n_rows) * W, "reads_per_gpu_per_step": n_reads,
+                   "row_bytes": W, "matrix_bytes": int(n_rows) * W, "kmer_table_bytes": int(ktable_bytes),
+                   "kmer_table": ("4^%d k-mer rows (AND of each k-mer's q-gram rows), derived on the device from the "
+                                  "matrix in %.1f ms; the mapper gathers 1 row per sample" % (ktable_k, ktable_ms))
+                                 if ktable_k else "off: the mapper gathers the k-q+1 q-gram rows per sample",
+                   "reads_per_gpu_per_step": n_reads,
                    "read_len": cfg["read_len"], "flags": "-k 9 -l 12 -s 15 -e 0.4 -p 10 -f %g" % cfg["frac"],
                    "parallelism": f"reads sharded x{world}, index replicated",
                    "timing": "CUDA events on the library stream" if world == 1 else "wall clock between device-synchronised barriers (NCCL gather on its own stream), max over ranks",
@@ -418,11 +430,13 @@ def main():
                      "ms_per_launch": vote_ms / vote_n if vote_n else None,
                      "rows_gathered_per_read": rows_gathered / max(1, n_reads),
                      "reference_cascade_bytes_per_launch": rows_gathered * W,
-                     "alg_bytes_definition": "16-B row loads issued by k_map_vote (counted in-kernel): the q-gram rows of "
+                     "rows_per_sample": rows_per_sample,
+                     "alg_bytes_definition": "16-B row loads issued by k_map_vote (counted in-kernel): %s of "
                                              "every 512-B column tile until all 4096 buckets of the tile have missed F "
-                                             "samples; reference_cascade_bytes = all S*(k-q+1) rows of both strands x W"},
+                                             "samples; reference_cascade_bytes = all S*(k-q+1) rows of both strands x W"
+                                             % ("the one k-mer-table row per sample" if ktable_k else "the q-gram rows")},
         "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
-        "index_build_ms": index_ms, "index_bcast_ms": bcast_ms, "setup_s": setup_s,
+        "index_build_ms": index_ms, "kmer_table_build_ms": ktable_ms, "index_bcast_ms": bcast_ms, "setup_s": setup_s,
         "mapped": {"reads_with_candidate": int(mstats[0]), "cand_fwd": int(mstats[1]), "cand_rev": int(mstats[2])},
     }
     if rank == 0 and world == 1 and not a.no_cpu:

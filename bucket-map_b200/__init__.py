@@ -12,8 +12,9 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbucketmap_b200.so")
 
-K_ROWPOP, K_INDEX, K_SAMPLE, K_MAP, K_LOCSAMPLE, K_LOCATE, K_MERGE, K_ALIGN, K_AUX, K_COUNT = range(10)
-KERNEL_NAMES = ["rowpop", "index_build", "map_sample", "map_vote", "loc_sample", "locate", "merge", "align", "aux"]
+K_ROWPOP, K_INDEX, K_SAMPLE, K_MAP, K_LOCSAMPLE, K_LOCATE, K_MERGE, K_ALIGN, K_AUX, K_KTABLE, K_COUNT = range(11)
+KERNEL_NAMES = ["rowpop", "index_build", "map_sample", "map_vote", "loc_sample", "locate", "merge", "align", "aux",
+                "kmer_table"]
 
 
 class Params(C.Structure):
@@ -48,6 +49,8 @@ SIGNATURES = {
     "bm_index_load": (C.c_int, [_vp, _vp, C.c_uint32, _vp, C.c_uint32, C.c_uint32]),
     "bm_index_download": (C.c_int, [_vp, _vp]),
     "bm_index_zeros": (C.c_int, [_vp, C.c_float, _vp, C.POINTER(C.c_uint32)]),
+    "bm_index_kmer_table": (C.c_int, [_vp, C.c_int, C.c_uint64]),
+    "bm_index_kmer_table_info": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
     "bm_index_free": (C.c_int, [_vp]),
     "bm_index_alloc": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32]),
     "bm_index_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
@@ -169,6 +172,15 @@ class Context:
         v = C.c_uint32()
         self._ck(self.lib.bm_index_zeros(self.h, d, _ptr(z), C.byref(v)), "bm_index_zeros")
         return z, v.value
+
+    def index_kmer_table(self, mode, max_bytes=0):
+        """0: the mapper gathers the k-q+1 q-gram rows per sample; 1 (default): one k-mer row when 4^k rows fit."""
+        self._ck(self.lib.bm_index_kmer_table(self.h, mode, max_bytes), "bm_index_kmer_table")
+
+    def index_kmer_table_info(self):
+        k, n = C.c_uint32(), C.c_uint64()
+        self._ck(self.lib.bm_index_kmer_table_info(self.h, C.byref(k), C.byref(n)), "bm_index_kmer_table_info")
+        return k.value, n.value
 
     def index_free(self):
         self._ck(self.lib.bm_index_free(self.h), "bm_index_free")

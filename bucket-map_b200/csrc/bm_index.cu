@@ -86,6 +86,43 @@ __global__ void k_distok(const int32_t* __restrict__ k2i, const uint32_t* __rest
     if ((threadIdx.x & 31) == 0 && g < n_codes) distok[g >> 5] = m;
 }
 
+// ---- K0b: k-mer row table ------------------------------------------------------------------------------------------------
+// krows[x] = AND over i in [0, k-q] of rows[kmer_to_index[(x >> 2i) & Q]] (un-indexed q-grams skipped), i.e. exactly the
+// bf_res that q_gram_mapper::query builds for sample hash x (q_gram_mapper.h:399-407) before filter->read().  With it the
+// mapper gathers one row per sample.  A CTA takes 64 consecutive k-mer codes -- they share all but the lowest three
+// base-4 digits, so the rows of the higher q-grams are re-read from L1 -- and one thread owns one 16-B column.
+// HBM traffic: one write of the table plus ~(1 + 1/4 + 1/16 + ...) reads of it; tens of ms for the 54.8 GB table.
+__global__ void __launch_bounds__(256)
+k_kmer_rows(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ k2i, uint32_t NQ,
+            uint32_t Q, uint64_t n_kmers, uint4* __restrict__ krows) {
+    for (uint64_t x0 = (uint64_t)blockIdx.x * 64; x0 < n_kmers; x0 += (uint64_t)gridDim.x * 64) {
+        const uint32_t nx = (uint32_t)min((uint64_t)64, n_kmers - x0);
+        for (uint32_t c = threadIdx.x; c < Wp16; c += blockDim.x) {
+            // a k-mer none of whose q-grams is indexed matches every REAL bucket; padding bits stay zero
+            uint32_t w[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                uint32_t b = c * 128u + 32u * i;
+                w[i] = (b >= NB) ? 0u : (NB - b >= 32u ? 0xFFFFFFFFu : ((1u << (NB - b)) - 1u));
+            }
+            const uint4 all = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll 4
+            for (uint32_t j = 0; j < nx; j++) {
+                const uint32_t x = (uint32_t)(x0 + j);
+                uint4 v = all;
+                for (uint32_t i = 0; i < NQ; i++) {
+                    const int32_t r = __ldg(k2i + ((x >> (2 * i)) & Q));
+                    if (r >= 0) {
+                        const uint4 t = __ldg(rows + (size_t)r * Wp16 + c);
+                        v.x &= t.x; v.y &= t.y; v.z &= t.z; v.w &= t.w;
+                    }
+                }
+                __stcs(krows + (x0 + j) * Wp16 + c, v);
+            }
+        }
+    }
+}
+
 int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t NB) {
     if (q == 0 || q > 14) BM_FAIL(c, BM_E_LIMIT, "index seed length q must be in [1,14]");
     if (NB == 0) BM_FAIL(c, BM_E_ARG, "NB must be > 0");
@@ -95,7 +132,7 @@ int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32
         if (k2i[i] >= 0) { if ((uint32_t)k2i[i] >= n_rows) BM_FAIL(c, BM_E_ARG, "kmer_to_index entry >= n_rows"); cnt++; }
     }
     (void)cnt;
-    c->have_index = false; c->zeros_for_d = -1.f;
+    c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0;
     c->q = q; c->n_rows = n_rows; c->NB = NB;
     c->W = (NB + 7) >> 3; c->Wp = (c->W + 63u) & ~63u;
     BM_CK(c, c->d_k2i.ensure(n_codes * 4));
@@ -134,7 +171,57 @@ int bm_internal_index_prepare(bm_ctx* c, float d) {
     return BM_OK;
 }
 
+// Builds (or re-uses) the k-mer row table for query seed length k; sets c->use_ktable.  Not built when k == q (the
+// q-gram rows already are the k-mer rows), when switched off, or when 4^k rows do not fit the memory budget: the
+// mapper then gathers the k-q+1 q-gram rows per sample.  Both ways are CUDA paths with identical results.
+int bm_internal_kmer_table_prepare(bm_ctx* c, uint32_t k) {
+    c->use_ktable = false;
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "no index resident (bm_index_build / bm_index_load first)");
+    if (c->ktable_mode == 0 || k <= c->q || k < 3 || k > 15 || c->n_rows == 0) {
+        if (c->ktable_mode == 0 && c->d_krows.p) { c->d_krows.release(); c->krows_k = 0; }
+        return BM_OK;
+    }
+    if (c->krows_k == k && c->d_krows.p) { c->use_ktable = true; return BM_OK; }
+    const uint64_t n_kmers = 1ull << (2 * k);
+    const uint64_t bytes = n_kmers * c->Wp;
+    c->d_krows.release(); c->krows_k = 0;
+    uint64_t budget = c->ktable_max_bytes;
+    if (!budget) {
+        size_t fr = 0, tot = 0;
+        BM_CK(c, cudaMemGetInfo(&fr, &tot));
+        budget = fr / 2;                          // leave the other half to read batches, candidates and scratch
+    }
+    if (bytes > budget) return BM_OK;
+    cudaError_t e = c->d_krows.ensure_exact(bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); return BM_OK; }   // does not fit after all: q-gram gather
+    {
+        KScope ks(c, BM_K_KTABLE);
+        const uint64_t want = (n_kmers + 63) / 64;
+        const uint32_t blocks = (uint32_t)(want < (uint64_t)c->sm_count * 64 ? want : (uint64_t)c->sm_count * 64);
+        k_kmer_rows<<<blocks, 256, 0, c->stream>>>(c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_k2i.as<int32_t>(),
+                                                   k - c->q + 1, (1u << (2 * c->q)) - 1u, n_kmers, c->d_krows.as<uint4>());
+    }
+    BM_CK(c, cudaGetLastError());
+    c->krows_k = k; c->use_ktable = true;
+    return BM_OK;
+}
+
 extern "C" {
+
+int bm_index_kmer_table(bm_ctx* c, int mode, uint64_t max_bytes) {
+    if (!c) return BM_E_ARG;
+    if (mode != 0 && mode != 1) BM_FAIL(c, BM_E_ARG, "bm_index_kmer_table: mode must be 0 (off) or 1 (when it fits)");
+    c->ktable_mode = mode; c->ktable_max_bytes = max_bytes;
+    if (mode == 0 || (max_bytes && c->d_krows.cap > max_bytes)) { cudaSetDevice(c->device); c->d_krows.release(); c->krows_k = 0; }
+    return BM_OK;
+}
+
+int bm_index_kmer_table_info(bm_ctx* c, uint32_t* k, uint64_t* bytes) {
+    if (!c) return BM_E_ARG;
+    if (k) *k = (c->d_krows.p ? c->krows_k : 0);
+    if (bytes) *bytes = (c->d_krows.p && c->krows_k) ? ((1ull << (2 * c->krows_k)) * c->Wp) : 0;
+    return BM_OK;
+}
 
 int bm_index_build(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint8_t* out_rows) {
     if (!c) return BM_E_ARG;
@@ -226,7 +313,7 @@ int bm_index_alloc(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, u
 int bm_index_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
     if (!c) return BM_E_ARG;
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_index_device: no index resident");
-    c->zeros_for_d = -1.f;                       // the caller may overwrite the rows: recompute zeros on next use
+    c->zeros_for_d = -1.f; c->krows_k = 0;                       // the caller may overwrite the rows: recompute zeros on next use
     if (dptr) *dptr = c->d_rows.p;
     if (bytes) *bytes = (uint64_t)c->n_rows * c->Wp;
     return BM_OK;
@@ -243,8 +330,9 @@ int bm_ref_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
 int bm_index_free(bm_ctx* c) {
     if (!c) return BM_E_ARG;
     cudaSetDevice(c->device);
+    c->d_krows.release();
     c->d_rows.release(); c->d_zeros.release(); c->d_distok.release(); c->d_k2i.release(); c->d_stage.release();
-    c->have_index = false; c->zeros_for_d = -1.f; c->have_map = false;
+    c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0; c->have_map = false;
     return BM_OK;
 }
 

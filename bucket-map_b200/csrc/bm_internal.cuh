@@ -25,6 +25,14 @@ struct DevBuf {
         if (e == cudaSuccess) cap = want;
         return e;
     }
+    // no slack: for the one buffer that is sized in tens of GB (the k-mer row table)
+    cudaError_t ensure_exact(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
     void release() { if (p && owned) cudaFree(p); p = nullptr; cap = 0; owned = true; }
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
@@ -67,6 +75,15 @@ struct bm_ctx {
     bool have_index = false;
     float zeros_for_d = -1.f;     // distinguishability the distok bitmap was built for (<0: none)
     uint32_t dist_threshold = 0, dist_valid = 0;
+
+    // k-mer row table: row x = AND of the indexed q-gram rows of query k-mer x (4^k rows of Wp bytes), derived on the
+    // device from d_rows so that the mapper gathers ONE row per sample instead of k-q+1.  Sized for 180 GB of HBM:
+    // 4^12 x 3,264 B = 54.8 GB on the 1.7 Gbp reference.  krows_k = the k it was built for (0: not resident).
+    DevBuf d_krows;
+    uint32_t krows_k = 0;
+    int ktable_mode = 1;          // 0 never, 1 when it fits (bm_index_kmer_table)
+    uint64_t ktable_max_bytes = 0;   // 0: half of the free device memory at build time
+    bool use_ktable = false;      // decided by bm_internal_kmer_table_prepare for the current mapper call
 
     // read batch
     DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len, d_read_seg0;
@@ -137,6 +154,7 @@ struct KScope {
 };
 
 int bm_internal_index_prepare(bm_ctx* ctx, float d);          // K0: zeros + distok bitmap for threshold d
+int bm_internal_kmer_table_prepare(bm_ctx* ctx, uint32_t k);  // K0b: k-mer row table for query seed length k (if it fits)
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
 // reads: size the batch buffers (host tables + device), then append the segment table of reads [r0, r1)
 int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads);

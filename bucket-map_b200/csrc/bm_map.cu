@@ -27,7 +27,7 @@ k_map_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, 
              const uint32_t* __restrict__ seg_read, const uint32_t* __restrict__ seg_start,
              const uint32_t* __restrict__ seg_len, uint32_t seg0, uint32_t n_seg, uint32_t max_seg_len,
              const int32_t* __restrict__ k2i, const uint32_t* __restrict__ distok, uint32_t k, uint32_t q, uint32_t S,
-             uint32_t minq, uint32_t min_good, int32_t* __restrict__ rowidx, uint8_t* __restrict__ segok,
+             uint32_t minq, uint32_t min_good, uint32_t ktable, int32_t* __restrict__ rowidx, uint8_t* __restrict__ segok,
              unsigned long long* __restrict__ stats) {
     extern __shared__ __align__(16) uint8_t smem[];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -73,11 +73,13 @@ k_map_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, 
         uint32_t pos = select_good(st.mask, nchunk, sample_index(s, S, G));   // :457-460
         uint32_t h = kmer_hash_at(st.base, pos, k);
         uint32_t hr = bm_revcomp_hash(h, k);                                  // :465-468
-        int32_t* o0 = rowidx + ((size_t)(2 * seg) * S + s) * NQ;
-        int32_t* o1 = rowidx + ((size_t)(2 * seg + 1) * S + s) * NQ;
+        const uint32_t NO = ktable ? 1u : NQ;                                // row ids written per sample
+        int32_t* o0 = rowidx + ((size_t)(2 * seg) * S + s) * NO;
+        int32_t* o1 = rowidx + ((size_t)(2 * seg + 1) * S + s) * NO;
+        if (ktable) { o0[0] = (int32_t)h; o1[0] = (int32_t)hr; }             // k-mer row table: the hash is the row id
         for (uint32_t i = 0; i < NQ; i++) {
             int32_t a = __ldg(k2i + ((h >> (2 * i)) & Q)), b = __ldg(k2i + ((hr >> (2 * i)) & Q));
-            o0[i] = a; o1[i] = b;
+            if (!ktable) { o0[i] = a; o1[i] = b; }
             gathered += (a >= 0) + (b >= 0);
         }
     }
@@ -160,6 +162,9 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
            const uint8_t* __restrict__ segok, uint32_t list0, uint32_t n_lists, uint32_t S, uint32_t F, uint32_t max_cand,
            uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt, unsigned long long* __restrict__ stats) {
     constexpr int B = (NQ >= 8) ? 1 : (8 / NQ);           // samples in flight per lane while no tile can be dead yet
+    // One row per sample (k-mer row table): a tile is practically never dead after exactly T samples (that needs all
+    // 4096 buckets to miss every one of them), so the (T+1)-th row is requested together with the first T.
+    constexpr uint32_t EXTRA = (NQ == 1) ? 1u : 0u;
     extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * S*NQ row ids
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t list = list0 + blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand; lists [list0, n_lists)
@@ -183,19 +188,19 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
         // a bucket is out of the race once it has missed T samples: T = F, or best+1 once an earlier tile holds a
         // bucket that finished with `best` misses (only buckets attaining the minimum are reported)
         const uint32_t T = (best < F) ? best + 1u : F;
-        const uint32_t s_blind = (min(S, T) / B) * B;     // fewer than T samples seen: nothing can be out yet
+        const uint32_t blind = min(S, T + EXTRA);         // fewer than T samples seen: nothing can be out yet
         uint4 p[NP];
 #pragma unroll
         for (int i = 0; i < NP; i++) p[i] = ZERO;
         uint32_t s = 0;
-        for (; s < s_blind; s += B) nloads += vote_group<NQ, NP, B>(colp, Wp16, my_idx + s * NQ, active, p);
+        if constexpr (B >= 8) for (; s + 8 <= blind; s += 8) nloads += vote_group<NQ, NP, 8>(colp, Wp16, my_idx + s * NQ, active, p);
+        if constexpr (B >= 4) for (; s + 4 <= blind; s += 4) nloads += vote_group<NQ, NP, 4>(colp, Wp16, my_idx + s * NQ, active, p);
+        if constexpr (B >= 2) for (; s + 2 <= blind; s += 2) nloads += vote_group<NQ, NP, 2>(colp, Wp16, my_idx + s * NQ, active, p);
+        for (; s < blind; s++) nloads += vote_group<NQ, NP, 1>(colp, Wp16, my_idx + s * NQ, active, p);
         bool tile_alive = true;
         for (; s < S; s++) {
-            bool lane_alive = active;
-            if (s >= T) {
-                lane_alive = active && any4(below_f<NP>(p, T));
-                if (!__any_sync(0xFFFFFFFFu, lane_alive)) { tile_alive = false; break; }
-            }
+            const bool lane_alive = active && any4(below_f<NP>(p, T));
+            if (!__any_sync(0xFFFFFFFFu, lane_alive)) { tile_alive = false; break; }
             nloads += vote_group<NQ, NP, 1>(colp, Wp16, my_idx + s * NQ, lane_alive, p);
         }
         if (!tile_alive) continue;
@@ -262,9 +267,10 @@ __global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const ui
 
 template <int NQ>
 cudaError_t launch_vote_np(bm_ctx* c, const bm_params* p, uint32_t NP, uint32_t list0, uint32_t n_lists, uint32_t blocks, size_t smem) {
+    const uint4* rows = c->use_ktable ? c->d_krows.as<uint4>() : c->d_rows.as<uint4>();
 #define BM_VOTE(NPv)                                                                                               \
     k_map_vote<NQ, NPv><<<blocks, kWarpsPerCta * 32, smem, c->stream>>>(                                           \
-        c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), list0, n_lists, \
+        rows, c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), list0, n_lists, \
         p->mapper_samples, p->mapper_fault, p->max_candidates, c->d_cand_fixed.as<uint32_t>(),                     \
         c->d_cand_cnt.as<uint32_t>(), c->d_stats.as<unsigned long long>())
     if (NP == 3) BM_VOTE(3); else if (NP == 4) BM_VOTE(4); else BM_VOTE(6);
@@ -328,6 +334,8 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
     c->have_map = false; c->have_locs = false; c->have_aln = false;
     int r = bm_internal_index_prepare(c, p->distinguishability);
     if (r) return r;
+    r = bm_internal_kmer_table_prepare(c, p->k);          // decides c->use_ktable for this call
+    if (r) return r;
     const size_t n_lists = 2 * (size_t)n_seg_cap;
     BM_CK(c, c->d_rowidx.ensure(n_lists * S * NQ * 4 + 16));
     BM_CK(c, c->d_segok.ensure((size_t)n_seg_cap + 16));
@@ -361,17 +369,18 @@ int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
             c->d_seq.as<uint8_t>(), c->d_qual.as<uint8_t>(), c->d_read_off.as<uint64_t>(),
             c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), seg0, seg1, msl,
             c->d_k2i.as<int32_t>(), c->d_distok.as<uint32_t>(), p->k, p->q, S, p->avg_base_quality * p->k, min_good,
-            c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
+            c->use_ktable ? 1u : 0u, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
     }
     BM_CK(c, cudaGetLastError());
     const uint32_t NP = (F <= 7) ? 3 : (F <= 15 ? 4 : 6);
-    size_t smem_v = (size_t)kWarpsPerCta * S * NQ * 4;
+    const uint32_t NQv = c->use_ktable ? 1u : NQ;         // rows gathered per sample
+    size_t smem_v = (size_t)kWarpsPerCta * S * NQv * 4;
     const uint32_t list0 = 2 * seg0, list1 = 2 * seg1;
     const uint32_t blocks_v = (list1 - list0 + kWarpsPerCta - 1) / kWarpsPerCta;
     cudaError_t e = cudaSuccess;
     {
         KScope ks(c, BM_K_MAP);
-        switch (NQ) {
+        switch (NQv) {
             case 1: e = launch_vote_np<1>(c, p, NP, list0, list1, blocks_v, smem_v); break;
             case 2: e = launch_vote_np<2>(c, p, NP, list0, list1, blocks_v, smem_v); break;
             case 3: e = launch_vote_np<3>(c, p, NP, list0, list1, blocks_v, smem_v); break;

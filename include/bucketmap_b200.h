@@ -78,7 +78,7 @@ typedef struct bm_aln {
 
 /* kernel ids for bm_kernel_stats */
 enum { BM_K_ROWPOP = 0, BM_K_INDEX = 1, BM_K_SAMPLE = 2, BM_K_MAP = 3, BM_K_LOCSAMPLE = 4, BM_K_LOCATE = 5,
-       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_COUNT = 9 };
+       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_COUNT = 10 };
 
 /* ---- context -------------------------------------------------------------------------------------------------- */
 int  bm_ctx_create(int device, bm_ctx** out);
@@ -107,6 +107,15 @@ int bm_index_load(bm_ctx* ctx, const int32_t* kmer_to_index, uint32_t q, const u
 int bm_index_download(bm_ctx* ctx, uint8_t* out_rows);
 /* distinguishability_filter::read (q_gram_mapper.h:171-187): zeros[] per row; *valid = the logged counter */
 int bm_index_zeros(bm_ctx* ctx, float distinguishability, uint32_t* zeros_out /* n_rows or NULL */, uint32_t* valid);
+/* k-mer row table (no reference counterpart: a B200 memory-layout choice).  For every possible query k-mer x the
+ * bitset q_gram_mapper::query builds per sample (q_gram_mapper.h:399-407: the AND of the rows of x's indexed q-grams)
+ * is precomputed on the device, 4^k rows of Wp bytes (54.8 GB for k=12 on the 1.7 Gbp reference), so that the mapper
+ * gathers one row per sample instead of k-q+1.  It is derived from the resident .qgram matrix at the first mapper call
+ * for a given k; index files are unchanged and results are identical.  mode 1 (default): build it when it fits in
+ * max_bytes (0 = half of the free device memory); mode 0: never (the mapper gathers the q-gram rows). */
+int bm_index_kmer_table(bm_ctx* ctx, int mode, uint64_t max_bytes);
+/* k the resident table was built for (0: none) and its size */
+int bm_index_kmer_table_info(bm_ctx* ctx, uint32_t* k, uint64_t* bytes);
 /* mapper::reset (q_gram_mapper.h:374-378) */
 int bm_index_free(bm_ctx* ctx);
 /* multi-GPU replication (no reference counterpart: the reference is one process).  bm_index_alloc sizes an empty

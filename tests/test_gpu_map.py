@@ -44,8 +44,10 @@ def test_index_load_roundtrip(oracle, bm, ctx):
     (dict(read_len=300, sub=0.01, indel=0.001), dict(s=20, e=0.6, k=14, b=10)),
     (dict(read_len=800, n_reads=500), dict()),           # long reads: 5 segments each
 ])
-def test_map_matches_oracle(oracle, bm, ctx, kw, pk):
+@pytest.mark.parametrize("ktable", [1, 0])   # 1: one k-mer row per sample (table derived on the device); 0: q-gram rows
+def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     d = dataset(**kw)
+    ctx.index_kmer_table(ktable)
     k2i, n_rows, rows = _index(oracle, d, d.frac)
     Po = oracle.params(d.L, **pk)
     P = bm.default_params(ctx.lib, d.L, **pk)
@@ -61,3 +63,6 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk):
     assert np.array_equal(gcand, cand)
     assert np.array_equal(gstats[:4], stats)
     assert stats[0] > 0.9 * len(segs[0]) or kw.get("read_len") == 800
+    tk, tbytes = ctx.index_kmer_table_info()
+    ctx.index_kmer_table(1)   # session-wide context: back to the default for the tests that follow
+    assert (tk, tbytes) == ((P.k, 4 ** P.k * ((((d.NB + 7) >> 3) + 63) & ~63)) if ktable else (0, 0))
