@@ -51,9 +51,10 @@ def parse():
     ap.add_argument("--reads", type=int, default=1_000_000, help="reads per GPU per step")
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--ktable", type=int, default=1, choices=[0, 1],
-                    help="1: mapper gathers one precomputed k-mer row per sample (table derived on the device when "
-                         "4^k rows fit); 0: gathers the k-q+1 q-gram rows per sample")
+    ap.add_argument("--ktable", type=int, default=1, choices=[0, 1, 8, 16, 32],
+                    help="1: mapper votes over the coarse k-mer table (derived on the device when 4^k rows fit; 16 "
+                         "buckets per coarse bit; 8/16/32 pick the group size); 0: gathers the k-q+1 q-gram rows per "
+                         "sample over the full row width")
     return ap.parse_args()
 
 
@@ -411,8 +412,9 @@ def main():
         "dtype": "u32 bitwise", "data": "synthetic",
         "config": {"workload": workload, "genome_bases": cfg["n_bases"], "bucket_len": cfg["L"], "NB": NB,
                    "row_bytes": W, "matrix_bytes": int(n_rows) * W, "kmer_table_bytes": int(ktable_bytes),
-                   "kmer_table": ("4^%d k-mer rows (AND of each k-mer's q-gram rows), derived on the device from the "
-                                  "matrix in %.1f ms; the mapper gathers 1 row per sample" % (ktable_k, ktable_ms))
+                   "kmer_table": ("4^%d coarse k-mer rows (AND of each k-mer's q-gram rows, OR-reduced over groups of "
+                                  "buckets), derived on the device from the matrix in %.1f ms; the mapper gathers 1 "
+                                  "coarse row per sample and recounts passing groups exactly" % (ktable_k, ktable_ms))
                                  if ktable_k else "off: the mapper gathers the k-q+1 q-gram rows per sample",
                    "reads_per_gpu_per_step": n_reads,
                    "read_len": cfg["read_len"], "flags": "-k 9 -l 12 -s 15 -e 0.4 -p 10 -f %g" % cfg["frac"],
@@ -424,7 +426,7 @@ def main():
                 "api": "bm_map_locate (pinned host buffers in, host records out; H2D chunks pipelined against the mapper inside the call)"},
         "gpu_launches": launches,
         "clocks": clk,
-        "roofline": {"kernel": "k_map_vote", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "roofline": {"kernel": "k_map_coarse" if ktable_k else "k_map_vote", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                      "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes,
                      "ms_per_launch": vote_ms / vote_n if vote_n else None,
@@ -434,7 +436,11 @@ def main():
                      "alg_bytes_definition": "16-B row loads issued by k_map_vote (counted in-kernel): %s of "
                                              "every 512-B column tile until all 4096 buckets of the tile have missed F "
                                              "samples; reference_cascade_bytes = all S*(k-q+1) rows of both strands x W"
-                                             % ("the one k-mer-table row per sample" if ktable_k else "the q-gram rows")},
+                                             % ("the one k-mer-table row per sample" if ktable_k else "the q-gram rows")
+                                             if not ktable_k else
+                                             "bytes k_map_coarse loads (counted in-kernel): S coarse k-mer rows per list "
+                                             "(row bytes in use, not the padded stride) + 4 B per .qgram word read for "
+                                             "the exact recount of passing groups"},
         "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
         "index_build_ms": index_ms, "kmer_table_build_ms": ktable_ms, "index_bcast_ms": bcast_ms, "setup_s": setup_s,
         "mapped": {"reads_with_candidate": int(mstats[0]), "cand_fwd": int(mstats[1]), "cand_rev": int(mstats[2])},

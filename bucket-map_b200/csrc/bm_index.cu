@@ -86,38 +86,57 @@ __global__ void k_distok(const int32_t* __restrict__ k2i, const uint32_t* __rest
     if ((threadIdx.x & 31) == 0 && g < n_codes) distok[g >> 5] = m;
 }
 
-// ---- K0b: k-mer row table ------------------------------------------------------------------------------------------------
-// krows[x] = AND over i in [0, k-q] of rows[kmer_to_index[(x >> 2i) & Q]] (un-indexed q-grams skipped), i.e. exactly the
-// bf_res that q_gram_mapper::query builds for sample hash x (q_gram_mapper.h:399-407) before filter->read().  With it the
-// mapper gathers one row per sample.  A CTA takes 64 consecutive k-mer codes -- they share all but the lowest three
-// base-4 digits, so the rows of the higher q-grams are re-read from L1 -- and one thread owns one 16-B column.
-// HBM traffic: one write of the table plus ~(1 + 1/4 + 1/16 + ...) reads of it; tens of ms for the 54.8 GB table.
+// ---- K0b: coarse k-mer table -----------------------------------------------------------------------------------------------
+// For k-mer code x: v = AND over i in [0, k-q] of rows[kmer_to_index[(x >> 2i) & Q]] (un-indexed q-grams skipped), i.e.
+// exactly the bf_res that q_gram_mapper::query builds for sample hash x (q_gram_mapper.h:399-407) before filter->read();
+// coarse bit g of row x = (32-bit word g of v != 0).  A CTA takes 64 consecutive k-mer codes -- they share all but the
+// lowest three base-4 digits, so the rows of the higher q-grams are re-read from L1 -- one thread owns one 16-B column
+// (4 coarse bits) and 8 neighbouring lanes assemble one coarse word.  Reads ~1.3x (4^k x Wp) bytes, writes 4^k x 128 B.
 __global__ void __launch_bounds__(256)
-k_kmer_rows(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ k2i, uint32_t NQ,
-            uint32_t Q, uint64_t n_kmers, uint4* __restrict__ krows) {
+k_kmer_coarse(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ k2i, uint32_t NQ,
+              uint32_t Q, uint64_t n_kmers, uint32_t* __restrict__ crows, uint32_t Wcs, uint32_t logg) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t nbits = 128u >> logg;          // coarse bits per 16-B column: 4 (G=32), 8 (G=16), 16 (G=8)
+    const uint32_t lpw = 32u / nbits;             // lanes that share one coarse word: 8, 4, 2
     for (uint64_t x0 = (uint64_t)blockIdx.x * 64; x0 < n_kmers; x0 += (uint64_t)gridDim.x * 64) {
         const uint32_t nx = (uint32_t)min((uint64_t)64, n_kmers - x0);
-        for (uint32_t c = threadIdx.x; c < Wp16; c += blockDim.x) {
+        for (uint32_t c0 = warp * 32; c0 < Wp16; c0 += 256) {
+            const uint32_t c = c0 + lane;
+            const bool act = c < Wp16;
             // a k-mer none of whose q-grams is indexed matches every REAL bucket; padding bits stay zero
             uint32_t w[4];
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 uint32_t b = c * 128u + 32u * i;
-                w[i] = (b >= NB) ? 0u : (NB - b >= 32u ? 0xFFFFFFFFu : ((1u << (NB - b)) - 1u));
+                w[i] = (!act || b >= NB) ? 0u : (NB - b >= 32u ? 0xFFFFFFFFu : ((1u << (NB - b)) - 1u));
             }
             const uint4 all = make_uint4(w[0], w[1], w[2], w[3]);
+            const uint32_t widx = c / lpw;
 #pragma unroll 4
             for (uint32_t j = 0; j < nx; j++) {
                 const uint32_t x = (uint32_t)(x0 + j);
                 uint4 v = all;
                 for (uint32_t i = 0; i < NQ; i++) {
                     const int32_t r = __ldg(k2i + ((x >> (2 * i)) & Q));
-                    if (r >= 0) {
+                    if (r >= 0 && act) {
                         const uint4 t = __ldg(rows + (size_t)r * Wp16 + c);
                         v.x &= t.x; v.y &= t.y; v.z &= t.z; v.w &= t.w;
                     }
                 }
-                __stcs(krows + (x0 + j) * Wp16 + c, v);
+                const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+                uint32_t nib = 0;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const uint32_t t = vw[i];
+                    if (logg == 5) nib |= (t ? 1u : 0u) << i;
+                    else if (logg == 4) nib |= ((t & 0xFFFFu ? 1u : 0u) | (t >> 16 ? 2u : 0u)) << (2 * i);
+                    else nib |= ((t & 0xFFu ? 1u : 0u) | (t & 0xFF00u ? 2u : 0u) | (t & 0xFF0000u ? 4u : 0u) | (t >> 24 ? 8u : 0u)) << (4 * i);
+                }
+                uint32_t cw = nib << (nbits * (lane & (lpw - 1)));
+                cw |= __shfl_xor_sync(0xFFFFFFFFu, cw, 1);
+                if (lpw > 2) cw |= __shfl_xor_sync(0xFFFFFFFFu, cw, 2);
+                if (lpw > 4) cw |= __shfl_xor_sync(0xFFFFFFFFu, cw, 4);
+                if ((lane & (lpw - 1)) == 0 && widx < Wcs) crows[(x0 + j) * Wcs + widx] = cw;
             }
         }
     }
@@ -171,19 +190,23 @@ int bm_internal_index_prepare(bm_ctx* c, float d) {
     return BM_OK;
 }
 
-// Builds (or re-uses) the k-mer row table for query seed length k; sets c->use_ktable.  Not built when k == q (the
-// q-gram rows already are the k-mer rows), when switched off, or when 4^k rows do not fit the memory budget: the
-// mapper then gathers the k-q+1 q-gram rows per sample.  Both ways are CUDA paths with identical results.
+// Builds (or re-uses) the coarse k-mer table for query seed length k; sets c->use_ktable.  Not built when switched off
+// or when 4^k rows do not fit the memory budget: the mapper then gathers the k-q+1 q-gram rows per sample over the full
+// row width.  Both ways are CUDA paths with identical results.
 int bm_internal_kmer_table_prepare(bm_ctx* c, uint32_t k) {
     c->use_ktable = false;
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "no index resident (bm_index_build / bm_index_load first)");
-    if (c->ktable_mode == 0 || k <= c->q || k < 3 || k > 15 || c->n_rows == 0) {
+    if (c->ktable_mode == 0 || k < c->q || k < 3 || k > 15 || c->n_rows == 0) {
         if (c->ktable_mode == 0 && c->d_krows.p) { c->d_krows.release(); c->krows_k = 0; }
         return BM_OK;
     }
-    if (c->krows_k == k && c->d_krows.p) { c->use_ktable = true; return BM_OK; }
+    if (c->krows_k == k && c->krows_logg == c->ktable_logg && c->d_krows.p) { c->use_ktable = true; return BM_OK; }
     const uint64_t n_kmers = 1ull << (2 * k);
-    const uint64_t bytes = n_kmers * c->Wp;
+    const uint32_t Wp32 = c->Wp / 4;
+    const uint32_t logg = c->ktable_logg;                          // buckets per coarse bit = 1 << logg
+    c->Wc = ((Wp32 << (5 - logg)) + 31) / 32;
+    c->Wcs = (c->Wc + 15u) & ~15u;
+    const uint64_t bytes = n_kmers * c->Wcs * 4;
     c->d_krows.release(); c->krows_k = 0;
     uint64_t budget = c->ktable_max_bytes;
     if (!budget) {
@@ -194,15 +217,17 @@ int bm_internal_kmer_table_prepare(bm_ctx* c, uint32_t k) {
     if (bytes > budget) return BM_OK;
     cudaError_t e = c->d_krows.ensure_exact(bytes);
     if (e != cudaSuccess) { cudaGetLastError(); return BM_OK; }   // does not fit after all: q-gram gather
+    BM_CK(c, cudaMemsetAsync(c->d_krows.p, 0, bytes, c->stream));   // stride padding words
     {
         KScope ks(c, BM_K_KTABLE);
         const uint64_t want = (n_kmers + 63) / 64;
         const uint32_t blocks = (uint32_t)(want < (uint64_t)c->sm_count * 64 ? want : (uint64_t)c->sm_count * 64);
-        k_kmer_rows<<<blocks, 256, 0, c->stream>>>(c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_k2i.as<int32_t>(),
-                                                   k - c->q + 1, (1u << (2 * c->q)) - 1u, n_kmers, c->d_krows.as<uint4>());
+        k_kmer_coarse<<<blocks, 256, 0, c->stream>>>(c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_k2i.as<int32_t>(),
+                                                     k - c->q + 1, (c->q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * c->q)) - 1u),
+                                                     n_kmers, c->d_krows.as<uint32_t>(), c->Wcs, logg);
     }
     BM_CK(c, cudaGetLastError());
-    c->krows_k = k; c->use_ktable = true;
+    c->krows_k = k; c->krows_logg = logg; c->use_ktable = true;
     return BM_OK;
 }
 
@@ -210,8 +235,10 @@ extern "C" {
 
 int bm_index_kmer_table(bm_ctx* c, int mode, uint64_t max_bytes) {
     if (!c) return BM_E_ARG;
-    if (mode != 0 && mode != 1) BM_FAIL(c, BM_E_ARG, "bm_index_kmer_table: mode must be 0 (off) or 1 (when it fits)");
-    c->ktable_mode = mode; c->ktable_max_bytes = max_bytes;
+    if (mode != 0 && mode != 1 && mode != 8 && mode != 16 && mode != 32)
+        BM_FAIL(c, BM_E_ARG, "bm_index_kmer_table: mode must be 0 (off), 1 (when it fits) or a group size 8/16/32");
+    c->ktable_logg = (mode == 8) ? 3 : (mode == 32) ? 5 : 4;
+    c->ktable_mode = mode ? 1 : 0; c->ktable_max_bytes = max_bytes;
     if (mode == 0 || (max_bytes && c->d_krows.cap > max_bytes)) { cudaSetDevice(c->device); c->d_krows.release(); c->krows_k = 0; }
     return BM_OK;
 }
@@ -219,7 +246,7 @@ int bm_index_kmer_table(bm_ctx* c, int mode, uint64_t max_bytes) {
 int bm_index_kmer_table_info(bm_ctx* c, uint32_t* k, uint64_t* bytes) {
     if (!c) return BM_E_ARG;
     if (k) *k = (c->d_krows.p ? c->krows_k : 0);
-    if (bytes) *bytes = (c->d_krows.p && c->krows_k) ? ((1ull << (2 * c->krows_k)) * c->Wp) : 0;
+    if (bytes) *bytes = (c->d_krows.p && c->krows_k) ? ((1ull << (2 * c->krows_k)) * c->Wcs * 4) : 0;
     return BM_OK;
 }
 

@@ -76,11 +76,15 @@ struct bm_ctx {
     float zeros_for_d = -1.f;     // distinguishability the distok bitmap was built for (<0: none)
     uint32_t dist_threshold = 0, dist_valid = 0;
 
-    // k-mer row table: row x = AND of the indexed q-gram rows of query k-mer x (4^k rows of Wp bytes), derived on the
-    // device from d_rows so that the mapper gathers ONE row per sample instead of k-q+1.  Sized for 180 GB of HBM:
-    // 4^12 x 3,264 B = 54.8 GB on the 1.7 Gbp reference.  krows_k = the k it was built for (0: not resident).
+    // coarse k-mer table: for every possible query k-mer x, the bitset q_gram_mapper::query builds for a sample with hash
+    // x (AND of the rows of x's indexed q-grams), OR-reduced over groups of 32 buckets: coarse bit g of row x = "some
+    // bucket of 32g..32g+31 contains all q-grams of x".  4^k rows of Wcs 32-bit words (Wcs*4 = 128 B on the 1.7 Gbp
+    // reference: ONE cache line per sample, 2.1 GB in all), derived on the device from d_rows.  A bucket with < F missed
+    // samples lies in a group with < F coarse misses, so the mapper counts coarse misses first and computes exact miss
+    // counts only for the (rare) groups that pass.  krows_k = the k it was built for (0: not resident).
     DevBuf d_krows;
-    uint32_t krows_k = 0;
+    uint32_t krows_k = 0, Wc = 0, Wcs = 0;   // coarse words in use per row / row stride in words (64-B multiple)
+    uint32_t ktable_logg = 4, krows_logg = 0;   // log2 of the buckets per coarse bit: wanted / of the resident table
     int ktable_mode = 1;          // 0 never, 1 when it fits (bm_index_kmer_table)
     uint64_t ktable_max_bytes = 0;   // 0: half of the free device memory at build time
     bool use_ktable = false;      // decided by bm_internal_kmer_table_prepare for the current mapper call

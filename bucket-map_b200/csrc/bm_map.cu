@@ -248,6 +248,123 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
     if (lane == 0) atomicAdd(stats + 4, (unsigned long long)nloads * 16ull);   // bytes actually gathered
 }
 
+// ---- K2c: coarse vote over the k-mer table + exact count of the groups that pass ---------------------------------------------
+// One warp per (segment, strand).  Lane w holds coarse word w of the row (32 groups = 1,024 buckets); the S sample rows
+// are S independent, fully coalesced 4-B loads per lane (one 128-B line per sample on the 1.7 Gbp reference), all in
+// flight together.  The same bit-sliced saturating counter as K2 counts COARSE misses per group; a bucket with < F
+// misses lies in a group with < F coarse misses (a coarse hit is the OR of its buckets' hits), so only passing groups
+// can hold a reportable bucket.  For those the exact per-bucket miss counts come from the .qgram matrix itself: lane s
+// ANDs the k-q+1 32-bit words of sample s (q_gram_mapper.h:399-407), 32 ballots transpose them into one count per lane.
+// Reported set, order and the > max_candidates rule are those of best_results() / query_sequence (:90-102, :471-476).
+// up to BB samples at once: every load is issued before the first counter update waits for one
+template <int NP, int BB>
+__device__ __forceinline__ void coarse_group(const uint32_t* __restrict__ colp, uint32_t Wcs, const int32_t* h, uint32_t n,
+                                             bool act, uint32_t (&p)[NP]) {
+    uint32_t v[BB];
+#pragma unroll
+    for (int b = 0; b < BB; b++) {
+        v[b] = 0xFFFFFFFFu;                                // b >= n: no sample, nothing missed
+        if (b < n) v[b] = act ? __ldg(colp + (size_t)(uint32_t)h[b] * Wcs) : 0u;
+    }
+#pragma unroll
+    for (int b = 0; b < BB; b++) {
+        uint32_t carry = ~v[b];                            // 1 = no bucket of the group holds this sample
+#pragma unroll
+        for (int i = 0; i < NP; i++) { uint32_t t = p[i] & carry; p[i] ^= carry; carry = t; }
+#pragma unroll
+        for (int i = 0; i < NP; i++) p[i] |= carry;        // saturate at 2^NP-1 (>= F by dispatch)
+    }
+}
+
+template <int NP>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_map_coarse(const uint32_t* __restrict__ crows, uint32_t Wcs, uint32_t Wc, uint32_t gshift, const uint32_t* __restrict__ rows32,
+             uint32_t Wp32, uint32_t NB, const int32_t* __restrict__ k2i, uint32_t NQ, uint32_t Q,
+             const int32_t* __restrict__ khash, const uint8_t* __restrict__ segok, uint32_t list0, uint32_t n_lists,
+             uint32_t S, uint32_t F, uint32_t max_cand, uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt,
+             unsigned long long* __restrict__ stats) {
+    extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * S sample hashes
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t list = list0 + blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand
+    if (list >= n_lists) return;
+    if (!segok[list >> 1]) {                              // q_gram_mapper.h:445-447: too few good k-mers
+        if (lane == 0) cand_cnt[list] = 0;
+        return;
+    }
+    int32_t* my_h = s_idx + (size_t)warp * S;
+    for (uint32_t t = lane; t < S; t += 32) my_h[t] = khash[(size_t)list * S + t];
+    __syncwarp();
+
+    uint32_t best = 0xFFFFFFFFu, count = 0, nfine = 0;
+    uint32_t* out = cand_fixed + (size_t)list * max_cand;
+    for (uint32_t w0 = 0; w0 < Wc; w0 += 32) {
+        const uint32_t w = w0 + lane;
+        const bool act = w < Wc;
+        const uint32_t* colp = crows + (act ? w : 0);
+        uint32_t p[NP];
+#pragma unroll
+        for (int i = 0; i < NP; i++) p[i] = 0u;
+        for (uint32_t s = 0; s < S; s += 16) coarse_group<NP, 16>(colp, Wcs, my_h + s, min(16u, S - s), act, p);
+        // groups with fewer than F coarse misses
+        uint32_t lt = 0u, eq = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = NP - 1; i >= 0; i--) {
+            if ((F >> i) & 1u) { lt |= eq & ~p[i]; eq &= p[i]; }
+            else eq &= ~p[i];
+        }
+        const uint32_t pass = act ? lt : 0u;
+        uint32_t any = __ballot_sync(0xFFFFFFFFu, pass != 0u);
+        while (any) {
+            const uint32_t l = __ffs(any) - 1; any &= any - 1;
+            uint32_t pw = __shfl_sync(0xFFFFFFFFu, pass, l);
+            uint32_t last_gi = 0xFFFFFFFFu;
+            while (pw) {
+                const uint32_t g = __ffs(pw) - 1; pw &= pw - 1;
+                // coarse bit -> the 32-bit word of a full row that holds its buckets (32*gi .. 32*gi+31); with 8 or 16
+                // buckets per coarse bit several bits share a word, which is evaluated once
+                const uint32_t gi = ((w0 + l) * 32 + g) >> gshift;
+                if (gi >= Wp32 || gi == last_gi) continue;
+                last_gi = gi;
+                const uint32_t b0 = gi * 32u;
+                const uint32_t vmask = (b0 >= NB) ? 0u : (NB - b0 >= 32u ? 0xFFFFFFFFu : ((1u << (NB - b0)) - 1u));
+                uint32_t hits = 0;                         // lane b: samples that hit bucket b0 + b
+                for (uint32_t sb = 0; sb < S; sb += 32) {
+                    const uint32_t si = sb + lane;
+                    uint32_t word = 0u;
+                    if (si < S) {
+                        const uint32_t h = (uint32_t)my_h[si];
+                        word = vmask;
+                        for (uint32_t i = 0; i < NQ; i++) {
+                            const int32_t r = __ldg(k2i + ((h >> (2 * i)) & Q));
+                            if (r >= 0) { word &= __ldg(rows32 + (size_t)r * Wp32 + gi); nfine++; }
+                        }
+                    }
+#pragma unroll
+                    for (uint32_t b = 0; b < 32; b++) {
+                        const uint32_t cnt = __popc(__ballot_sync(0xFFFFFFFFu, (word >> b) & 1u));
+                        if (lane == b) hits += cnt;
+                    }
+                }
+                const uint32_t miss = S - hits;
+                const uint32_t lvl = (b0 + lane < NB && miss < F) ? miss : 0xFFFFu;
+                const uint32_t tmin = __reduce_min_sync(0xFFFFFFFFu, lvl);
+                if (tmin >= F) continue;
+                if (tmin < best) { best = tmin; count = 0; }
+                if (tmin == best) {
+                    const uint32_t m = __ballot_sync(0xFFFFFFFFu, lvl == best);
+                    const uint32_t pos = count + __popc(m & ((1u << lane) - 1u));
+                    if (lvl == best && pos < max_cand) out[pos] = b0 + lane;   // ascending, like _Find_next
+                    count += __popc(m);
+                }
+            }
+        }
+    }
+    // :471-476: a list longer than the cap is emptied, not truncated
+    if (lane == 0) cand_cnt[list] = (best < F && count <= max_cand) ? count : 0u;
+    nfine = __reduce_add_sync(0xFFFFFFFFu, nfine);
+    if (lane == 0) atomicAdd(stats + 4, (unsigned long long)S * Wc * 4ull + (unsigned long long)nfine * 4ull);   // bytes gathered
+}
+
 // ---- compaction of the fixed-slot lists into cand_off / cand ---------------------------------------------------------------
 __global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const uint32_t* __restrict__ cand_cnt,
                                const uint32_t* __restrict__ cand_off, uint32_t n_lists, uint32_t max_cand,
@@ -267,7 +384,7 @@ __global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const ui
 
 template <int NQ>
 cudaError_t launch_vote_np(bm_ctx* c, const bm_params* p, uint32_t NP, uint32_t list0, uint32_t n_lists, uint32_t blocks, size_t smem) {
-    const uint4* rows = c->use_ktable ? c->d_krows.as<uint4>() : c->d_rows.as<uint4>();
+    const uint4* rows = c->d_rows.as<uint4>();
 #define BM_VOTE(NPv)                                                                                               \
     k_map_vote<NQ, NPv><<<blocks, kWarpsPerCta * 32, smem, c->stream>>>(                                           \
         rows, c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), list0, n_lists, \
@@ -378,7 +495,18 @@ int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     const uint32_t list0 = 2 * seg0, list1 = 2 * seg1;
     const uint32_t blocks_v = (list1 - list0 + kWarpsPerCta - 1) / kWarpsPerCta;
     cudaError_t e = cudaSuccess;
-    {
+    if (c->use_ktable) {
+        KScope ks(c, BM_K_MAP);
+        const uint32_t Q = (p->q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * p->q)) - 1u);
+#define BM_COARSE(NPv)                                                                                              \
+        k_map_coarse<NPv><<<blocks_v, kWarpsPerCta * 32, smem_v, c->stream>>>(                                      \
+            c->d_krows.as<uint32_t>(), c->Wcs, c->Wc, 5u - c->krows_logg, c->d_rows.as<uint32_t>(), c->Wp / 4, c->NB, c->d_k2i.as<int32_t>(), \
+            NQ, Q, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), list0, list1, S, F, p->max_candidates,      \
+            c->d_cand_fixed.as<uint32_t>(), c->d_cand_cnt.as<uint32_t>(), c->d_stats.as<unsigned long long>())
+        if (NP == 3) BM_COARSE(3); else if (NP == 4) BM_COARSE(4); else BM_COARSE(6);
+#undef BM_COARSE
+        e = cudaGetLastError();
+    } else {
         KScope ks(c, BM_K_MAP);
         switch (NQv) {
             case 1: e = launch_vote_np<1>(c, p, NP, list0, list1, blocks_v, smem_v); break;

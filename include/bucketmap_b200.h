@@ -107,12 +107,15 @@ int bm_index_load(bm_ctx* ctx, const int32_t* kmer_to_index, uint32_t q, const u
 int bm_index_download(bm_ctx* ctx, uint8_t* out_rows);
 /* distinguishability_filter::read (q_gram_mapper.h:171-187): zeros[] per row; *valid = the logged counter */
 int bm_index_zeros(bm_ctx* ctx, float distinguishability, uint32_t* zeros_out /* n_rows or NULL */, uint32_t* valid);
-/* k-mer row table (no reference counterpart: a B200 memory-layout choice).  For every possible query k-mer x the
+/* coarse k-mer table (no reference counterpart: a B200 memory-layout choice).  For every possible query k-mer x the
  * bitset q_gram_mapper::query builds per sample (q_gram_mapper.h:399-407: the AND of the rows of x's indexed q-grams)
- * is precomputed on the device, 4^k rows of Wp bytes (54.8 GB for k=12 on the 1.7 Gbp reference), so that the mapper
- * gathers one row per sample instead of k-q+1.  It is derived from the resident .qgram matrix at the first mapper call
- * for a given k; index files are unchanged and results are identical.  mode 1 (default): build it when it fits in
- * max_bytes (0 = half of the free device memory); mode 0: never (the mapper gathers the q-gram rows). */
+ * is precomputed on the device and OR-reduced over groups of G buckets: 4^k rows of NB/G bits (4^12 x 256 B = 4.3 GB
+ * for G=16 on the 1.7 Gbp reference).  The mapper counts missed samples per GROUP from one coarse row per sample (a
+ * bucket with < F misses lies in a group with < F coarse misses) and recounts the few passing groups exactly from the
+ * .qgram matrix.  The table is derived from the resident matrix at the first mapper call for a given k; index files are
+ * unchanged and results are identical.  mode 1 (default): build it when it fits in max_bytes (0 = half of the free
+ * device memory), G=16; mode 8/16/32: the same with that G; mode 0: never (the mapper gathers the k-q+1 q-gram rows of
+ * every sample over the full row width). */
 int bm_index_kmer_table(bm_ctx* ctx, int mode, uint64_t max_bytes);
 /* k the resident table was built for (0: none) and its size */
 int bm_index_kmer_table_info(bm_ctx* ctx, uint32_t* k, uint64_t* bytes);

@@ -44,7 +44,7 @@ def test_index_load_roundtrip(oracle, bm, ctx):
     (dict(read_len=300, sub=0.01, indel=0.001), dict(s=20, e=0.6, k=14, b=10)),
     (dict(read_len=800, n_reads=500), dict()),           # long reads: 5 segments each
 ])
-@pytest.mark.parametrize("ktable", [1, 0])   # 1: one k-mer row per sample (table derived on the device); 0: q-gram rows
+@pytest.mark.parametrize("ktable", [1, 0, 8, 32])   # 1: coarse k-mer table + exact recount of passing groups; 0: q-gram rows
 def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     d = dataset(**kw)
     ctx.index_kmer_table(ktable)
@@ -65,4 +65,7 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     assert stats[0] > 0.9 * len(segs[0]) or kw.get("read_len") == 800
     tk, tbytes = ctx.index_kmer_table_info()
     ctx.index_kmer_table(1)   # session-wide context: back to the default for the tests that follow
-    assert (tk, tbytes) == ((P.k, 4 ** P.k * ((((d.NB + 7) >> 3) + 63) & ~63)) if ktable else (0, 0))
+    wp = (((d.NB + 7) >> 3) + 63) & ~63                       # padded row bytes
+    group = 16 if ktable == 1 else ktable                      # buckets per coarse bit (default 16)
+    wcs = ((wp * 8 // max(group, 1) + 31) // 32 + 15) & ~15    # coarse row stride in 32-bit words
+    assert (tk, tbytes) == ((P.k, 4 ** P.k * wcs * 4) if ktable else (0, 0))
