@@ -142,6 +142,20 @@ k_kmer_coarse(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const 
     }
 }
 
+// the same bits indexed by the two q-bit planes of a q-gram as the fused mapper kernel reads them out of its ballot
+// words: index = (hi << q) | lo, bit t of lo / hi = low / high bit of the rank of base t (first base = bit 0)
+__global__ void k_distok_planes(const uint32_t* __restrict__ distok, uint32_t q, uint32_t n_codes, uint32_t* __restrict__ out) {
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_codes || !((distok[g >> 5] >> (g & 31)) & 1u)) return;
+    uint32_t lo = 0, hi = 0;
+    for (uint32_t t = 0; t < q; t++) {
+        uint32_t base = (g >> (2 * (q - 1 - t))) & 3u;
+        lo |= (base & 1u) << t; hi |= (base >> 1) << t;
+    }
+    uint32_t idx = (hi << q) | lo;
+    atomicOr(out + (idx >> 5), 1u << (idx & 31));
+}
+
 int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t NB) {
     if (q == 0 || q > 14) BM_FAIL(c, BM_E_LIMIT, "index seed length q must be in [1,14]");
     if (NB == 0) BM_FAIL(c, BM_E_ARG, "NB must be > 0");
@@ -159,6 +173,7 @@ int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32
     BM_CK(c, c->d_rows.ensure((size_t)n_rows * c->Wp + 64));
     BM_CK(c, c->d_zeros.ensure((size_t)(n_rows + 1) * 4));
     BM_CK(c, c->d_distok.ensure((size_t)((n_codes + 31) / 32) * 4 + 64));
+    BM_CK(c, c->d_distok_p.ensure((size_t)((n_codes + 31) / 32) * 4 + 64));
     return BM_OK;
 }
 
@@ -182,6 +197,9 @@ int bm_internal_index_prepare(bm_ctx* c, float d) {
         KScope ks(c, BM_K_AUX);
         k_distok<<<(n_codes + 255) / 256, 256, 0, c->stream>>>(c->d_k2i.as<int32_t>(), c->d_zeros.as<uint32_t>(), n_codes,
                                                                thr, c->d_distok.as<uint32_t>());
+        BM_CK(c, cudaMemsetAsync(c->d_distok_p.p, 0, (size_t)((n_codes + 31) / 32) * 4, c->stream));
+        k_distok_planes<<<(n_codes + 255) / 256, 256, 0, c->stream>>>(c->d_distok.as<uint32_t>(), c->q, n_codes,
+                                                                      c->d_distok_p.as<uint32_t>());
     }
     BM_CK(c, cudaGetLastError());
     BM_CK(c, cudaMemcpyAsync(&c->dist_valid, d_valid, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -358,7 +376,7 @@ int bm_index_free(bm_ctx* c) {
     if (!c) return BM_E_ARG;
     cudaSetDevice(c->device);
     c->d_krows.release();
-    c->d_rows.release(); c->d_zeros.release(); c->d_distok.release(); c->d_k2i.release(); c->d_stage.release();
+    c->d_rows.release(); c->d_zeros.release(); c->d_distok.release(); c->d_distok_p.release(); c->d_k2i.release(); c->d_stage.release();
     c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0; c->have_map = false;
     return BM_OK;
 }

@@ -70,7 +70,7 @@ struct bm_ctx {
     uint32_t n_emit = 0, NB = 0, max_blen = 0;
 
     // q-gram bit matrix, rows padded to Wp bytes (multiple of 64 B: whole DRAM bursts, 16-B aligned vector loads)
-    DevBuf d_rows, d_k2i, d_zeros, d_distok, d_stage;
+    DevBuf d_rows, d_k2i, d_zeros, d_distok, d_distok_p, d_stage;   // d_distok_p: distok in bit-plane order (K2f)
     uint32_t q = 0, n_rows = 0, W = 0, Wp = 0;
     bool have_index = false;
     float zeros_for_d = -1.f;     // distinguishability the distok bitmap was built for (<0: none)
@@ -88,6 +88,9 @@ struct bm_ctx {
     int ktable_mode = 1;          // 0 never, 1 when it fits (bm_index_kmer_table)
     uint64_t ktable_max_bytes = 0;   // 0: half of the free device memory at build time
     bool use_ktable = false;      // decided by bm_internal_kmer_table_prepare for the current mapper call
+    // locator samples written by the fused mapper kernel for the resident batch (0: none; else the (k, P, b) they
+    // were drawn with) -- bm_locate_device then skips K3a
+    uint32_t lsamp_k = 0, lsamp_P = 0, lsamp_b = 0;
 
     // read batch
     DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len, d_read_seg0;
@@ -167,6 +170,7 @@ int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* re
 int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uint32_t max_seg_len);
 int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len);
 int bm_internal_map_finish(bm_ctx* c, const bm_params* p);
+int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len);   // K2f
 int bm_internal_map_locate_serial(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
                                   const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off,
                                   bm_loc* locs, uint64_t loc_cap, uint64_t* stats);

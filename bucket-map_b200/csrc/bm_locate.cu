@@ -501,7 +501,9 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
     BM_CK(c, c->d_loc_off.ensure((size_t)(n_reads + 1) * 4));
     BM_CK(c, c->d_locs.ensure((size_t)(n_cand + 1) * sizeof(bm_loc)));
     BM_CK(c, cudaMemsetAsync(c->d_loc_cnt.p, 0, (size_t)(n_reads + 1) * 4, c->stream));
-    if (n_seg) {
+    // the fused mapper kernel has already drawn these samples when it ran with the same (k, P, b) on this batch
+    const bool have_samples = c->lsamp_k == k && c->lsamp_P == P && c->lsamp_b == p->avg_base_quality;
+    if (n_seg && !have_samples) {
         const uint32_t msl = c->max_seg_len ? c->max_seg_len : 1;
         size_t smem = (size_t)kSampWarps * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
         if (smem > 48 * 1024)

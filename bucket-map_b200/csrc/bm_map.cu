@@ -463,6 +463,13 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
     BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * 8, c->stream));
     c->map_max_cand = p->max_candidates;
     c->n_cand = 0;
+    c->lsamp_k = c->lsamp_P = c->lsamp_b = 0;
+    if (c->use_ktable && p->locator_samples && p->locator_samples <= 1024) {
+        // K2f also draws the locator's samples (same k-mers, quality filter only: bucket_locator.h:315-341)
+        BM_CK(c, c->d_lsamp_idx.ensure((size_t)n_seg_cap * p->locator_samples * 2 + 16));
+        BM_CK(c, c->d_lsamp_hash.ensure((size_t)n_seg_cap * p->locator_samples * 4 + 16));
+        c->lsamp_k = p->k; c->lsamp_P = p->locator_samples; c->lsamp_b = p->avg_base_quality;
+    }
     const uint32_t msl = max_seg_len ? max_seg_len : 1;
     size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
     if (smem_a > 48 * 1024)
@@ -473,6 +480,7 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
 // K2a + K2 over segments [seg0, seg1); everything they read must already be resident (or ordered before on c->stream)
 int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len) {
     if (seg1 <= seg0) return BM_OK;
+    if (c->use_ktable && p->k <= 16 && p->mapper_samples <= 256) return bm_internal_map_fused(c, p, seg0, seg1, max_seg_len);
     const uint32_t NQ = p->k - p->q + 1, S = p->mapper_samples, F = p->mapper_fault;
     // smallest G with !(G < 0.2*S), the comparison of q_gram_mapper.h:445 in double
     uint32_t min_good = 0;
