@@ -12,9 +12,10 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbucketmap_b200.so")
 
-K_ROWPOP, K_INDEX, K_SAMPLE, K_MAP, K_LOCSAMPLE, K_LOCATE, K_MERGE, K_ALIGN, K_AUX, K_KTABLE, K_COUNT = range(11)
+(K_ROWPOP, K_INDEX, K_SAMPLE, K_MAP, K_LOCSAMPLE, K_LOCATE, K_MERGE, K_ALIGN, K_AUX, K_KTABLE, K_GIDX, K_LOCSCAN,
+ K_COUNT) = range(13)
 KERNEL_NAMES = ["rowpop", "index_build", "map_sample", "map_vote", "loc_sample", "locate", "merge", "align", "aux",
-                "kmer_table"]
+                "kmer_table", "locator_index", "locate_scan"]
 
 
 class Params(C.Structure):
@@ -52,6 +53,7 @@ SIGNATURES = {
     "bm_index_kmer_table": (C.c_int, [_vp, C.c_int, C.c_uint64]),
     "bm_index_kmer_table_info": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
     "bm_index_free": (C.c_int, [_vp]),
+    "bm_locator_index": (C.c_int, [_vp, C.c_int]),
     "bm_index_alloc": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32]),
     "bm_index_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
     "bm_ref_device": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]),
@@ -181,6 +183,10 @@ class Context:
         k, n = C.c_uint32(), C.c_uint64()
         self._ck(self.lib.bm_index_kmer_table_info(self.h, C.byref(k), C.byref(n)), "bm_index_kmer_table_info")
         return k.value, n.value
+
+    def locator_index(self, mode):
+        """0: the locator scans each candidate bucket's text; 1 (default): genome k-mer position index when it fits."""
+        self._ck(self.lib.bm_locator_index(self.h, mode), "bm_locator_index")
 
     def index_free(self):
         self._ck(self.lib.bm_index_free(self.h), "bm_index_free")

@@ -42,7 +42,8 @@ void bm_ctx_destroy(bm_ctx* c) {
                       &c->d_cand, &c->d_stats, &c->d_scan_tmp, &c->d_lsamp_idx, &c->d_lsamp_hash, &c->d_cres_pos,
                       &c->d_cres_votes, &c->d_cseg, &c->d_loc_cnt, &c->d_loc_off, &c->d_locs, &c->d_locs2,
                       &c->d_loc_off2, &c->d_vote_scratch, &c->d_locs3, &c->d_loc_pool, &c->d_loc_flags, &c->d_read_seg0, &c->d_aln, &c->d_cigar_fixed, &c->d_cigar_cnt,
-                      &c->d_cigar_off, &c->d_cigar, &c->d_aln_scratch, &c->d_flush};
+                      &c->d_cigar_off, &c->d_cigar, &c->d_aln_scratch, &c->d_flush, &c->d_krows, &c->d_distok_p, &c->d_gidx_pos,
+                      &c->d_gidx_off, &c->d_loc_over};
     for (DevBuf* b : bufs) b->release();
     for (HostBuf* h : {&c->h_read_seg0, &c->h_seg_read, &c->h_seg_start, &c->h_seg_len, &c->h_off_rel}) h->release();
     for (auto e : c->chunk_ev) cudaEventDestroy(e);
@@ -74,12 +75,21 @@ void bm_params_default(bm_params* p, uint32_t bucket_len) {
     bm_params_derive(p, bucket_len, 300, 9, 12, 15, 0.5f, 25, 0.4f, 0.02f, 10, 40);
 }
 
+int bm_locator_index(bm_ctx* c, int mode) {
+    if (!c) return BM_E_ARG;
+    if (mode != 0 && mode != 1) BM_FAIL(c, BM_E_ARG, "bm_locator_index: mode must be 0 (off) or 1 (when it fits)");
+    c->gidx_mode = mode;
+    if (!mode) { cudaSetDevice(c->device); c->d_gidx_pos.release(); c->d_gidx_off.release(); c->gidx_k = 0; }
+    return BM_OK;
+}
+
 int bm_ref_upload(bm_ctx* c, const uint8_t* packed, uint64_t n_bases, const uint64_t* bstart, const uint32_t* blen,
                   uint32_t n_emit, uint32_t NB) {
     if (!c) return BM_E_ARG;
     if (!packed || (n_emit && (!bstart || !blen)) || n_emit > NB) BM_FAIL(c, BM_E_ARG, "bm_ref_upload: bad arguments");
     cudaSetDevice(c->device);
     uint64_t nbytes = (n_bases + 3) / 4;
+    c->d_gidx_pos.release(); c->d_gidx_off.release(); c->gidx_k = 0;          // the position index belongs to the old text
     BM_CK(c, c->d_packed.ensure(nbytes + 64));
     BM_CK(c, cudaMemsetAsync((uint8_t*)c->d_packed.p + nbytes, 0, 64, c->stream));   // kernels read whole words
     BM_CK(c, cudaMemcpyAsync(c->d_packed.p, packed, nbytes, cudaMemcpyHostToDevice, c->stream));

@@ -367,6 +367,7 @@ int bm_index_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
 int bm_ref_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
     if (!c) return BM_E_ARG;
     if (!c->d_packed.p) BM_FAIL(c, BM_E_ARG, "bm_ref_device: bm_ref_upload first");
+    c->d_gidx_pos.release(); c->d_gidx_off.release(); c->gidx_k = 0;   // the caller may overwrite the text
     if (dptr) *dptr = c->d_packed.p;
     if (bytes) *bytes = (c->n_bases + 3) / 4;
     return BM_OK;

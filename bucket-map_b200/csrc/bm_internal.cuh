@@ -92,6 +92,13 @@ struct bm_ctx {
     // were drawn with) -- bm_locate_device then skips K3a
     uint32_t lsamp_k = 0, lsamp_P = 0, lsamp_b = 0;
 
+    // genome k-mer position index for the locator (bm_locidx.cu): start positions of all k-mers of the reference sorted
+    // by (hash, position) + 4^k+1 run offsets; gidx_k = the k it was built for (0: not resident)
+    DevBuf d_gidx_pos, d_gidx_off;
+    uint32_t gidx_k = 0;
+    int gidx_mode = 1;            // 0 never, 1 when it fits (bm_locator_index)
+    bool use_gidx = false;
+
     // read batch
     DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len, d_read_seg0;
     HostBuf h_read_seg0, h_seg_read, h_seg_start, h_seg_len, h_off_rel;   // pinned; filled by bm_internal_build_segments
@@ -107,7 +114,7 @@ struct bm_ctx {
 
     // locator results
     DevBuf d_lsamp_idx, d_lsamp_hash, d_cres_pos, d_cres_votes, d_cseg, d_loc_cnt, d_loc_off, d_locs, d_locs2,
-           d_loc_off2, d_vote_scratch, d_locs3, d_loc_pool, d_loc_flags;
+           d_loc_off2, d_vote_scratch, d_locs3, d_loc_pool, d_loc_flags, d_loc_over;
     uint64_t n_locs = 0, n_locs_best = 0;
     bool have_locs = false, locs_filtered = false, n_locs_known = false;
 
@@ -162,6 +169,8 @@ struct KScope {
 
 int bm_internal_index_prepare(bm_ctx* ctx, float d);          // K0: zeros + distok bitmap for threshold d
 int bm_internal_kmer_table_prepare(bm_ctx* ctx, uint32_t k);  // K0b: k-mer row table for query seed length k (if it fits)
+int bm_internal_gidx_prepare(bm_ctx* ctx, uint32_t k);        // genome k-mer position index for seed length k (if it fits)
+int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* over_list, uint32_t* d_n_over, uint32_t* n_over);
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
 // reads: size the batch buffers (host tables + device), then append the segment table of reads [r0, r1)
 int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads);

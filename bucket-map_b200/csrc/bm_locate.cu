@@ -82,6 +82,12 @@ k_loc_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, 
     }
 }
 
+__global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n,
+                             uint32_t* __restrict__ dst) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
+}
+
 __global__ void k_iota(uint32_t* __restrict__ v, uint32_t n) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) v[i] = i;
@@ -516,9 +522,32 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
     }
     BM_CK(c, cudaGetLastError());
     if (n_cand) {
-        const uint32_t n = (uint32_t)n_cand;
-        BM_CK(c, c->d_cres_pos.ensure((size_t)n * 4));
-        BM_CK(c, c->d_cres_votes.ensure((size_t)n * 4));
+        const uint32_t n_all = (uint32_t)n_cand;
+        BM_CK(c, c->d_cres_pos.ensure((size_t)n_all * 4));
+        BM_CK(c, c->d_cres_votes.ensure((size_t)n_all * 4));
+        // K3i: occurrence search on the genome k-mer position index; what it cannot finish in its small vote arrays
+        // (repeats) is left in over_list for the bucket-scan kernel below
+        const uint32_t* keys_in = c->d_cand.as<uint32_t>();   // bucket of every candidate to scan
+        const uint32_t* vals_in = nullptr;                    // their candidate ids (nullptr: 0..n-1)
+        uint32_t n = n_all;
+        int ri = bm_internal_gidx_prepare(c, k);
+        if (ri) return ri;
+        if (c->use_gidx) {
+            BM_CK(c, c->d_loc_over.ensure((size_t)n_all * 8 + 64));
+            uint32_t* over_list = c->d_loc_over.as<uint32_t>();
+            uint32_t* over_bucket = over_list + n_all;
+            uint32_t* d_n_over = over_bucket + n_all;
+            uint32_t n_over = 0;
+            ri = bm_internal_locate_idx(c, p, n_all, over_list, d_n_over, &n_over);
+            if (ri) return ri;
+            n = n_over;
+            if (n) {
+                KScope ks(c, BM_K_AUX);
+                k_gather_u32<<<(n + 255) / 256, 256, 0, c->stream>>>(c->d_cand.as<uint32_t>(), over_list, n, over_bucket);
+                keys_in = over_bucket; vals_in = over_list;
+            }
+        }
+        if (n) {
         // scratch: [chunks (uint2 x n) | iota | sorted bucket | sorted cand | n_chunks]
         BM_CK(c, c->d_vote_scratch.ensure((size_t)n * 4 * 5 + 64));
         uint2* chunks = c->d_vote_scratch.as<uint2>();
@@ -530,7 +559,7 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
         int end_bit = 1;
         while (end_bit < 32 && (1ull << end_bit) <= (uint64_t)c->NB) end_bit++;
         size_t tmp = 0;
-        BM_CK(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp, c->d_cand.as<uint32_t>(), sbucket, iota, scand, (int)n, 0,
+        BM_CK(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp, keys_in, sbucket, iota, scand, (int)n, 0,
                                                  end_bit, c->stream));
         BM_CK(c, c->d_scan_tmp.ensure(tmp));
         const uint32_t CH = (kMaxQueries / P) < kMaxCH ? (kMaxQueries / P) : kMaxCH;
@@ -544,8 +573,8 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
         BM_CK(c, cudaMemsetAsync(pool_flags, 0, kPoolSlots * 4, c->stream));
         {
             KScope ks(c, BM_K_AUX, 2);
-            k_iota<<<(n + 255) / 256, 256, 0, c->stream>>>(iota, n);
-            BM_CK(c, cub::DeviceRadixSort::SortPairs(c->d_scan_tmp.p, tmp, c->d_cand.as<uint32_t>(), sbucket, iota, scand,
+            if (!vals_in) { k_iota<<<(n + 255) / 256, 256, 0, c->stream>>>(iota, n); vals_in = iota; }
+            BM_CK(c, cub::DeviceRadixSort::SortPairs(c->d_scan_tmp.p, tmp, keys_in, sbucket, vals_in, scand,
                                                      (int)n, 0, end_bit, c->stream));
             k_loc_chunks<<<(n + 255) / 256, 256, 0, c->stream>>>(sbucket, n, CH, chunks, n_chunks);
         }
@@ -561,12 +590,13 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
         a.hits_cap = hits_cap; a.dense_cap = dense_cap;
         a.res_pos = c->d_cres_pos.as<int32_t>(); a.res_votes = c->d_cres_votes.as<uint32_t>();
         {
-            KScope ks(c, BM_K_LOCATE);
+            KScope ks(c, BM_K_LOCSCAN);
             uint32_t grid = (uint32_t)c->sm_count * 4;
             if (grid > n) grid = n;
             k_locate<<<grid, kLocThreads, 0, c->stream>>>(a);
         }
         BM_CK(c, cudaGetLastError());
+        }
     }
     int r = 0;
     if (n_reads) {

@@ -27,7 +27,7 @@ struct FusedArgs {
     const uint32_t* seg_read; const uint32_t* seg_start; const uint32_t* seg_len;
     uint32_t seg0, n_seg, NC;                 // NC: plane/mask words per warp in shared memory
     const int32_t* k2i; const uint32_t* distok_p;
-    uint32_t k, q, NQ, S, minq, min_good;
+    uint32_t k, q, NQ, S, minq, bq, min_good;
     const uint2* crows; uint32_t Wcs2, Wc, gshift;
     const uint32_t* rows32; uint32_t Wp32, NB, F, max_cand;
     uint32_t* cand_fixed; uint32_t* cand_cnt; uint8_t* segok; unsigned long long* stats;
@@ -89,6 +89,18 @@ __device__ __forceinline__ uint32_t hash_from_planes(const uint32_t* lo, const u
     return (spread16(__brev(hw) >> (32 - k)) << 1) | spread16(__brev(lw) >> (32 - k));   // first base most significant
 }
 
+// 32x32 bit-matrix transpose across the warp: lane i holds row i (bit j = column j) and ends up with column i
+__device__ __forceinline__ uint32_t transpose32(uint32_t x, uint32_t lane) {
+    uint32_t m = 0x0000FFFFu;
+#pragma unroll
+    for (int j = 16; j; j >>= 1) {
+        const uint32_t y = __shfl_xor_sync(0xFFFFFFFFu, x, j);
+        x = (lane & j) ? ((x & ~m) | ((y >> j) & m)) : ((x & m) | ((y & m) << j));
+        m ^= m << (j >> 1);
+    }
+    return x;
+}
+
 template <int NP>
 __global__ void __launch_bounds__(kFW * 32)
 k_map_fused(const FusedArgs a) {
@@ -113,17 +125,15 @@ k_map_fused(const FusedArgs a) {
     // ---- 1. streaming pass ---------------------------------------------------------------------------------------------
     uint32_t lo1 = 0, hi1 = 0;                        // planes of chunk c-1
     uint32_t Dp = 0;                                  // q-gram distinguishability bits of chunk c-2
-    uint32_t Pi1 = 0, Pi2 = 0, q2 = 0, q1 = 0, tot2 = 0, tot1 = 0;   // inclusive phred prefix sums / own value / chunk totals
+    uint32_t q2 = 0, q1 = 0;                          // phred rank of this lane's position in chunks c-2, c-1
+    uint32_t mn2 = 0xFFFFFFFFu, mn1 = 0xFFFFFFFFu;    // lowest phred rank inside chunks c-2, c-1
     uint32_t GA = 0, GB = 0;
     for (uint32_t c = 0; c <= nbch + 1; c++) {
         const uint32_t i = c * 32 + lane;
         uint32_t r = 0, qv = 0;
         if (i < n) { r = bm_rank_dna4(a.seq[off + i]); qv = (uint32_t)a.qual[off + i] - 33u; }
         const uint32_t lo0 = __ballot_sync(0xFFFFFFFFu, r & 1u), hi0 = __ballot_sync(0xFFFFFFFFu, r & 2u);
-        uint32_t Pi0 = qv;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, Pi0, o); if (lane >= o) Pi0 += t; }
-        const uint32_t tot0 = __shfl_sync(0xFFFFFFFFu, Pi0, 31);
+        const uint32_t mn0 = __reduce_min_sync(0xFFFFFFFFu, (i < n) ? qv : 0xFFFFFFFFu);
         if (lane == 0) { lo[c] = lo0; hi[c] = hi0; }
         uint32_t Dc = 0;                               // ... of chunk c-1
         if (c >= 1) {                                  // q-grams starting in chunk c-1 (windows reach into chunk c)
@@ -134,16 +144,26 @@ k_map_fused(const FusedArgs a) {
         if (c >= 2 && c - 2 < nchunk) {                // k-mers starting in chunk c-2
             const uint32_t j = (c - 2) * 32 + lane;
             const bool dist = (__funnelshift_r(Dp, Dc, lane) & nqmask) != 0u;     // q_gram_mapper.h:189-196
-            const uint32_t e = lane + k - 1;
-            const uint32_t pa = __shfl_sync(0xFFFFFFFFu, Pi2, e & 31), pb = __shfl_sync(0xFFFFFFFFu, Pi1, e & 31);
-            const uint32_t qs = ((e < 32) ? pa : tot2 + pb) - (Pi2 - q2);         // views::kmer_quality window sum
-            const bool qok = j < nk && qs >= a.minq;
+            bool qok = j < nk;                         // views::kmer_quality window sum >= b*k (:437-442)
+            if (min(mn2, mn1) < a.bq) {                // else every base of both chunks has phred >= b: all windows pass
+                uint32_t Pi2 = q2, Pi1 = q1;           // inclusive prefix sums of the two chunks
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t t2 = __shfl_up_sync(0xFFFFFFFFu, Pi2, o), t1 = __shfl_up_sync(0xFFFFFFFFu, Pi1, o);
+                    if (lane >= o) { Pi2 += t2; Pi1 += t1; }
+                }
+                const uint32_t tot2 = __shfl_sync(0xFFFFFFFFu, Pi2, 31);
+                const uint32_t e = lane + k - 1;
+                const uint32_t pa = __shfl_sync(0xFFFFFFFFu, Pi2, e & 31), pb = __shfl_sync(0xFFFFFFFFu, Pi1, e & 31);
+                const uint32_t qs = ((e < 32) ? pa : tot2 + pb) - (Pi2 - q2);
+                qok = qok && qs >= a.minq;
+            }
             const uint32_t b = __ballot_sync(0xFFFFFFFFu, qok), m = __ballot_sync(0xFFFFFFFFu, qok && dist);   // :437-442
             if (lane == 0) { mA[c - 2] = m; mB[c - 2] = b; }
             GA += __popc(m); GB += __popc(b);
         }
         lo1 = lo0; hi1 = hi0; Dp = Dc;
-        Pi2 = Pi1; q2 = q1; tot2 = tot1; Pi1 = Pi0; q1 = qv; tot1 = tot0;
+        q2 = q1; q1 = qv; mn2 = mn1; mn1 = mn0;
     }
     __syncwarp();
 
@@ -248,11 +268,7 @@ k_map_fused(const FusedArgs a) {
                                     if (r >= 0) { word &= __ldg(a.rows32 + (size_t)r * a.Wp32 + gi); nfine++; }
                                 }
                             }
-#pragma unroll
-                            for (uint32_t b = 0; b < 32; b++) {
-                                const uint32_t cnt = __popc(__ballot_sync(0xFFFFFFFFu, (word >> b) & 1u));
-                                if (lane == b) hits += cnt;
-                            }
+                            hits += __popc(transpose32(word, lane));   // lane b: which of these 32 samples hit bucket b0+b
                         }
                         const uint32_t miss = S - hits;
                         const uint32_t lvl = (b0 + lane < a.NB && miss < a.F) ? miss : 0xFFFFu;
@@ -294,7 +310,7 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     a.seg_read = c->d_seg_read.as<uint32_t>(); a.seg_start = c->d_seg_start.as<uint32_t>(); a.seg_len = c->d_seg_len.as<uint32_t>();
     a.seg0 = seg0; a.n_seg = seg1; a.NC = (msl + 31) / 32 + 3;
     a.k2i = c->d_k2i.as<int32_t>(); a.distok_p = c->d_distok_p.as<uint32_t>();
-    a.k = p->k; a.q = p->q; a.NQ = NQ; a.S = S; a.minq = p->avg_base_quality * p->k; a.min_good = min_good;
+    a.k = p->k; a.q = p->q; a.NQ = NQ; a.S = S; a.minq = p->avg_base_quality * p->k; a.bq = p->avg_base_quality; a.min_good = min_good;
     a.crows = c->d_krows.as<uint2>(); a.Wcs2 = c->Wcs / 2; a.Wc = c->Wc; a.gshift = 5u - c->krows_logg;
     a.rows32 = c->d_rows.as<uint32_t>(); a.Wp32 = c->Wp / 4; a.NB = c->NB; a.F = p->mapper_fault; a.max_cand = p->max_candidates;
     a.cand_fixed = c->d_cand_fixed.as<uint32_t>(); a.cand_cnt = c->d_cand_cnt.as<uint32_t>(); a.segok = c->d_segok.as<uint8_t>();

@@ -78,7 +78,7 @@ typedef struct bm_aln {
 
 /* kernel ids for bm_kernel_stats */
 enum { BM_K_ROWPOP = 0, BM_K_INDEX = 1, BM_K_SAMPLE = 2, BM_K_MAP = 3, BM_K_LOCSAMPLE = 4, BM_K_LOCATE = 5,
-       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_COUNT = 10 };
+       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_GIDX = 10, BM_K_LOCSCAN = 11, BM_K_COUNT = 12 };
 
 /* ---- context -------------------------------------------------------------------------------------------------- */
 int  bm_ctx_create(int device, bm_ctx** out);
@@ -148,6 +148,13 @@ int bm_map_reads(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint
 
 /* ---- locator (replaces bucket_locator::_prepare_read_query/_create_kmer_index/_find_offset/_locate/
  *      _filter_best_locations, bucket_locator.h:162-405,613-705) ------------------------------------------------- */
+/* genome k-mer position index (no reference counterpart: a B200 memory-layout choice).  The reference rebuilds an
+ * unordered_multimap of a bucket's k-mers for every non-empty bucket (bucket_locator.h:162-177); here the start positions
+ * of ALL k-mers of the reference are kept sorted by (hash, position) (4 B per base + 4^k offsets; 6.9 GB for the 1.7 Gbp
+ * reference), built on the device at the first locator call for a given k, and a bucket's occurrences of a k-mer are a
+ * contiguous run found by binary search.  mode 1 (default): build it when it fits (k <= 14, < 2^32 bases); mode 0:
+ * never (the locator scans the text of each candidate bucket).  Results are identical. */
+int bm_locator_index(bm_ctx* ctx, int mode);
 /* K3a+K3 (+K3b when filter_best != 0) on the resident batch and the candidates of the last bm_map_device. */
 int bm_locate_device(bm_ctx* ctx, const bm_params* p, int filter_best);
 /* loc_off: n_reads+1; locs: capacity loc_cap (cand_off[2*n_seg] always suffices) */

@@ -20,8 +20,20 @@ CASES = [
 ]
 
 
+# (coarse k-mer table + fused mapper kernel, genome k-mer position index) on / off: every combination is a CUDA path
+@pytest.mark.parametrize("modes", [(1, 1), (0, 0), (1, 0), (0, 1)])
 @pytest.mark.parametrize("kw,pk", CASES)
-def test_locate_matches_oracle(oracle, bm, ctx, kw, pk):
+def test_locate_matches_oracle(oracle, bm, ctx, kw, pk, modes):
+    ctx.index_kmer_table(modes[0])
+    ctx.locator_index(modes[1])
+    try:
+        _locate_case(oracle, bm, ctx, kw, pk)
+    finally:
+        ctx.index_kmer_table(1)
+        ctx.locator_index(1)
+
+
+def _locate_case(oracle, bm, ctx, kw, pk):
     d = dataset(**kw)
     k2i, n_rows = oracle.fracminhash(d.q, X, Y, d.frac)
     rows = oracle.index_build(d.packed, d.b_start, d.b_len, d.NB, d.q, k2i, n_rows)
