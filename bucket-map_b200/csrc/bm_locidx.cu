@@ -21,7 +21,7 @@ namespace {
 
 constexpr uint32_t kEmptyHash = 0xFFFFFFFFu;
 constexpr int kIdxThreads = 128;
-constexpr uint32_t kVCi = 8;                    // vote-map entries per candidate kept in shared memory
+constexpr uint32_t kVCi = 8;                    // vote-map entries per candidate kept in shared memory (P <= 64 by bm_locate_device)
 
 // seqan3 views::kmer_hash(ungapped{k}) of the k-mer starting at base i of the 2-bit genome (k <= 16)
 __device__ __forceinline__ uint32_t genome_kmer(const uint8_t* __restrict__ packed, uint64_t i, uint32_t k) {
@@ -68,63 +68,89 @@ __device__ __forceinline__ uint32_t lb_pos(const uint32_t* __restrict__ pos, uin
     return lo;
 }
 
+// 16 lanes per candidate run the P occurrence searches side by side (two offsets, a binary search for the bucket start
+// and a short forward walk to the bucket end: every step is a dependent load, so the searches of one candidate must not
+// be serialised); lane 0 of the group then replays the vote loop over the runs in the reference's order.
+constexpr int kSub = 16;
+constexpr int kCandPerCta = kIdxThreads / kSub;
+constexpr uint32_t kMaxP = 64;
+
 __global__ void __launch_bounds__(kIdxThreads)
 k_locate_idx(const IdxArgs a) {
-    __shared__ int32_t s_vp[kVCi * kIdxThreads];     // [entry][thread]: conflict-free
-    __shared__ uint32_t s_vc[kVCi * kIdxThreads];
-    const uint32_t tid = threadIdx.x;
-    const uint32_t cand = blockIdx.x * kIdxThreads + tid;
-    if (cand >= a.n_cand) return;
-    const uint32_t bucket = a.cand[cand];
-    if (bucket >= a.n_emit) { a.res_pos[cand] = -1; a.res_votes[cand] = 0; return; }   // phantom bucket (SURVEY 8a note 4)
-    const uint32_t list = a.cseg[cand], seg = list >> 1;
-    const bool reverse = (list & 1u) != 0;
-    const uint32_t slen = a.seg_len[seg], k = a.k, P = a.P;
-    const uint64_t start = a.bstart[bucket];
-    const uint32_t len = a.blen[bucket];
-    const uint32_t npos = (len >= k) ? len - k + 1 : 0;
-    int32_t* vp = s_vp + tid; uint32_t* vc = s_vc + tid;
-#define VP(e) vp[(e) * kIdxThreads]
-#define VC(e) vc[(e) * kIdxThreads]
+    __shared__ uint32_t s_x0[kCandPerCta][kMaxP], s_x1[kCandPerCta][kMaxP], s_cur[kCandPerCta][kMaxP];
+    __shared__ int32_t s_vp[kCandPerCta][kVCi];
+    __shared__ uint32_t s_vc[kCandPerCta][kVCi];
+    const uint32_t tid = threadIdx.x, grp = tid / kSub, sub = tid % kSub;
+    const uint32_t cand = blockIdx.x * kCandPerCta + grp;
+    const bool valid = cand < a.n_cand;
+    const uint32_t k = a.k, P = a.P;
+    uint32_t bucket = 0, list = 0, seg = 0, slen = 0, npos = 0;
+    uint64_t start = 0;
+    bool reverse = false, phantom = false;
+    if (valid) {
+        bucket = a.cand[cand];
+        phantom = bucket >= a.n_emit;                                   // SURVEY 8a note 4
+        list = a.cseg[cand]; seg = list >> 1; reverse = (list & 1u) != 0;
+        slen = a.seg_len[seg];
+        if (!phantom) {
+            start = a.bstart[bucket];
+            const uint32_t len = a.blen[bucket];
+            npos = (len >= k) ? len - k + 1 : 0;
+        }
+    }
+    for (uint32_t i = sub; i < P; i += kSub) {                          // bucket_locator.h:233-243
+        uint32_t x0 = 0, x1 = 0, cur = 0;
+        if (valid && !phantom && npos) {
+            const uint32_t si = reverse ? P - 1 - i : i;
+            uint32_t h = a.shash[(size_t)seg * P + si];
+            if (h != kEmptyHash) {                                      // else: segment shorter than k
+                if (reverse) h = bm_revcomp_hash(h, k);
+                cur = a.sidx[(size_t)seg * P + si];
+                if (reverse) cur = slen - k - cur;
+                const uint32_t o0 = __ldg(a.off + h), o1 = __ldg(a.off + h + 1);
+                if (o0 != o1) {
+                    x0 = lb_pos(a.pos, o0, o1, start);
+                    x1 = x0;
+                    const uint64_t end = start + npos;
+                    while (x1 < o1 && (uint64_t)__ldg(a.pos + x1) < end) x1++;
+                }
+            }
+        }
+        s_x0[grp][i] = x0; s_x1[grp][i] = x1; s_cur[grp][i] = cur;
+    }
+    __syncwarp();
+    if (sub != 0 || !valid) return;
+    if (phantom) { a.res_pos[cand] = -1; a.res_votes[cand] = 0; return; }
+    int32_t* vp = s_vp[grp]; uint32_t* vc = s_vc[grp];
     uint32_t nv = 0;
     bool over = false;
-    for (uint32_t i = 0; i < P && !over; i++) {                       // bucket_locator.h:233-287
-        const uint32_t si = reverse ? P - 1 - i : i;
-        uint32_t h = a.shash[(size_t)seg * P + si];
-        if (h == kEmptyHash) continue;                                  // segment shorter than k
-        if (reverse) h = bm_revcomp_hash(h, k);                         // :239-243
-        uint32_t cur = a.sidx[(size_t)seg * P + si];
-        if (reverse) cur = slen - k - cur;
-        const uint32_t o0 = __ldg(a.off + h), o1 = __ldg(a.off + h + 1);
-        if (o0 == o1 || npos == 0) continue;
-        const uint32_t x0 = lb_pos(a.pos, o0, o1, start), x1 = lb_pos(a.pos, x0, o1, start + npos);
+    for (uint32_t i = 0; i < P && !over; i++) {                         // :244-287
+        const uint32_t x0 = s_x0[grp][i], x1 = s_x1[grp][i], cur = s_cur[grp][i];
         const bool first_mode = nv == 0;
         for (uint32_t x = x1; x > x0 && !over; x--) {                   // equal_range order: largest offset first
             const int32_t position = (int32_t)((uint32_t)((uint64_t)__ldg(a.pos + x - 1) - start) - cur);
             uint32_t e = 0;
             bool voted = false;
             if (first_mode) {
-                while (e < nv && VP(e) < position) e++;
-                if (e < nv && VP(e) == position) { VC(e)++; voted = true; }
+                while (e < nv && vp[e] < position) e++;
+                if (e < nv && vp[e] == position) { vc[e]++; voted = true; }
             } else {
-                while (e < nv && VP(e) < position - a.A) e++;
-                for (uint32_t f = e; f < nv && VP(f) <= position + a.A; f++) { VC(f)++; voted = true; }
-                while (e < nv && VP(e) < position) e++;                 // insertion point if nothing voted
+                while (e < nv && vp[e] < position - a.A) e++;
+                for (uint32_t f = e; f < nv && vp[f] <= position + a.A; f++) { vc[f]++; voted = true; }
+                while (e < nv && vp[e] < position) e++;                 // insertion point if nothing voted
             }
             if (!voted) {
                 if (nv == kVCi) { over = true; break; }
-                for (uint32_t t = nv; t > e; t--) { VP(t) = VP(t - 1); VC(t) = VC(t - 1); }
-                VP(e) = position; VC(e) = 1; nv++;
+                for (uint32_t t = nv; t > e; t--) { vp[t] = vp[t - 1]; vc[t] = vc[t - 1]; }
+                vp[e] = position; vc[e] = 1; nv++;
             }
         }
     }
     if (over) { a.over_list[atomicAdd(a.n_over, 1u)] = cand; return; }   // repeats: bucket-scan kernel with the dense table
     int32_t bp = -1; uint32_t bv = 0;
-    for (uint32_t e = 0; e < nv; e++) if (VC(e) > bv) { bv = VC(e); bp = VP(e); }   // ties: smallest key
+    for (uint32_t e = 0; e < nv; e++) if (vc[e] > bv) { bv = vc[e]; bp = vp[e]; }   // ties: smallest key
     if (nv && bv >= a.min_votes && bp >= 0) { a.res_pos[cand] = bp; a.res_votes[cand] = bv; }
     else { a.res_pos[cand] = -1; a.res_votes[cand] = 0; }
-#undef VP
-#undef VC
 }
 
 }  // namespace
@@ -202,7 +228,7 @@ int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* 
     BM_CK(c, cudaMemsetAsync(d_n_over, 0, 4, c->stream));
     {
         KScope ks(c, BM_K_LOCATE);
-        k_locate_idx<<<(n + kIdxThreads - 1) / kIdxThreads, kIdxThreads, 0, c->stream>>>(a);
+        k_locate_idx<<<(n + kCandPerCta - 1) / kCandPerCta, kIdxThreads, 0, c->stream>>>(a);
     }
     BM_CK(c, cudaGetLastError());
     BM_CK(c, cudaMemcpyAsync(n_over, d_n_over, 4, cudaMemcpyDeviceToHost, c->stream));
