@@ -1,15 +1,17 @@
 #!/usr/bin/env python
 """bench.py -- reads/sec mapped through the candidate-bucket hot path (BASELINE.json metric) on N B200s.
 
-A step is one pass of the hot path (mapper K2a+K2, locator K3a+K3+gather, best-location merge K3b) over one batch of
-synthetic reads.  Workload at any N: BASELINE config 1 of `configs` ("synthetic 1.7 Gbp reference, BUCKET_LEN=65536,
+A step is one pass of the hot path (mapper K2f = filter + sampler + coarse vote + exact recount, locator K3i + gather,
+best-location merge K3b) over one batch of synthetic reads.  Workload at any N: BASELINE config 1 of `configs` ("synthetic 1.7 Gbp reference, BUCKET_LEN=65536,
 1M x 300bp reads, 0.2% sub, 0.025% ins/del") per GPU -- reads are sharded, the index is replicated (weak scaling).
 
   value     whole-job reads/s with the read batch resident in HBM (CUDA events on the library's stream, max over ranks)
   e2e       the same through bm_map_locate() with pinned HOST buffers: H2D of bases/qualities/offsets and D2H of the
             location records inside the timed region
-  roofline  the mapper vote kernel (k_map_vote): algorithmic bytes = rows gathered x W, time = CUDA events around each
-            launch inside the timed region
+  roofline  the dominant kernel of the step, the fused mapper kernel (k_map_fused): algorithmic bytes = the bytes its
+            loads ask for, counted in the kernel; time = CUDA events around each launch inside the timed region.
+            roofline_qgram_path: the same for k_map_vote, the full-width q-gram row gather used when the coarse k-mer
+            table is off or does not fit (measured in the same run, outside the timed region)
   cpu_baseline / --impl reference: the CPU restatement of the reference (oracle/, "port") on the host cores, on a
             bounded sample of the same workload
 
@@ -51,6 +53,8 @@ def parse():
     ap.add_argument("--reads", type=int, default=1_000_000, help="reads per GPU per step")
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--lidx", type=int, default=1, choices=[0, 1],
+                    help="1: locator searches the genome k-mer position index; 0: scans each candidate bucket's text")
     ap.add_argument("--ktable", type=int, default=1, choices=[0, 1, 8, 16, 32],
                     help="1: mapper votes over the coarse k-mer table (derived on the device when 4^k rows fit; 16 "
                          "buckets per coarse bit; 8/16/32 pick the group size); 0: gathers the k-q+1 q-gram rows per "
@@ -278,6 +282,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = bm.Context(local)
     ctx.index_kmer_table(a.ktable)
+    ctx.locator_index(a.lidx)
     P = bm.default_params(ctx.lib, cfg["L"])
     q = 9
 
@@ -333,6 +338,7 @@ def main():
         step_resident()
     ctx.sync()
     ktable_ms = ctx.kernel_stats()["kmer_table"][0]     # one-off, inside the first (untimed) mapper call
+    lidx_ms = ctx.kernel_stats()["locator_index"][0]    # one-off, inside the first (untimed) locator call
     ktable_k, ktable_bytes = ctx.index_kmer_table_info()
     ctx.kernel_stats_reset()
     barrier()
@@ -398,6 +404,26 @@ def main():
 
     # ---- roofline of the dominant kernel -------------------------------------------------------------------------------
     vote_ms, vote_n = kst["map_vote"]
+
+    # the full-width q-gram gather (k_map_vote) on the same batch, outside the timed region: the mapper when the coarse
+    # table is off / does not fit, and the kernel the HBM roofline target of BASELINE.json was written for
+    alt = None
+    if ktable_k and rank == 0:
+        ctx.index_kmer_table(0)
+        ctx.map_device(P)                                # warm-up (frees the table)
+        ctx.kernel_stats_reset()
+        for _ in range(3):
+            ctx.map_device(P)
+        ctx.sync()
+        k2 = ctx.kernel_stats()
+        _, _, ms2 = ctx.map_download()
+        t_ms = k2["map_vote"][0] / max(1, k2["map_vote"][1])
+        alt = {"kernel": "k_map_vote", "bound": "hbm", "achieved": int(ms2[4]) / (t_ms * 1e-3) / 1e9,
+               "unit": "GB/s", "alg_bytes_per_launch": int(ms2[4]), "ms_per_launch": t_ms,
+               "map_sample_ms_per_launch": k2["map_sample"][0] / max(1, k2["map_sample"][1]),
+               "alg_bytes_definition": "16-B q-gram row loads issued by k_map_vote (counted in-kernel) until all 4096 "
+                                       "buckets of a 512-B column tile have missed F samples"}
+        ctx.index_kmer_table(a.ktable)
     rows_gathered = int(mstats[3])          # rows the reference's cascade ANDs (R of SURVEY 8d)
     alg_bytes = int(mstats[4])              # bytes of those rows K2's algorithm needs: 16-B loads it issued, counted
                                             # in the kernel (tiles whose buckets all reached F misses stop early)
@@ -421,12 +447,13 @@ def main():
                    "parallelism": f"reads sharded x{world}, index replicated",
                    "timing": "CUDA events on the library stream" if world == 1 else "wall clock between device-synchronised barriers (NCCL gather on its own stream), max over ranks",
                    "l2": "inputs larger than L2 (bit matrix %d MB vs 126 MB L2)" % (n_rows * W >> 20),
+                   "locator": "genome k-mer position index (K3i)" if a.lidx else "bucket text scan (K3)",
                    "step": "bm_map_device + bm_locate_device(filter_best=1)" + (" + NCCL gather" if world > 1 else "")},
         "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "api": "bm_map_locate (pinned host buffers in, host records out; H2D chunks pipelined against the mapper inside the call)"},
         "gpu_launches": launches,
         "clocks": clk,
-        "roofline": {"kernel": "k_map_coarse" if ktable_k else "k_map_vote", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "roofline": {"kernel": "k_map_fused" if ktable_k else "k_map_vote", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                      "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes,
                      "ms_per_launch": vote_ms / vote_n if vote_n else None,
@@ -438,11 +465,16 @@ def main():
                                              "samples; reference_cascade_bytes = all S*(k-q+1) rows of both strands x W"
                                              % ("the one k-mer-table row per sample" if ktable_k else "the q-gram rows")
                                              if not ktable_k else
-                                             "bytes k_map_coarse loads (counted in-kernel): S coarse k-mer rows per list "
-                                             "(row bytes in use, not the padded stride) + 4 B per .qgram word read for "
-                                             "the exact recount of passing groups"},
+                                             "bytes k_map_fused's loads ask for (counted in-kernel): the read's bases and "
+                                             "qualities + S coarse k-mer rows per strand (row bytes in use, not the "
+                                             "padded stride) + 4 B per .qgram word read for the exact recount of "
+                                             "passing groups; the kernel is issue-bound after these reductions (ncu: "
+                                             "IPC 2.2 of 4, DRAM 47 %), see DESIGN.md section 4",
+                     "reference_cascade_equivalent_gbs": (rows_gathered * W) / (vote_ms / vote_n * 1e-3) / 1e9 if vote_n else None},
+        "roofline_qgram_path": dict(alt, peak=peak, frac=alt["achieved"] / peak) if alt else None,
         "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
-        "index_build_ms": index_ms, "kmer_table_build_ms": ktable_ms, "index_bcast_ms": bcast_ms, "setup_s": setup_s,
+        "index_build_ms": index_ms, "kmer_table_build_ms": ktable_ms, "locator_index_build_ms": lidx_ms,
+        "index_bcast_ms": bcast_ms, "setup_s": setup_s,
         "mapped": {"reads_with_candidate": int(mstats[0]), "cand_fwd": int(mstats[1]), "cand_rev": int(mstats[2])},
     }
     if rank == 0 and world == 1 and not a.no_cpu:

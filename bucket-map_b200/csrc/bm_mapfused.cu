@@ -74,6 +74,17 @@ __device__ __forceinline__ uint32_t below(const uint32_t (&p)[NP], uint32_t F) {
     return (F >> NP) ? 0xFFFFFFFFu : lt;
 }
 
+// bm_rank_dna4 (seqan3 dna4 char_to_rank incl. IUPAC first-base convention) as two 32-bit tables of 2-bit entries
+// indexed by the low 5 bits of a letter: C,Y,S,B -> 1; G,K -> 2; T,U -> 3; everything else 0
+__device__ __forceinline__ uint32_t rank_dna4_lut(uint32_t c) {
+    // letters @ABCDEFGHIJKLMNO (0..15): B=2:1 C=3:1 G=7:2 K=11:2      PQRSTUVWXYZ (16..26): S=19:1 T=20:3 U=21:3 Y=25:1
+    constexpr uint32_t LO = (1u << 4) | (1u << 6) | (2u << 14) | (2u << 22);
+    constexpr uint32_t HI = (1u << 6) | (3u << 8) | (3u << 10) | (1u << 18);
+    const uint32_t t = (c & 0x10u) ? HI : LO;
+    const uint32_t r = (t >> ((c & 15u) * 2u)) & 3u;
+    return ((c & 0xC0u) == 0x40u) ? r : 0u;           // only 0x40..0x7F are letters (either case)
+}
+
 // zero bit between neighbouring bits of a 16-bit value
 __device__ __forceinline__ uint32_t spread16(uint32_t x) {
     x = (x | (x << 8)) & 0x00FF00FFu;
@@ -101,8 +112,8 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t x, uint32_t lane) {
     return x;
 }
 
-template <int NP>
-__global__ void __launch_bounds__(kFW * 32)
+template <int NP, int MINB>
+__global__ void __launch_bounds__(kFW * 32, MINB)
 k_map_fused(const FusedArgs a) {
     extern __shared__ uint32_t sm[];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -128,10 +139,14 @@ k_map_fused(const FusedArgs a) {
     uint32_t q2 = 0, q1 = 0;                          // phred rank of this lane's position in chunks c-2, c-1
     uint32_t mn2 = 0xFFFFFFFFu, mn1 = 0xFFFFFFFFu;    // lowest phred rank inside chunks c-2, c-1
     uint32_t GA = 0, GB = 0;
+    uint32_t nb = 'A', nq = 33;                       // bytes of the NEXT chunk, requested one step ahead
+    if (lane < n) { nb = a.seq[off + lane]; nq = a.qual[off + lane]; }
     for (uint32_t c = 0; c <= nbch + 1; c++) {
         const uint32_t i = c * 32 + lane;
-        uint32_t r = 0, qv = 0;
-        if (i < n) { r = bm_rank_dna4(a.seq[off + i]); qv = (uint32_t)a.qual[off + i] - 33u; }
+        const uint32_t cb = nb, cq = nq;
+        nb = 'A'; nq = 33;
+        if (i + 32 < n) { nb = a.seq[off + i + 32]; nq = a.qual[off + i + 32]; }
+        const uint32_t r = rank_dna4_lut(cb), qv = cq - 33u;   // positions >= n: rank 0, phred 0
         const uint32_t lo0 = __ballot_sync(0xFFFFFFFFu, r & 1u), hi0 = __ballot_sync(0xFFFFFFFFu, r & 2u);
         const uint32_t mn0 = __reduce_min_sync(0xFFFFFFFFu, (i < n) ? qv : 0xFFFFFFFFu);
         if (lane == 0) { lo[c] = lo0; hi[c] = hi0; }
@@ -321,13 +336,14 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     const uint32_t blocks = (seg1 - seg0 + kFW - 1) / kFW;
     const int NP = (S <= 15) ? 4 : (S <= 63 ? 6 : 9);
     KScope ks(c, BM_K_MAP);
-#define BM_FUSED(NPv)                                                                                              \
+#define BM_FUSED(NPv, MB)                                                                                          \
     do {                                                                                                           \
         if (smem > 48 * 1024)                                                                                      \
-            BM_CK(c, cudaFuncSetAttribute(k_map_fused<NPv>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        k_map_fused<NPv><<<blocks, kFW * 32, smem, c->stream>>>(a);                                                \
+            BM_CK(c, cudaFuncSetAttribute(k_map_fused<NPv, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        k_map_fused<NPv, MB><<<blocks, kFW * 32, smem, c->stream>>>(a);                                            \
     } while (0)
-    if (NP == 4) BM_FUSED(4); else if (NP == 6) BM_FUSED(6); else BM_FUSED(9);
+    // min CTAs per SM: 9 x 4 warps at 56 registers; forcing 12 (40 registers) spills and was measured no faster
+    if (NP == 4) BM_FUSED(4, 9); else if (NP == 6) BM_FUSED(6, 8); else BM_FUSED(9, 6);
 #undef BM_FUSED
     BM_CK(c, cudaGetLastError());
     return BM_OK;
