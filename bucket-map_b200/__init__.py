@@ -68,6 +68,7 @@ SIGNATURES = {
     "bm_locate_device_buffers": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_uint64)]),
     "bm_map_locate": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, C.c_uint32, C.c_int, _vp, _vp, C.c_uint64,
                                 _vp]),
+    "bm_pipeline_lanes": (C.c_int, [_vp, C.c_uint32]),
     "bm_align_device": (C.c_int, [_vp, C.POINTER(Params)]),
     "bm_align_download": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64)]),
     "bm_timer_start": (C.c_int, [_vp]),
@@ -183,6 +184,10 @@ class Context:
         k, n = C.c_uint32(), C.c_uint64()
         self._ck(self.lib.bm_index_kmer_table_info(self.h, C.byref(k), C.byref(n)), "bm_index_kmer_table_info")
         return k.value, n.value
+
+    def pipeline_lanes(self, min_reads):
+        """batches of >= min_reads reads go through bm_map_locate on two lanes (0 / 0xFFFFFFFF: never, the default)"""
+        self._ck(self.lib.bm_pipeline_lanes(self.h, min_reads), "bm_pipeline_lanes")
 
     def locator_index(self, mode):
         """0: the locator scans each candidate bucket's text; 1 (default): genome k-mer position index when it fits."""

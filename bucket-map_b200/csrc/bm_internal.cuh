@@ -126,9 +126,14 @@ struct bm_ctx {
     // L2 flush scratch
     DevBuf d_flush;
 
-    // bm_map_locate pipeline: copy stream + one event per chunk
+    // bm_map_locate pipeline: copy stream + one event per chunk; second lane (a child context viewing this one's index)
     cudaStream_t copy_stream = nullptr;
     std::vector<cudaEvent_t> chunk_ev;
+    bm_ctx* lane = nullptr;
+    cudaEvent_t lane_ev = nullptr;
+    bool lanes_off = false;       // true in the child lane itself
+    uint32_t lane_min_reads = 0xFFFFFFFFu;   // batches from this size on run on two lanes (bm_pipeline_lanes; default: never)
+    HostBuf h_lane_off;
 
     // measurement
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;

@@ -7,21 +7,66 @@
 // ~3/4 of the device time) therefore starts after the first chunk has landed and hides the rest of the 600 B/read
 // transfer.  The locator runs ONCE over the whole batch afterwards: its cost is per non-empty bucket (it streams each
 // bucket's text once for all candidates in it), so it must not be split.  Results do not depend on the chunking.
+//
+// Opt-in (bm_pipeline_lanes): a batch is cut in two halves that run through this pipeline on two LANES at once: the
+// context itself and a child context whose index buffers (bit matrix, coarse k-mer table, genome k-mer index, reference) are views of the
+// parent's, each with its own streams and batch buffers, the child driven by a second host thread.  The host->device
+// copies of both lanes share the link (the call is PCIe-bound), and the tail of a lane that cannot run under its own
+// copy -- compaction, locator, merge, result copy -- runs under the other lane's.  The second lane writes its records
+// behind the first lane's once that count is known.  Measured on C2 (1 M x 300 bp): 60.9 M reads/s against 63.8 M on one
+// lane -- the call is bound by the 608 MB host->device copy (13 ms at the 47 GB/s the chunked copies reach, 55 GB/s
+// link), and what the second lane hides of the 3.5 ms tail it loses again starting its copies late; hence off by default.
+#include <atomic>
+#include <chrono>
+#include <cstdlib>
+#include <thread>
+
 #include "bm_internal.cuh"
 
 namespace {
 constexpr uint32_t kPipeMinReads = 32768;      // below this the serial path is used
 constexpr uint32_t kChunkMin = 16384, kChunkMax = 131072;
+
+// what the second lane needs from the first: its record count (-1: not known yet, -2: the first lane failed)
+struct LaneLink {
+    std::atomic<long long> base{-1};
+    // the link is shared: lane 1's copies are ordered behind lane 0's last one, so that lane 0 has the whole link first
+    // and its tail then runs under lane 1's copies (0: not recorded yet, 1: h2d_done is recorded, -1: lane 0 failed)
+    std::atomic<int> h2d_state{0};
+    cudaEvent_t h2d_done = nullptr;
+};
+
+int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
+                 uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats,
+                 LaneLink* publish, LaneLink* wait_for, uint64_t* n_out);
+
+// the child lane sees the parent's index, tables and reference through views
+void lane_share_index(bm_ctx* l, bm_ctx* c) {
+    l->d_packed.view_of(c->d_packed); l->d_bstart.view_of(c->d_bstart); l->d_blen.view_of(c->d_blen);
+    l->n_bases = c->n_bases; l->n_emit = c->n_emit; l->NB = c->NB; l->max_blen = c->max_blen;
+    l->d_rows.view_of(c->d_rows); l->d_k2i.view_of(c->d_k2i); l->d_zeros.view_of(c->d_zeros);
+    l->d_distok.view_of(c->d_distok); l->d_distok_p.view_of(c->d_distok_p);
+    l->q = c->q; l->n_rows = c->n_rows; l->W = c->W; l->Wp = c->Wp; l->have_index = c->have_index;
+    l->zeros_for_d = c->zeros_for_d; l->dist_threshold = c->dist_threshold; l->dist_valid = c->dist_valid;
+    l->d_krows.view_of(c->d_krows); l->krows_k = c->krows_k; l->Wc = c->Wc; l->Wcs = c->Wcs;
+    l->ktable_logg = c->ktable_logg; l->krows_logg = c->krows_logg;
+    l->ktable_mode = c->d_krows.p ? 1 : 0;          // never build in the lane: use the parent's table or none
+    l->ktable_max_bytes = c->ktable_max_bytes;
+    l->d_gidx_pos.view_of(c->d_gidx_pos); l->d_gidx_off.view_of(c->d_gidx_off); l->gidx_k = c->gidx_k;
+    l->gidx_mode = (c->d_gidx_pos.p && c->d_gidx_off.p) ? 1 : 0;
+    l->ktiming = c->ktiming;
+}
 }  // namespace
 
-extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
-                             const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs,
-                             uint64_t loc_cap, uint64_t* stats) {
-    if (!c) return BM_E_ARG;
-    if (!p || !read_off || (n_reads && (!seq || !qual))) BM_FAIL(c, BM_E_ARG, "bm_map_locate: bad arguments");
-    if (n_reads < kPipeMinReads)
-        return bm_internal_map_locate_serial(c, p, seq, qual, read_off, n_reads, filter_best, loc_off, locs, loc_cap, stats);
+namespace {
+int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
+                 uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats,
+                 LaneLink* publish, LaneLink* wait_for, uint64_t* n_out) {
     cudaSetDevice(c->device);
+    static const bool trace = getenv("BM_PIPE_TRACE") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count(); };
+    double t_enq = 0, t_h2d = 0, t_fin = 0, t_loc = 0;
     if (!c->copy_stream) BM_CK(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
 
     uint32_t chunk = n_reads / 16;
@@ -43,6 +88,12 @@ extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, 
 
     const uint64_t base = read_off[0];
     uint8_t *d_seq = c->d_seq.as<uint8_t>(), *d_qual = c->d_qual.as<uint8_t>();
+    if (wait_for) {
+        int st;
+        while ((st = wait_for->h2d_state.load(std::memory_order_acquire)) == 0) std::this_thread::yield();
+        if (st < 0) BM_FAIL(c, BM_E_ARG, "bm_map_locate: the first lane failed");
+        BM_CK(c, cudaStreamWaitEvent(c->copy_stream, wait_for->h2d_done, 0));
+    }
     for (uint32_t j = 0; j < n_chunks; j++) {
         const uint32_t r0 = j * chunk, r1 = (r0 + chunk < n_reads) ? r0 + chunk : n_reads;
         const uint32_t s0 = c->n_seg;
@@ -71,11 +122,112 @@ extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, 
         r = bm_internal_map_range(c, p, s0, s1, msl);                               // K2a + K2 on this chunk
         if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; }
     }
+    t_enq = since();
+    if (trace) { cudaStreamSynchronize(c->copy_stream); t_h2d = since(); }
+    if (publish) {
+        BM_CK(c, cudaEventRecord(publish->h2d_done, c->copy_stream));
+        publish->h2d_state.store(1, std::memory_order_release);
+    }
     c->have_reads = true;
     r = bm_internal_map_finish(c, p);
     if (r) return r;
+    if (trace) { cudaStreamSynchronize(c->stream); t_fin = since(); }
     r = bm_locate_device(c, p, filter_best);                                       // K3a, K3, gather, K3b: whole batch
     if (r) return r;
+    if (trace) { cudaStreamSynchronize(c->stream); t_loc = since(); }
     if (stats) BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 8 * 8, cudaMemcpyDeviceToHost, c->stream));
-    return bm_locate_download(c, loc_off, locs, loc_cap);
+    if (!publish && !wait_for) {
+        r = bm_locate_download(c, loc_off, locs, loc_cap);
+        if (trace) fprintf(stderr, "[pipe] reads %u: enqueued %.2f  h2d done %.2f  map+finish %.2f  locate %.2f  download %.2f ms\n",
+                           n_reads, t_enq, t_h2d, t_fin, t_loc, since());
+        return r;
+    }
+    // one of two lanes: lane 0 announces how many records it has, lane 1 appends its own behind them
+    uint64_t n = 0;
+    r = bm_locate_count(c, &n);
+    if (r) return r;
+    if (n_out) *n_out = n;
+    if (publish) publish->base.store((long long)n, std::memory_order_release);
+    long long lbase = 0;
+    if (wait_for) {
+        while ((lbase = wait_for->base.load(std::memory_order_acquire)) == -1) std::this_thread::yield();
+        if (lbase < 0) BM_FAIL(c, BM_E_ARG, "bm_map_locate: the first lane failed");
+    }
+    if ((uint64_t)lbase + n > loc_cap) BM_FAIL(c, BM_E_ARG, "bm_map_locate: location buffer too small");
+    const void* off = c->locs_filtered ? c->d_loc_off2.p : c->d_loc_off.p;
+    const void* src = c->locs_filtered ? c->d_locs3.p : c->d_locs.p;
+    uint32_t* off_dst = loc_off;
+    if (wait_for) {                                 // offsets are rebased on the host: stage them
+        BM_CK(c, c->h_lane_off.ensure((size_t)(n_reads + 1) * 4));
+        off_dst = c->h_lane_off.as<uint32_t>();
+    }
+    BM_CK(c, cudaMemcpyAsync(off_dst, off, (size_t)(n_reads + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (n) BM_CK(c, cudaMemcpyAsync(locs + lbase, src, (size_t)n * sizeof(bm_loc), cudaMemcpyDeviceToHost, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    if (wait_for) for (uint32_t i = 1; i <= n_reads; i++) loc_off[i] = off_dst[i] + (uint32_t)lbase;   // [0] is lane 0's last
+    if (trace) fprintf(stderr, "[pipe] lane %d reads %u: enqueued %.2f  h2d done %.2f  map+finish %.2f  locate %.2f  download %.2f ms\n",
+                       wait_for ? 1 : 0, n_reads, t_enq, t_h2d, t_fin, t_loc, since());
+    return BM_OK;
+}
+}  // namespace
+
+extern "C" int bm_pipeline_lanes(bm_ctx* c, uint32_t min_reads) {
+    if (!c) return BM_E_ARG;
+    c->lane_min_reads = min_reads ? min_reads : 0xFFFFFFFFu;
+    return BM_OK;
+}
+
+extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
+                             const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs,
+                             uint64_t loc_cap, uint64_t* stats) {
+    if (!c) return BM_E_ARG;
+    if (!p || !read_off || (n_reads && (!seq || !qual))) BM_FAIL(c, BM_E_ARG, "bm_map_locate: bad arguments");
+    if (n_reads < kPipeMinReads)
+        return bm_internal_map_locate_serial(c, p, seq, qual, read_off, n_reads, filter_best, loc_off, locs, loc_cap, stats);
+    if (n_reads < c->lane_min_reads || n_reads < 2 * kPipeMinReads || !loc_off || !locs || c->lanes_off)
+        return pipeline_run(c, p, seq, qual, read_off, n_reads, filter_best, loc_off, locs, loc_cap, stats, nullptr, nullptr, nullptr);
+
+    // ---- two lanes ----
+    cudaSetDevice(c->device);
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_map_device: no index resident (the q-gram index is empty)");
+    // derived tables are built once, by the parent, before the lanes start (the child only ever views them)
+    int r = bm_internal_index_prepare(c, p->distinguishability);
+    if (r) return r;
+    if (p->k >= p->q && p->k <= 16) { r = bm_internal_kmer_table_prepare(c, p->k); if (r) return r; }
+    r = bm_internal_gidx_prepare(c, p->k);
+    if (r) return r;
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    if (!c->lane) {
+        r = bm_ctx_create(c->device, &c->lane);
+        if (r) BM_FAIL(c, r, "bm_map_locate: cannot create the second pipeline lane");
+        c->lane->lanes_off = true;
+    }
+    bm_ctx* l = c->lane;
+    lane_share_index(l, c);
+    const uint32_t h = n_reads / 2;
+    LaneLink link;
+    if (!c->lane_ev) BM_CK(c, cudaEventCreateWithFlags(&c->lane_ev, cudaEventDisableTiming));
+    link.h2d_done = c->lane_ev;
+    uint64_t st0[8] = {0}, st1[8] = {0}, n0 = 0, n1 = 0;
+    int r1 = BM_OK;
+    std::thread t([&] {
+        r1 = pipeline_run(l, p, seq, qual, read_off + h, n_reads - h, filter_best, loc_off + h, locs, loc_cap, st1, nullptr,
+                          &link, &n1);
+    });
+    int r0 = pipeline_run(c, p, seq, qual, read_off, h, filter_best, loc_off, locs, loc_cap, st0, &link, nullptr, &n0);
+    if (r0) { link.h2d_state.store(-1, std::memory_order_release); link.base.store(-2, std::memory_order_release); }
+    t.join();
+    // the lane's kernel launches and timings count as this context's
+    for (int k = 0; k < BM_K_COUNT; k++) {
+        double ms = 0; uint64_t ln = 0;
+        bm_kernel_stats(l, k, &ms, &ln);
+        c->kstat[k].ms += ms; c->kstat[k].launches += ln;
+    }
+    bm_kernel_stats_reset(l);
+    // no batch is resident as a whole after a two-lane call
+    c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
+    if (r0) return r0;
+    if (r1) { c->err = l->err; return r1; }
+    if (stats) for (int i = 0; i < 8; i++) stats[i] = st0[i] + st1[i];
+    return BM_OK;
 }

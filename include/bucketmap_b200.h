@@ -168,6 +168,11 @@ int bm_locate_device_buffers(bm_ctx* ctx, void** loc_off, void** locs, uint64_t*
 int bm_map_locate(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
                   const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs,
                   uint64_t loc_cap, uint64_t* stats);
+/* Opt-in: bm_map_locate cuts batches of at least min_reads reads (default and 0: never) in two halves that run on two
+ * pipeline lanes at once, so that the locator / merge / result copy of one half run under the host->device copy of the
+ * other.  Same records in the same order; after such a call no batch is resident in ctx.  Not faster on a PCIe-bound
+ * box (see bm_pipeline.cu), kept for hosts with a faster link. */
+int bm_pipeline_lanes(bm_ctx* ctx, uint32_t min_reads);
 
 /* ---- bucketmap_align verification (replaces seqan3::align_pairwise + cigar_from_alignment at
  *      bucket_locator.h:520-528,560-589) -------------------------------------------------------------------------- */

@@ -87,9 +87,18 @@ def test_locator_samples_match_oracle(oracle, bm, ctx):
     assert np.array_equal(g2, loff) and np.array_equal(gl, locs)
 
 
+@pytest.mark.parametrize("lanes", [0xFFFFFFFF, 65536])   # one pipeline lane / the batch cut in two lanes
 @pytest.mark.parametrize("filter_best", [True, False])
-def test_pipelined_map_locate_matches_oracle_and_serial_path(oracle, bm, ctx, filter_best):
-    """bm_map_locate cuts batches of >= 32768 reads into chunks over two lanes: same records, same order"""
+def test_pipelined_map_locate_matches_oracle_and_serial_path(oracle, bm, ctx, filter_best, lanes):
+    """bm_map_locate cuts batches of >= 32768 reads into chunks (and large ones over two lanes): same records, same order"""
+    ctx.pipeline_lanes(lanes)
+    try:
+        _pipelined_case(oracle, bm, ctx, filter_best)
+    finally:
+        ctx.pipeline_lanes(0)
+
+
+def _pipelined_case(oracle, bm, ctx, filter_best):
     d = dataset(n_bases=3_000_000, n_reads=70_001, read_len=150, repeats=20)
     k2i, n_rows = oracle.fracminhash(d.q, X, Y, d.frac)
     rows = oracle.index_build(d.packed, d.b_start, d.b_len, d.NB, d.q, k2i, n_rows)
