@@ -320,7 +320,9 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    gatherer = bmd.LocationGatherer() if world > 1 else None
+    # resident steps leave their results on the device (as at N=1): gathered records stay on rank 0's device; the
+    # end-to-end steps bring them to rank 0's host
+    gatherer = bmd.LocationGatherer(host_copy=False) if world > 1 else None
 
     def gather():
         """N>1: location records of every rank -> rank 0 (NCCL gather; pinned host copy on a side stream)"""
@@ -387,6 +389,8 @@ def main():
             return gatherer.gather(counts, lb)
         return None
 
+    if world > 1:
+        gatherer = bmd.LocationGatherer(host_copy=True)
     for _ in range(max(1, min(a.warmup, 3))):
         n_locs, _ = ctx.map_locate_into(P, hseq, hqual, hoff, ooff, olocs, True)
     barrier()
@@ -449,7 +453,7 @@ def main():
                    "reads_per_gpu_per_step": n_reads,
                    "read_len": cfg["read_len"], "flags": "-k 9 -l 12 -s 15 -e 0.4 -p 10 -f %g" % cfg["frac"],
                    "parallelism": f"reads sharded x{world}, index replicated",
-                   "timing": "CUDA events on the library stream" if world == 1 else "wall clock between device-synchronised barriers (NCCL gather on its own stream), max over ranks",
+                   "timing": "CUDA events on the library stream" if world == 1 else "wall clock between device-synchronised barriers (NCCL gather of the records to rank 0's device inside the step), max over ranks",
                    "l2": "inputs larger than L2 (bit matrix %d MB vs 126 MB L2)" % (n_rows * W >> 20),
                    "locator": "genome k-mer position index (K3i)" if a.lidx else "bucket text scan (K3)",
                    "step": "bm_map_device + bm_locate_device(filter_best=1)" + (" + NCCL gather" if world > 1 else "")},

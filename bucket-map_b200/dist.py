@@ -48,10 +48,11 @@ class LocationGatherer:
     [world, cap] receive buffer on dst (grown on demand), so a step costs one tiny all_gather of the record counts, one
     gather of the per-read counts, one gather of the records -- NCCL over NVLink when the tensors are on the GPU, gloo
     on CPU tensors in the tests -- then a device-side prefix sum / compaction and, on CUDA, an asynchronous copy of the
-    result into pinned host memory on a side stream (wait() before reading it)."""
+    result into pinned host memory on a side stream (wait() before reading it; host_copy=False leaves the gathered
+    records on dst's device)."""
 
-    def __init__(self, dst=0, group=None):
-        self.dst, self.group = dst, group
+    def __init__(self, dst=0, group=None, host_copy=True):
+        self.dst, self.group, self.host_copy = dst, group, host_copy
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.cap = 0
         self.send = self.recv = self.cnt_recv = None
@@ -91,6 +92,9 @@ class LocationGatherer:
         off = torch.zeros(self.cnt_recv.numel() + 1, dtype=torch.int64, device=device)
         torch.cumsum(self.cnt_recv.view(-1), 0, out=off[1:])
         locs = torch.cat([self.recv[r, :sizes[r]] for r in range(self.world)]) if total else self.recv[0, :0]
+        if device.type == "cuda" and not self.host_copy:
+            self.result = None                     # results stay on dst's device, like a single GPU's resident results
+            return (off, locs)
         if device.type == "cuda":
             if self.side is None:
                 self.side = torch.cuda.Stream(device)

@@ -21,9 +21,9 @@ def _flags(g):
     return out
 
 
-def _run(exe, args, cwd):
+def _run(exe, args, cwd, env=None):
     p = subprocess.run([os.path.join(BIN, exe)] + args, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
-                       timeout=600)
+                       timeout=600, env=dict(os.environ, **env) if env else None)
     assert p.returncode == 0, p.stderr[-3000:]
     return p.stderr
 
@@ -74,6 +74,17 @@ def test_cli_align_sam_matches_reference(tmp_path, case):
     fa, fq, _ = _index(g, d)
     _run("bucketmap_align", ["-i", "idx", "-q", fq, "-o", "out.sam", "-g", fa, "-L", str(g.L)] + _flags(g), d)
     _assert_sam_equal(open(tmp_path / "out.sam").read(), g.sam(True))
+
+
+@pytest.mark.parametrize("case", ["repeats", "lowqual", "long800"])
+def test_cli_table_free_kernels_give_the_same_sam(tmp_path, case):
+    """$BM_KMER_TABLE=0 / $BM_LOCATOR_INDEX=0: q-gram row gather and bucket text scan instead of the derived tables"""
+    g = Golden(case)
+    d = str(tmp_path)
+    fa, fq, _ = _index(g, d)
+    _run("bucketmap", ["-i", "idx", "-q", fq, "-o", "a.sam", "-g", fa, "-L", str(g.L)] + _flags(g), d,
+         env={"BM_KMER_TABLE": "0", "BM_LOCATOR_INDEX": "0"})
+    _assert_sam_equal(open(tmp_path / "a.sam").read(), g.sam(False))
 
 
 def test_cli_small_batches_give_the_same_sam(tmp_path):
