@@ -13,9 +13,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbucketmap_b200.so")
 
 (K_ROWPOP, K_INDEX, K_SAMPLE, K_MAP, K_LOCSAMPLE, K_LOCATE, K_MERGE, K_ALIGN, K_AUX, K_KTABLE, K_GIDX, K_LOCSCAN,
- K_COUNT) = range(13)
+ K_MAPOVER, K_COUNT) = range(14)
 KERNEL_NAMES = ["rowpop", "index_build", "map_sample", "map_vote", "loc_sample", "locate", "merge", "align", "aux",
-                "kmer_table", "locator_index", "locate_scan"]
+                "kmer_table", "locator_index", "locate_scan", "map_vote_handover"]
 
 
 class Params(C.Structure):
@@ -52,6 +52,7 @@ SIGNATURES = {
     "bm_index_zeros": (C.c_int, [_vp, C.c_float, _vp, C.POINTER(C.c_uint32)]),
     "bm_index_kmer_table": (C.c_int, [_vp, C.c_int, C.c_uint64]),
     "bm_index_kmer_table_info": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
+    "bm_map_handover": (C.c_int, [_vp, C.c_int]),
     "bm_index_free": (C.c_int, [_vp]),
     "bm_locator_index": (C.c_int, [_vp, C.c_int]),
     "bm_index_alloc": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32]),
@@ -184,6 +185,10 @@ class Context:
         k, n = C.c_uint32(), C.c_uint64()
         self._ck(self.lib.bm_index_kmer_table_info(self.h, C.byref(k), C.byref(n)), "bm_index_kmer_table_info")
         return k.value, n.value
+
+    def map_handover(self, max_groups):
+        """lists with more than max_groups passing coarse groups go to the full-width gather (-1: default)"""
+        self._ck(self.lib.bm_map_handover(self.h, max_groups), "bm_map_handover")
 
     def pipeline_lanes(self, min_reads):
         """batches of >= min_reads reads go through bm_map_locate on two lanes (0 / 0xFFFFFFFF: never, the default)"""

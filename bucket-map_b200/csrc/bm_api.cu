@@ -43,7 +43,7 @@ void bm_ctx_destroy(bm_ctx* c) {
                       &c->d_cres_votes, &c->d_cseg, &c->d_loc_cnt, &c->d_loc_off, &c->d_locs, &c->d_locs2,
                       &c->d_loc_off2, &c->d_vote_scratch, &c->d_locs3, &c->d_loc_pool, &c->d_loc_flags, &c->d_read_seg0, &c->d_aln, &c->d_cigar_fixed, &c->d_cigar_cnt,
                       &c->d_cigar_off, &c->d_cigar, &c->d_aln_scratch, &c->d_flush, &c->d_krows, &c->d_distok_p, &c->d_gidx_pos,
-                      &c->d_gidx_off, &c->d_loc_over};
+                      &c->d_gidx_off, &c->d_loc_over, &c->d_map_over};
     if (c->lane_ev) cudaEventDestroy(c->lane_ev);
     if (c->lane) { bm_ctx_destroy(c->lane); c->lane = nullptr; cudaSetDevice(c->device); }
     for (DevBuf* b : bufs) b->release();

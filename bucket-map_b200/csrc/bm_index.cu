@@ -183,8 +183,8 @@ int bm_internal_index_prepare(bm_ctx* c, float d) {
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "no index resident (bm_index_build / bm_index_load first)");
     if (c->zeros_for_d == d) return BM_OK;
     const uint32_t thr = (unsigned int)(d * c->NB);          // q_gram_mapper.h:163 (float * unsigned, truncated)
-    BM_CK(c, c->d_stats.ensure(64 * 8));
-    uint32_t* d_valid = c->d_stats.as<uint32_t>() + 100;     // scratch word well past the mapper's stats
+    BM_CK(c, c->d_stats.ensure(136 * 8));
+    uint32_t* d_valid = c->d_stats.as<uint32_t>() + 260;     // scratch word past the mapper's stats and counter slots
     BM_CK(c, cudaMemsetAsync(d_valid, 0, 4, c->stream));
     if (c->n_rows) {
         KScope ks(c, BM_K_ROWPOP);

@@ -107,6 +107,9 @@ struct bm_ctx {
     bool have_reads = false;
 
     // mapper results
+    DevBuf d_map_over;            // lists the fused mapper kernel hands to K2 (too many groups pass: repeats) + count
+    uint32_t map_over_cap = 0;
+    int map_max_pass = -1;        // hand-over threshold in passing groups (-1: max(16, n_groups/8); bm_map_handover)
     DevBuf d_rowidx, d_segok, d_cand_fixed, d_cand_cnt, d_cand_off, d_cand, d_stats, d_scan_tmp;
     uint32_t map_max_cand = 0;
     uint64_t n_cand = 0;          // total candidates of the last bm_map_device (valid after bm_map_finish)

@@ -157,18 +157,16 @@ __device__ __forceinline__ uint4 below_f(const uint4 (&p)[NP], uint32_t F) {
 // list that the reference's cascade touches, with identical results.  Only the buckets attaining the MINIMUM miss count
 // are reported, so once a finished tile holds a bucket with `best` misses the bar for later tiles drops to best+1.
 template <int NQ, int NP>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
-k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ rowidx,
-           const uint8_t* __restrict__ segok, uint32_t list0, uint32_t n_lists, uint32_t S, uint32_t F, uint32_t max_cand,
-           uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt, unsigned long long* __restrict__ stats) {
+__device__ __forceinline__ void vote_list(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB,
+                                          const int32_t* __restrict__ rowidx, const uint8_t* __restrict__ segok,
+                                          uint32_t list, uint32_t S, uint32_t F, uint32_t max_cand,
+                                          uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt,
+                                          unsigned long long* __restrict__ stats, int32_t* s_idx) {
     constexpr int B = (NQ >= 8) ? 1 : (8 / NQ);           // samples in flight per lane while no tile can be dead yet
     // One row per sample (k-mer row table): a tile is practically never dead after exactly T samples (that needs all
     // 4096 buckets to miss every one of them), so the (T+1)-th row is requested together with the first T.
     constexpr uint32_t EXTRA = (NQ == 1) ? 1u : 0u;
-    extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * S*NQ row ids
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t list = list0 + blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand; lists [list0, n_lists)
-    if (list >= n_lists) return;
     if (!segok[list >> 1]) {                              // q_gram_mapper.h:445-447: too few good k-mers
         if (lane == 0) cand_cnt[list] = 0;
         return;
@@ -248,121 +246,40 @@ k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int
     if (lane == 0) atomicAdd(stats + 4, (unsigned long long)nloads * 16ull);   // bytes actually gathered
 }
 
-// ---- K2c: coarse vote over the k-mer table + exact count of the groups that pass ---------------------------------------------
-// One warp per (segment, strand).  Lane w holds coarse word w of the row (32 groups = 1,024 buckets); the S sample rows
-// are S independent, fully coalesced 4-B loads per lane (one 128-B line per sample on the 1.7 Gbp reference), all in
-// flight together.  The same bit-sliced saturating counter as K2 counts COARSE misses per group; a bucket with < F
-// misses lies in a group with < F coarse misses (a coarse hit is the OR of its buckets' hits), so only passing groups
-// can hold a reportable bucket.  For those the exact per-bucket miss counts come from the .qgram matrix itself: lane s
-// ANDs the k-q+1 32-bit words of sample s (q_gram_mapper.h:399-407), 32 ballots transpose them into one count per lane.
-// Reported set, order and the > max_candidates rule are those of best_results() / query_sequence (:90-102, :471-476).
-// up to BB samples at once: every load is issued before the first counter update waits for one
-template <int NP, int BB>
-__device__ __forceinline__ void coarse_group(const uint32_t* __restrict__ colp, uint32_t Wcs, const int32_t* h, uint32_t n,
-                                             bool act, uint32_t (&p)[NP]) {
-    uint32_t v[BB];
-#pragma unroll
-    for (int b = 0; b < BB; b++) {
-        v[b] = 0xFFFFFFFFu;                                // b >= n: no sample, nothing missed
-        if (b < n) v[b] = act ? __ldg(colp + (size_t)(uint32_t)h[b] * Wcs) : 0u;
-    }
-#pragma unroll
-    for (int b = 0; b < BB; b++) {
-        uint32_t carry = ~v[b];                            // 1 = no bucket of the group holds this sample
-#pragma unroll
-        for (int i = 0; i < NP; i++) { uint32_t t = p[i] & carry; p[i] ^= carry; carry = t; }
-#pragma unroll
-        for (int i = 0; i < NP; i++) p[i] |= carry;        // saturate at 2^NP-1 (>= F by dispatch)
+// one warp per list of [list0, n_lists)
+template <int NQ, int NP>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_map_vote(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ rowidx,
+           const uint8_t* __restrict__ segok, uint32_t list0, uint32_t n_lists, uint32_t S, uint32_t F, uint32_t max_cand,
+           uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt, unsigned long long* __restrict__ stats) {
+    extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * S*NQ row ids
+    const uint32_t list = list0 + blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);   // = 2*segment + strand
+    if (list >= n_lists) return;
+    vote_list<NQ, NP>(rows, Wp16, NB, rowidx, segok, list, S, F, max_cand, cand_fixed, cand_cnt, stats, s_idx);
+}
+
+// the lists the fused kernel handed over (too many groups passed its coarse vote: repeats); fixed grid, the count is
+// read on the device so that no host round trip is needed
+template <int NQ, int NP>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_map_vote_lists(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ rowidx,
+                 const uint8_t* __restrict__ segok, const uint32_t* __restrict__ list_ids, const uint32_t* __restrict__ n_ids,
+                 uint32_t S, uint32_t F, uint32_t max_cand, uint32_t* __restrict__ cand_fixed,
+                 uint32_t* __restrict__ cand_cnt, unsigned long long* __restrict__ stats) {
+    extern __shared__ int32_t s_idx[];
+    const uint32_t n = *n_ids;
+    for (uint32_t i = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); i < n; i += gridDim.x * kWarpsPerCta) {
+        vote_list<NQ, NP>(rows, Wp16, NB, rowidx, segok, list_ids[i], S, F, max_cand, cand_fixed, cand_cnt, stats, s_idx);
+        __syncwarp();
     }
 }
 
-template <int NP>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
-k_map_coarse(const uint32_t* __restrict__ crows, uint32_t Wcs, uint32_t Wc, uint32_t gshift, const uint32_t* __restrict__ rows32,
-             uint32_t Wp32, uint32_t NB, const int32_t* __restrict__ k2i, uint32_t NQ, uint32_t Q,
-             const int32_t* __restrict__ khash, const uint8_t* __restrict__ segok, uint32_t list0, uint32_t n_lists,
-             uint32_t S, uint32_t F, uint32_t max_cand, uint32_t* __restrict__ cand_fixed, uint32_t* __restrict__ cand_cnt,
-             unsigned long long* __restrict__ stats) {
-    extern __shared__ int32_t s_idx[];                    // kWarpsPerCta * S sample hashes
-    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t list = list0 + blockIdx.x * kWarpsPerCta + warp;   // = 2*segment + strand
-    if (list >= n_lists) return;
-    if (!segok[list >> 1]) {                              // q_gram_mapper.h:445-447: too few good k-mers
-        if (lane == 0) cand_cnt[list] = 0;
-        return;
-    }
-    int32_t* my_h = s_idx + (size_t)warp * S;
-    for (uint32_t t = lane; t < S; t += 32) my_h[t] = khash[(size_t)list * S + t];
-    __syncwarp();
-
-    uint32_t best = 0xFFFFFFFFu, count = 0, nfine = 0;
-    uint32_t* out = cand_fixed + (size_t)list * max_cand;
-    for (uint32_t w0 = 0; w0 < Wc; w0 += 32) {
-        const uint32_t w = w0 + lane;
-        const bool act = w < Wc;
-        const uint32_t* colp = crows + (act ? w : 0);
-        uint32_t p[NP];
-#pragma unroll
-        for (int i = 0; i < NP; i++) p[i] = 0u;
-        for (uint32_t s = 0; s < S; s += 16) coarse_group<NP, 16>(colp, Wcs, my_h + s, min(16u, S - s), act, p);
-        // groups with fewer than F coarse misses
-        uint32_t lt = 0u, eq = 0xFFFFFFFFu;
-#pragma unroll
-        for (int i = NP - 1; i >= 0; i--) {
-            if ((F >> i) & 1u) { lt |= eq & ~p[i]; eq &= p[i]; }
-            else eq &= ~p[i];
-        }
-        const uint32_t pass = act ? lt : 0u;
-        uint32_t any = __ballot_sync(0xFFFFFFFFu, pass != 0u);
-        while (any) {
-            const uint32_t l = __ffs(any) - 1; any &= any - 1;
-            uint32_t pw = __shfl_sync(0xFFFFFFFFu, pass, l);
-            uint32_t last_gi = 0xFFFFFFFFu;
-            while (pw) {
-                const uint32_t g = __ffs(pw) - 1; pw &= pw - 1;
-                // coarse bit -> the 32-bit word of a full row that holds its buckets (32*gi .. 32*gi+31); with 8 or 16
-                // buckets per coarse bit several bits share a word, which is evaluated once
-                const uint32_t gi = ((w0 + l) * 32 + g) >> gshift;
-                if (gi >= Wp32 || gi == last_gi) continue;
-                last_gi = gi;
-                const uint32_t b0 = gi * 32u;
-                const uint32_t vmask = (b0 >= NB) ? 0u : (NB - b0 >= 32u ? 0xFFFFFFFFu : ((1u << (NB - b0)) - 1u));
-                uint32_t hits = 0;                         // lane b: samples that hit bucket b0 + b
-                for (uint32_t sb = 0; sb < S; sb += 32) {
-                    const uint32_t si = sb + lane;
-                    uint32_t word = 0u;
-                    if (si < S) {
-                        const uint32_t h = (uint32_t)my_h[si];
-                        word = vmask;
-                        for (uint32_t i = 0; i < NQ; i++) {
-                            const int32_t r = __ldg(k2i + ((h >> (2 * i)) & Q));
-                            if (r >= 0) { word &= __ldg(rows32 + (size_t)r * Wp32 + gi); nfine++; }
-                        }
-                    }
-#pragma unroll
-                    for (uint32_t b = 0; b < 32; b++) {
-                        const uint32_t cnt = __popc(__ballot_sync(0xFFFFFFFFu, (word >> b) & 1u));
-                        if (lane == b) hits += cnt;
-                    }
-                }
-                const uint32_t miss = S - hits;
-                const uint32_t lvl = (b0 + lane < NB && miss < F) ? miss : 0xFFFFu;
-                const uint32_t tmin = __reduce_min_sync(0xFFFFFFFFu, lvl);
-                if (tmin >= F) continue;
-                if (tmin < best) { best = tmin; count = 0; }
-                if (tmin == best) {
-                    const uint32_t m = __ballot_sync(0xFFFFFFFFu, lvl == best);
-                    const uint32_t pos = count + __popc(m & ((1u << lane) - 1u));
-                    if (lvl == best && pos < max_cand) out[pos] = b0 + lane;   // ascending, like _Find_next
-                    count += __popc(m);
-                }
-            }
-        }
-    }
-    // :471-476: a list longer than the cap is emptied, not truncated
-    if (lane == 0) cand_cnt[list] = (best < F && count <= max_cand) ? count : 0u;
-    nfine = __reduce_add_sync(0xFFFFFFFFu, nfine);
-    if (lane == 0) atomicAdd(stats + 4, (unsigned long long)S * Wc * 4ull + (unsigned long long)nfine * 4ull);   // bytes gathered
+// K2f spreads its two counters over 60 slots (stats[8 + 2s], stats[9 + 2s]); fold them into stats[3], stats[4]
+__global__ void k_stats_fold(unsigned long long* __restrict__ stats) {
+    unsigned long long a = 0, b = 0;
+    if (threadIdx.x < 60) { a = stats[8 + 2 * threadIdx.x]; b = stats[9 + 2 * threadIdx.x]; stats[8 + 2 * threadIdx.x] = 0; stats[9 + 2 * threadIdx.x] = 0; }
+    for (int o = 16; o; o >>= 1) { a += __shfl_xor_sync(0xFFFFFFFFu, a, o); b += __shfl_xor_sync(0xFFFFFFFFu, b, o); }
+    if ((threadIdx.x & 31) == 0) { if (a) atomicAdd(stats + 3, a); if (b) atomicAdd(stats + 4, b); }
 }
 
 // ---- compaction of the fixed-slot lists into cand_off / cand ---------------------------------------------------------------
@@ -371,15 +288,35 @@ __global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const ui
                                uint32_t* __restrict__ cand, uint32_t* __restrict__ cand_list,
                                unsigned long long* __restrict__ stats) {
     uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x;
-    if (2 * seg >= n_lists) return;
-    uint32_t tot = 0;
-    for (uint32_t d = 0; d < 2; d++) {
-        uint32_t l = 2 * seg + d, n = cand_cnt[l], o = cand_off[l];
-        for (uint32_t i = 0; i < n; i++) { cand[o + i] = cand_fixed[(size_t)l * max_cand + i]; cand_list[o + i] = l; }
-        if (n) atomicAdd(stats + 1 + d, (unsigned long long)n);
-        tot += n;
+    uint32_t nd[2] = {0, 0};
+    if (2 * seg < n_lists) {
+        for (uint32_t d = 0; d < 2; d++) {
+            uint32_t l = 2 * seg + d, n = cand_cnt[l], o = cand_off[l];
+            for (uint32_t i = 0; i < n; i++) { cand[o + i] = cand_fixed[(size_t)l * max_cand + i]; cand_list[o + i] = l; }
+            nd[d] = n;
+        }
     }
-    if (tot) atomicAdd(stats + 0, 1ull);
+    // the three counters of the batch: one atomic per warp, not per segment (3 M adds on one address cost ~0.5 ms)
+    const uint32_t s0 = __reduce_add_sync(0xFFFFFFFFu, (nd[0] + nd[1]) ? 1u : 0u);
+    const uint32_t s1 = __reduce_add_sync(0xFFFFFFFFu, nd[0]), s2 = __reduce_add_sync(0xFFFFFFFFu, nd[1]);
+    if ((threadIdx.x & 31) == 0) {
+        if (s0) atomicAdd(stats + 0, (unsigned long long)s0);
+        if (s1) atomicAdd(stats + 1, (unsigned long long)s1);
+        if (s2) atomicAdd(stats + 2, (unsigned long long)s2);
+    }
+}
+
+template <int NQ>
+cudaError_t launch_vote_lists_np(bm_ctx* c, const bm_params* p, uint32_t NP, const uint32_t* ids, const uint32_t* n_ids,
+                                 uint32_t blocks, size_t smem) {
+#define BM_VOTEL(NPv)                                                                                              \
+    k_map_vote_lists<NQ, NPv><<<blocks, kWarpsPerCta * 32, smem, c->stream>>>(                                     \
+        c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), ids, n_ids,  \
+        p->mapper_samples, p->mapper_fault, p->max_candidates, c->d_cand_fixed.as<uint32_t>(),                     \
+        c->d_cand_cnt.as<uint32_t>(), c->d_stats.as<unsigned long long>())
+    if (NP == 3) BM_VOTEL(3); else if (NP == 4) BM_VOTEL(4); else BM_VOTEL(6);
+#undef BM_VOTEL
+    return cudaGetLastError();
 }
 
 template <int NQ>
@@ -459,10 +396,15 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
     BM_CK(c, c->d_cand_fixed.ensure(n_lists * p->max_candidates * 4 + 16));
     BM_CK(c, c->d_cand_cnt.ensure((n_lists + 1) * 4));
     BM_CK(c, c->d_cand_off.ensure((n_lists + 1) * 4));
-    BM_CK(c, c->d_stats.ensure(128 * 8));
-    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * 8, c->stream));
+    BM_CK(c, c->d_stats.ensure(136 * 8));
+    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 128 * 8, c->stream));   // [0..7] the counters, [8..127] K2f's slots
     c->map_max_cand = p->max_candidates;
     c->n_cand = 0;
+    if (c->use_ktable) {                                  // lists K2f hands over to K2 (+ their count)
+        BM_CK(c, c->d_map_over.ensure((n_lists + 2) * 4));
+        BM_CK(c, cudaMemsetAsync(c->d_map_over.as<uint32_t>() + n_lists, 0, 4, c->stream));
+        c->map_over_cap = (uint32_t)n_lists;
+    }
     c->lsamp_k = c->lsamp_P = c->lsamp_b = 0;
     if (c->use_ktable && p->locator_samples && p->locator_samples <= 1024) {
         // K2f also draws the locator's samples (same k-mers, quality filter only: bucket_locator.h:315-341)
@@ -480,7 +422,7 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
 // K2a + K2 over segments [seg0, seg1); everything they read must already be resident (or ordered before on c->stream)
 int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len) {
     if (seg1 <= seg0) return BM_OK;
-    if (c->use_ktable && p->k <= 16 && p->mapper_samples <= 256) return bm_internal_map_fused(c, p, seg0, seg1, max_seg_len);
+    if (c->use_ktable) return bm_internal_map_fused(c, p, seg0, seg1, max_seg_len);   // K2f
     const uint32_t NQ = p->k - p->q + 1, S = p->mapper_samples, F = p->mapper_fault;
     // smallest G with !(G < 0.2*S), the comparison of q_gram_mapper.h:445 in double
     uint32_t min_good = 0;
@@ -494,27 +436,16 @@ int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
             c->d_seq.as<uint8_t>(), c->d_qual.as<uint8_t>(), c->d_read_off.as<uint64_t>(),
             c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), seg0, seg1, msl,
             c->d_k2i.as<int32_t>(), c->d_distok.as<uint32_t>(), p->k, p->q, S, p->avg_base_quality * p->k, min_good,
-            c->use_ktable ? 1u : 0u, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
+            0u, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
     }
     BM_CK(c, cudaGetLastError());
     const uint32_t NP = (F <= 7) ? 3 : (F <= 15 ? 4 : 6);
-    const uint32_t NQv = c->use_ktable ? 1u : NQ;         // rows gathered per sample
+    const uint32_t NQv = NQ;                              // rows gathered per sample
     size_t smem_v = (size_t)kWarpsPerCta * S * NQv * 4;
     const uint32_t list0 = 2 * seg0, list1 = 2 * seg1;
     const uint32_t blocks_v = (list1 - list0 + kWarpsPerCta - 1) / kWarpsPerCta;
     cudaError_t e = cudaSuccess;
-    if (c->use_ktable) {
-        KScope ks(c, BM_K_MAP);
-        const uint32_t Q = (p->q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * p->q)) - 1u);
-#define BM_COARSE(NPv)                                                                                              \
-        k_map_coarse<NPv><<<blocks_v, kWarpsPerCta * 32, smem_v, c->stream>>>(                                      \
-            c->d_krows.as<uint32_t>(), c->Wcs, c->Wc, 5u - c->krows_logg, c->d_rows.as<uint32_t>(), c->Wp / 4, c->NB, c->d_k2i.as<int32_t>(), \
-            NQ, Q, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), list0, list1, S, F, p->max_candidates,      \
-            c->d_cand_fixed.as<uint32_t>(), c->d_cand_cnt.as<uint32_t>(), c->d_stats.as<unsigned long long>())
-        if (NP == 3) BM_COARSE(3); else if (NP == 4) BM_COARSE(4); else BM_COARSE(6);
-#undef BM_COARSE
-        e = cudaGetLastError();
-    } else {
+    {
         KScope ks(c, BM_K_MAP);
         switch (NQv) {
             case 1: e = launch_vote_np<1>(c, p, NP, list0, list1, blocks_v, smem_v); break;
@@ -534,6 +465,30 @@ int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
 // fixed-slot lists of all c->n_seg segments -> cand_off / cand
 int bm_internal_map_finish(bm_ctx* c, const bm_params* p) {
     const uint32_t n_seg = c->n_seg, n_lists = 2 * n_seg;
+    if (c->use_ktable && n_seg) {
+        const uint32_t NQ = p->k - p->q + 1, S = p->mapper_samples, F = p->mapper_fault;
+        const uint32_t NP = (F <= 7) ? 3 : (F <= 15 ? 4 : 6);
+        const size_t smem_v = (size_t)kWarpsPerCta * S * NQ * 4;
+        const uint32_t* ids = c->d_map_over.as<uint32_t>();
+        const uint32_t* n_ids = ids + c->map_over_cap;
+        const uint32_t blocks = (uint32_t)c->sm_count * 8;
+        cudaError_t e = cudaSuccess;
+        {
+            KScope ks(c, BM_K_MAPOVER);
+            switch (NQ) {
+                case 1: e = launch_vote_lists_np<1>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+                case 2: e = launch_vote_lists_np<2>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+                case 3: e = launch_vote_lists_np<3>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+                case 4: e = launch_vote_lists_np<4>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+                case 5: e = launch_vote_lists_np<5>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+                case 6: e = launch_vote_lists_np<6>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+                case 7: e = launch_vote_lists_np<7>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+                default: e = launch_vote_lists_np<8>(c, p, NP, ids, n_ids, blocks, smem_v); break;
+            }
+        }
+        BM_CK(c, e);
+        k_stats_fold<<<1, 64, 0, c->stream>>>(c->d_stats.as<unsigned long long>());
+    }
     if (n_seg) {
         int r = bm_internal_exclusive_scan(c, c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists + 1);
         if (r) return r;

@@ -32,6 +32,7 @@ struct FusedArgs {
     const uint32_t* rows32; uint32_t Wp32, NB, F, max_cand;
     uint32_t* cand_fixed; uint32_t* cand_cnt; uint8_t* segok; unsigned long long* stats;
     uint32_t P; uint16_t* sidx; uint32_t* shash;
+    uint32_t max_pass; int32_t* rowidx; uint32_t* over_list; uint32_t* n_over;   // hand-over to K2 (repeats)
 };
 
 __device__ __forceinline__ void fa(uint32_t a, uint32_t b, uint32_t c, uint32_t& s, uint32_t& cy) {
@@ -231,7 +232,8 @@ k_map_fused(const FusedArgs a) {
         const uint32_t* hs = hsh + strand * S;
         const int32_t* rs = rid + (size_t)strand * S * NQ;
         const uint32_t list = 2 * seg + strand;
-        uint32_t best = 0xFFFFFFFFu, count = 0;
+        uint32_t best = 0xFFFFFFFFu, count = 0, npass = 0;
+        bool handover = false;
         uint32_t* out = a.cand_fixed + (size_t)list * a.max_cand;
         for (uint32_t w0 = 0; 2 * w0 < a.Wc; w0 += 32) {
             const uint32_t w = w0 + lane;              // this lane: coarse words 2w, 2w+1
@@ -255,6 +257,10 @@ k_map_fused(const FusedArgs a) {
                 add16<NP>(py, my);
             }
             const uint32_t passx = act ? below<NP>(px, a.F) : 0u, passy = act ? below<NP>(py, a.F) : 0u;
+            // On a repeat-rich reference a read made of repeat k-mers passes the coarse vote almost everywhere; recounting
+            // group after group would then cost more than gathering the full-width rows once: such lists go to K2.
+            npass += __reduce_add_sync(0xFFFFFFFFu, __popc(passx) + __popc(passy));
+            if (npass > a.max_pass) { handover = true; break; }
             uint32_t any = __ballot_sync(0xFFFFFFFFu, (passx | passy) != 0u);
             while (any) {
                 const uint32_t l = __ffs(any) - 1; any &= any - 1;
@@ -300,18 +306,32 @@ k_map_fused(const FusedArgs a) {
                 }
             }
         }
+        if (handover) {
+            for (uint32_t t = lane; t < S * NQ; t += 32) a.rowidx[(size_t)list * S * NQ + t] = rs[t];
+            if (lane == 0) { a.cand_cnt[list] = 0u; a.over_list[atomicAdd(a.n_over, 1u)] = list; }
+            continue;
+        }
         // :471-476: a list longer than the cap is emptied, not truncated
         if (lane == 0) a.cand_cnt[list] = (best < a.F && count <= a.max_cand) ? count : 0u;
     }
     gathered = __reduce_add_sync(0xFFFFFFFFu, gathered);
     nfine = __reduce_add_sync(0xFFFFFFFFu, nfine);
     if (lane == 0) {
-        if (gathered) atomicAdd(a.stats + 3, (unsigned long long)gathered);
-        atomicAdd(a.stats + 4, 2ull * S * a.Wc * 4ull + (unsigned long long)nfine * 4ull + 2ull * n);   // bytes loaded
+        // 60 counter slots picked by CTA (a million adds on one address would queue up in one L2 slice); folded into
+        // stats[3], stats[4] by bm_internal_map_finish
+        unsigned long long* slot = a.stats + 8 + 2 * (blockIdx.x % 60u);
+        if (gathered) atomicAdd(slot, (unsigned long long)gathered);
+        atomicAdd(slot + 1, 2ull * S * a.Wc * 4ull + (unsigned long long)nfine * 4ull + 2ull * n);   // bytes loaded
     }
 }
 
 }  // namespace
+
+extern "C" int bm_map_handover(bm_ctx* c, int max_groups) {
+    if (!c) return BM_E_ARG;
+    c->map_max_pass = max_groups < 0 ? -1 : max_groups;
+    return BM_OK;
+}
 
 // K2f over segments [seg0, seg1); also leaves the locator's samples for the batch (c->lsamp_*)
 int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len) {
@@ -332,6 +352,9 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     a.stats = c->d_stats.as<unsigned long long>();
     a.P = (P && P <= 1024 && c->d_lsamp_idx.p && c->d_lsamp_hash.p) ? P : 0;
     a.sidx = c->d_lsamp_idx.as<uint16_t>(); a.shash = c->d_lsamp_hash.as<uint32_t>();
+    const uint32_t n_groups = c->Wc * 32;             // coarse bits per row
+    a.max_pass = c->map_max_pass >= 0 ? (uint32_t)c->map_max_pass : (n_groups / 8 > 16 ? n_groups / 8 : 16);
+    a.rowidx = c->d_rowidx.as<int32_t>(); a.over_list = c->d_map_over.as<uint32_t>(); a.n_over = a.over_list + c->map_over_cap;
     const size_t smem = (size_t)kFW * (4 * a.NC + 2 * S + 2 * S * NQ) * 4;
     const uint32_t blocks = (seg1 - seg0 + kFW - 1) / kFW;
     const int NP = (S <= 15) ? 4 : (S <= 63 ? 6 : 9);

@@ -78,7 +78,7 @@ typedef struct bm_aln {
 
 /* kernel ids for bm_kernel_stats */
 enum { BM_K_ROWPOP = 0, BM_K_INDEX = 1, BM_K_SAMPLE = 2, BM_K_MAP = 3, BM_K_LOCSAMPLE = 4, BM_K_LOCATE = 5,
-       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_GIDX = 10, BM_K_LOCSCAN = 11, BM_K_COUNT = 12 };
+       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_GIDX = 10, BM_K_LOCSCAN = 11, BM_K_MAPOVER = 12, BM_K_COUNT = 13 };
 
 /* ---- context -------------------------------------------------------------------------------------------------- */
 int  bm_ctx_create(int device, bm_ctx** out);
@@ -117,6 +117,11 @@ int bm_index_zeros(bm_ctx* ctx, float distinguishability, uint32_t* zeros_out /*
  * device memory), G=16; mode 8/16/32: the same with that G; mode 0: never (the mapper gathers the k-q+1 q-gram rows of
  * every sample over the full row width). */
 int bm_index_kmer_table(bm_ctx* ctx, int mode, uint64_t max_bytes);
+/* With the coarse table the mapper recounts exactly every group of buckets that passes the coarse vote.  A read made of
+ * repeat k-mers passes almost everywhere; once more than max_groups groups of a list have passed, the list is handed to
+ * the full-width q-gram gather (k_map_vote) instead.  -1 (default): max(16, groups per row / 8).  Results are identical
+ * for any value. */
+int bm_map_handover(bm_ctx* ctx, int max_groups);
 /* k the resident table was built for (0: none) and its size */
 int bm_index_kmer_table_info(bm_ctx* ctx, uint32_t* k, uint64_t* bytes);
 /* mapper::reset (q_gram_mapper.h:374-378) */

@@ -44,10 +44,13 @@ def test_index_load_roundtrip(oracle, bm, ctx):
     (dict(read_len=300, sub=0.01, indel=0.001), dict(s=20, e=0.6, k=14, b=10)),
     (dict(read_len=800, n_reads=500), dict()),           # long reads: 5 segments each
 ])
-@pytest.mark.parametrize("ktable", [1, 0, 8, 32])   # 1: coarse k-mer table + exact recount of passing groups; 0: q-gram rows
+@pytest.mark.parametrize("ktable", [1, 0, 8, 32, -1, -2])   # -1 / -2: table on, every list / lists with > 1 passing group handed to K2
 def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     d = dataset(**kw)
+    handover = {-1: 0, -2: 1}.get(ktable, -1)
+    ktable = 1 if ktable < 0 else ktable
     ctx.index_kmer_table(ktable)
+    ctx.map_handover(handover)
     k2i, n_rows, rows = _index(oracle, d, d.frac)
     Po = oracle.params(d.L, **pk)
     P = bm.default_params(ctx.lib, d.L, **pk)
@@ -65,6 +68,7 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     assert stats[0] > 0.9 * len(segs[0]) or kw.get("read_len") == 800
     tk, tbytes = ctx.index_kmer_table_info()
     ctx.index_kmer_table(1)   # session-wide context: back to the default for the tests that follow
+    ctx.map_handover(-1)
     wp = (((d.NB + 7) >> 3) + 63) & ~63                       # padded row bytes
     group = 16 if ktable == 1 else ktable                      # buckets per coarse bit (default 16)
     wcs = ((wp * 8 // max(group, 1) + 31) // 32 + 15) & ~15    # coarse row stride in 32-bit words
