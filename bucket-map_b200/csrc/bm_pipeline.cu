@@ -25,7 +25,7 @@
 
 namespace {
 constexpr uint32_t kPipeMinReads = 32768;      // below this the serial path is used
-constexpr uint32_t kChunkMin = 16384, kChunkMax = 131072;
+constexpr uint32_t kChunkMin = 16384;
 
 // what the second lane needs from the first: its record count (-1: not known yet, -2: the first lane failed)
 struct LaneLink {
@@ -69,9 +69,18 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
     double t_enq = 0, t_h2d = 0, t_fin = 0, t_loc = 0;
     if (!c->copy_stream) BM_CK(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
 
-    uint32_t chunk = n_reads / 16;
-    chunk = chunk < kChunkMin ? kChunkMin : (chunk > kChunkMax ? kChunkMax : chunk);
-    const uint32_t n_chunks = (n_reads + chunk - 1) / chunk;
+    // Chunk schedule: large chunks first (every chunk costs five small table copies on top of its two large ones, and the
+    // link is the bottleneck), then halving towards the end so that only a small mapper launch is left when the last
+    // byte has landed: n/4, n/4, n/4, n/8, n/16, ... down to kChunkMin reads.
+    std::vector<uint32_t> bounds(1, 0u);
+    while (bounds.back() < n_reads) {
+        const uint32_t rem = n_reads - bounds.back();
+        uint32_t take = rem / 2 < n_reads / 4 ? rem / 2 : n_reads / 4;
+        if (take < kChunkMin) take = kChunkMin;
+        if (take > rem || rem - take < kChunkMin / 2) take = rem;
+        bounds.push_back(bounds.back() + take);
+    }
+    const uint32_t n_chunks = (uint32_t)bounds.size() - 1;
     while (c->chunk_ev.size() < n_chunks) {
         cudaEvent_t e;
         BM_CK(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -95,7 +104,7 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
         BM_CK(c, cudaStreamWaitEvent(c->copy_stream, wait_for->h2d_done, 0));
     }
     for (uint32_t j = 0; j < n_chunks; j++) {
-        const uint32_t r0 = j * chunk, r1 = (r0 + chunk < n_reads) ? r0 + chunk : n_reads;
+        const uint32_t r0 = bounds[j], r1 = bounds[j + 1];
         const uint32_t s0 = c->n_seg;
         r = bm_internal_build_segments(c, p, read_off, r0, r1);
         if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; }
