@@ -47,6 +47,7 @@ genome const* load_genome_cached(fs::path const& fasta, uint32_t bucket_len, uin
     static std::string key;
     std::string k = fasta.string() + "|" + std::to_string(bucket_len) + "|" + std::to_string(read_len);
     if (k != key) {
+        const auto t0 = std::chrono::steady_clock::now();
         if (!g.read_fasta(fasta)) {
             std::cerr << "[ERROR]\t\tCannot read the reference genome " << fasta << ".\n";
             key.clear();
@@ -54,6 +55,8 @@ genome const* load_genome_cached(fs::path const& fasta, uint32_t bucket_len, uin
         }
         g.bucketize(bucket_len, read_len);
         key = k;
+        std::cerr << "[BENCHMARK]\tElapsed time for reading the reference genome (" << g.n_bases << " bases): "
+                  << std::chrono::duration<float>(std::chrono::steady_clock::now() - t0).count() << " s.\n";
     }
     return &g;
 }

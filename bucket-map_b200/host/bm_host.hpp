@@ -11,6 +11,9 @@
 // construction fails loudly when no CUDA device is usable.
 #pragma once
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <filesystem>
 #include <functional>
 #include <string>
@@ -58,12 +61,48 @@ struct genome {
 };
 
 // ---- reads: FASTQ -> batches of concatenated bases / qualities -------------------------------------------------------------------
+// growable byte array in pinned host memory (bm_host_alloc): the copy engine reads it directly, so the host->device copy
+// of a batch overlaps the mapper kernels inside bm_map_locate
+class pinned_bytes {
+public:
+    pinned_bytes() = default;
+    pinned_bytes(pinned_bytes const&) = delete;
+    pinned_bytes& operator=(pinned_bytes const&) = delete;
+    ~pinned_bytes() { if (p_) bm_host_free(p_); }
+    uint8_t* data() { return p_; }
+    const uint8_t* data() const { return p_; }
+    size_t size() const { return n_; }
+    void clear() { n_ = 0; }
+    void truncate(size_t n) { if (n < n_) n_ = n; }
+    uint8_t& operator[](size_t i) { return p_[i]; }
+    const uint8_t& operator[](size_t i) const { return p_[i]; }
+    void reserve(size_t cap) {
+        if (cap <= cap_) return;
+        size_t want = cap_ ? cap_ : (size_t)1 << 20;
+        while (want < cap) want *= 2;
+        uint8_t* q = (uint8_t*)bm_host_alloc(want);
+        if (!q) { fprintf(stderr, "[ERROR]\t\tOut of pinned host memory (%zu bytes).\n", want); std::exit(2); }
+        if (n_) memcpy(q, p_, n_);
+        if (p_) bm_host_free(p_);
+        p_ = q; cap_ = want;
+    }
+    void append(const void* src, size_t len) { reserve(n_ + len); memcpy(p_ + n_, src, len); n_ += len; }
+    void append_fill(uint8_t v, size_t len) { reserve(n_ + len); memset(p_ + n_, v, len); n_ += len; }
+
+private:
+    uint8_t* p_ = nullptr;
+    size_t n_ = 0, cap_ = 0;
+};
+
 struct read_batch {
-    std::vector<std::string> ids;
-    std::vector<uint8_t> seq, qual;          // ASCII
+    pinned_bytes seq, qual;                  // ASCII, concatenated
     std::vector<uint64_t> off{0};
-    uint32_t size() const { return (uint32_t)ids.size(); }
-    void clear() { ids.clear(); seq.clear(); qual.clear(); off.assign(1, 0); }
+    std::vector<char> id_pool;               // id lines (after '@'), concatenated
+    std::vector<uint64_t> id_off{0};
+    uint32_t size() const { return (uint32_t)off.size() - 1; }
+    const char* id(uint32_t i) const { return id_pool.data() + id_off[i]; }
+    size_t id_len(uint32_t i) const { return (size_t)(id_off[i + 1] - id_off[i]); }
+    void clear() { seq.clear(); qual.clear(); off.assign(1, 0); id_pool.clear(); id_off.assign(1, 0); }
 };
 
 class fastq_reader {
@@ -75,7 +114,8 @@ public:
     bool next(read_batch& b, uint32_t max_reads, uint64_t max_bases);
 
 private:
-    bool getline(std::string& s);
+    // next line as a view into the file buffer (no copy); false at end of file
+    bool line(const char*& s, size_t& len);
     void* f_ = nullptr;
     std::vector<char> buf_;
     size_t pos_ = 0, end_ = 0;
@@ -195,7 +235,7 @@ private:
     unsigned int sample_size_, avg_base_quality_, num_segment_samples_;
     bool align_;
     std::filesystem::path genome_file_name;
-    uint32_t batch_reads_ = 1u << 20;
+    uint32_t batch_reads_ = 1u << 18;   // reads per device batch: small enough for the parse / device / SAM stages to overlap
 };
 
 }   // namespace bm

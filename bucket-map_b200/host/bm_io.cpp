@@ -1,4 +1,5 @@
 // bm_io.cpp -- device context wrapper, FASTA / FASTQ readers, FracMinHash hash function of the C++ host.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -44,42 +45,71 @@ static inline uint8_t rank_fasta(unsigned char c) {
     }
 }
 
+// Line-oriented: memchr finds the end of the line, a sequence line is packed four bases per byte through a 256-entry
+// table (whitespace inside a line falls back to the per-character path).  ~1 GB/s instead of a per-byte state machine.
 bool genome::read_fasta(std::filesystem::path const& p) {
     FILE* f = fopen(p.c_str(), "rb");
     if (!f) return false;
     ids.clear(); rec_len.clear(); packed.clear(); n_bases = 0;
     std::error_code ec;
     auto fsz = std::filesystem::file_size(p, ec);
-    if (!ec) packed.reserve((size_t)fsz / 4 + 64);
-    std::vector<char> buf(1 << 22);
+    packed.assign((ec ? (size_t)1 << 20 : (size_t)fsz / 4) + 128, 0);
+    static uint8_t lut[256];
+    static bool lut_ready = false;
+    if (!lut_ready) {
+        for (int c = 0; c < 256; c++) lut[c] = rank_fasta((unsigned char)c);
+        lut[(unsigned char)'\r'] = lut[(unsigned char)' '] = lut[(unsigned char)'\t'] = 0xFF;   // skipped
+        lut_ready = true;
+    }
+    std::vector<char> buf(1 << 24);
     bool in_header = false, line_start = true;
     std::string header;
-    uint8_t cur = 0;
     size_t n;
+    auto put = [&](uint8_t r) {
+        if ((n_bases >> 2) + 1 >= packed.size()) packed.resize(packed.size() * 2, 0);
+        packed[n_bases >> 2] |= (uint8_t)(r << ((n_bases & 3) << 1));
+        n_bases++;
+    };
     while ((n = fread(buf.data(), 1, buf.size(), f)) > 0) {
-        for (size_t i = 0; i < n; i++) {
-            const char c = buf[i];
-            if (in_header) {
-                if (c == '\n') {
+        size_t i = 0;
+        while (i < n) {
+            const char* nl = (const char*)memchr(buf.data() + i, '\n', n - i);
+            const size_t e = nl ? (size_t)(nl - buf.data()) : n;          // segment [i, e) lies inside one line
+            if (in_header) header.append(buf.data() + i, e - i);
+            else if (line_start && e > i && buf[i] == '>') { in_header = true; header.assign(buf.data() + i + 1, e - i - 1); }
+            else if (!ids.empty() && e > i) {
+                const unsigned char* s = (const unsigned char*)buf.data();
+                const uint64_t before = n_bases;
+                size_t t = i;
+                while (t < e) {
+                    if ((n_bases & 3) == 0 && t + 4 <= e) {
+                        if ((n_bases >> 2) + 2 >= packed.size()) packed.resize(packed.size() * 2, 0);
+                        const uint8_t v0 = lut[s[t]], v1 = lut[s[t + 1]], v2 = lut[s[t + 2]], v3 = lut[s[t + 3]];
+                        if (!((v0 | v1 | v2 | v3) & 0x80)) {
+                            packed[n_bases >> 2] = (uint8_t)(v0 | (v1 << 2) | (v2 << 4) | (v3 << 6));
+                            n_bases += 4; t += 4;
+                            continue;
+                        }
+                    }
+                    const uint8_t v = lut[s[t++]];
+                    if (v != 0xFF) put(v);
+                }
+                rec_len.back() += n_bases - before;
+            }
+            if (e > i || nl) line_start = false;
+            if (nl) {
+                if (in_header) {
                     if (!header.empty() && header.back() == '\r') header.pop_back();
                     ids.push_back(header); rec_len.push_back(0); header.clear();
-                    in_header = false; line_start = true;
-                } else header.push_back(c);
-                continue;
-            }
-            if (c == '\n') { line_start = true; continue; }
-            if (line_start && c == '>') { in_header = true; line_start = false; continue; }
-            line_start = false;
-            if (c == '\r' || c == ' ' || c == '\t' || ids.empty()) continue;
-            cur |= (uint8_t)(rank_fasta((unsigned char)c) << ((n_bases & 3) << 1));
-            n_bases++;
-            rec_len.back()++;
-            if ((n_bases & 3) == 0) { packed.push_back(cur); cur = 0; }
+                    in_header = false;
+                }
+                line_start = true;
+                i = e + 1;
+            } else i = e;
         }
     }
     if (in_header) { ids.push_back(header); rec_len.push_back(0); }
-    if (n_bases & 3) packed.push_back(cur);
-    packed.resize(packed.size() + 64, 0);
+    packed.resize(((size_t)n_bases + 3) / 4 + 64, 0);
     fclose(f);
     return true;
 }
@@ -109,39 +139,56 @@ void genome::bucketize(uint32_t bucket_len, uint32_t read_len) {
 fastq_reader::fastq_reader(std::filesystem::path const& p) : buf_(1 << 24) { f_ = fopen(p.c_str(), "rb"); }
 fastq_reader::~fastq_reader() { if (f_) fclose((FILE*)f_); }
 
-bool fastq_reader::getline(std::string& s) {
-    s.clear();
+// Lines are handed out as views into the 16 MB file buffer; when a line is cut by the end of the buffer the unread tail
+// is moved to the front and the buffer refilled (grown if a single line is longer than the buffer).
+bool fastq_reader::line(const char*& s, size_t& len) {
     while (true) {
-        if (pos_ == end_) {
-            if (eof_) return !s.empty();
-            end_ = fread(buf_.data(), 1, buf_.size(), (FILE*)f_);
-            pos_ = 0;
-            if (end_ == 0) { eof_ = true; return !s.empty(); }
-        }
         const char* b = buf_.data() + pos_;
-        const char* nl = (const char*)memchr(b, '\n', end_ - pos_);
+        const char* nl = (end_ > pos_) ? (const char*)memchr(b, '\n', end_ - pos_) : nullptr;
         if (nl) {
-            s.append(b, nl - b);
-            pos_ += (size_t)(nl - b) + 1;
-            if (!s.empty() && s.back() == '\r') s.pop_back();
+            s = b; len = (size_t)(nl - b);
+            pos_ += len + 1;
+            if (len && s[len - 1] == '\r') len--;
             return true;
         }
-        s.append(b, end_ - pos_);
-        pos_ = end_;
+        if (eof_) {
+            if (end_ == pos_) return false;
+            s = b; len = end_ - pos_;                        // last line without a newline
+            pos_ = end_;
+            if (len && s[len - 1] == '\r') len--;
+            return true;
+        }
+        const size_t rest = end_ - pos_;
+        if (rest && pos_) memmove(buf_.data(), buf_.data() + pos_, rest);
+        pos_ = 0; end_ = rest;
+        if (end_ == buf_.size()) buf_.resize(buf_.size() * 2);
+        const size_t got = fread(buf_.data() + end_, 1, buf_.size() - end_, (FILE*)f_);
+        if (got == 0) eof_ = true;
+        end_ += got;
     }
 }
 
 bool fastq_reader::next(read_batch& b, uint32_t max_reads, uint64_t max_bases) {
     b.clear();
     if (!f_) return false;
-    std::string id, s, plus, q;
+    const char *id, *s, *plus, *q;
+    size_t nid, ns, np, nq;
     while (b.size() < max_reads && b.seq.size() < max_bases) {
-        do { if (!getline(id)) return b.size() > 0; } while (id.empty());
-        if (!getline(s) || !getline(plus) || !getline(q)) break;
-        b.ids.emplace_back(id, 1, std::string::npos);                 // full id line after '@' (seqan3 default)
-        b.seq.insert(b.seq.end(), s.begin(), s.end());
-        q.resize(s.size(), '!');
-        b.qual.insert(b.qual.end(), q.begin(), q.end());
+        do { if (!line(id, nid)) return b.size() > 0; } while (nid == 0);
+        // a view dies with the next refill: copy each line before asking for the next one
+        const size_t id_mark = b.id_pool.size(), seq_mark = b.seq.size();
+        b.id_pool.insert(b.id_pool.end(), id + 1, id + nid);     // full id line after '@' (seqan3 default)
+        bool ok = line(s, ns);
+        if (ok && b.size() == 0) {
+            // pinned allocations are slow (and growing means copying): size the batch from its first read
+            const uint64_t want = std::min<uint64_t>(max_bases + ns, (uint64_t)(ns + 8) * max_reads);
+            b.seq.reserve((size_t)want); b.qual.reserve((size_t)want);
+        }
+        if (ok) { b.seq.append(s, ns); ok = line(plus, np) && line(q, nq); }
+        if (!ok) { b.id_pool.resize(id_mark); b.seq.truncate(seq_mark); break; }   // truncated record: dropped
+        if (nq >= ns) b.qual.append(q, ns);
+        else { b.qual.append(q, nq); b.qual.append_fill('!', ns - nq); }
+        b.id_off.push_back(b.id_pool.size());
         b.off.push_back(b.seq.size());
     }
     return b.size() > 0;

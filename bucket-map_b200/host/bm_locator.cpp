@@ -8,8 +8,12 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <condition_variable>
+#include <deque>
 #include <fstream>
 #include <iostream>
+#include <mutex>
+#include <thread>
 
 #include "bm_host.hpp"
 
@@ -52,6 +56,14 @@ unsigned int bucket_locator::initialize(fs::path const& fasta_file_name, fs::pat
 }
 
 namespace {
+
+// blocking FIFO between two pipeline stages
+template <class T>
+struct batch_queue {
+    std::mutex m; std::condition_variable cv; std::deque<T> q;
+    void push(T v) { { std::lock_guard<std::mutex> g(m); q.push_back(v); } cv.notify_one(); }
+    bool pop(T& v) { std::unique_lock<std::mutex> g(m); cv.wait(g, [&] { return !q.empty(); }); v = q.front(); q.pop_front(); return true; }
+};
 
 struct sam_writer {
     FILE* f = nullptr;
@@ -132,89 +144,141 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
 
     bm_kernel_timing(c, 1);
     bm_kernel_stats_reset(c);
-    read_batch b;
-    std::vector<uint32_t> loc_off, cigar;
-    std::vector<bm_loc> locs;
-    std::vector<bm_aln> aln;
+
+    // Three stages on three threads, batches handed on through two queues: FASTQ parsing into pinned buffers, the device
+    // pass (this thread: one context, one host thread at a time), SAM rendering.  Records leave in read order because
+    // every stage is a single thread working through the batches in order.
+    struct work {
+        read_batch b;
+        std::vector<uint32_t> loc_off, cigar;
+        std::vector<bm_loc> locs;
+        std::vector<bm_aln> aln;
+    };
+    constexpr int kDepth = 3;
+    work pool[kDepth];
+    batch_queue<work*> free_q, parsed_q, done_q;
+    for (auto& w : pool) free_q.push(&w);
+    const uint32_t batch_reads = batch_reads_;
+    double parse_s = 0;
+    const double t_pipe = now_s();
+    std::thread reader([&] {
+        work* w;
+        while (free_q.pop(w) && w) {
+            const double t = now_s();
+            const bool more = fin.next(w->b, batch_reads, (uint64_t)1 << 31);
+            parse_s += now_s() - t;
+            if (!more) break;
+            parsed_q.push(w);
+        }
+        parsed_q.push(nullptr);
+    });
+
     std::string seq_text;
     unsigned int read_id = 0, mapped_locations = 0;
     double device_s = 0, output_s = 0;
-    while (fin.next(b, batch_reads_, (uint64_t)1 << 31)) {
-        const uint32_t n = b.size();
-        const double t0 = now_s();
-        uint64_t stats[8] = {0};
-        uint64_t n_locs = 0;
-        loc_off.resize((size_t)n + 1);
-        if (!align_) {
-            const size_t cap = (size_t)2 * n * (num_segment_samples_ ? num_segment_samples_ : 1) * p.max_candidates + 1;
-            // one record per candidate at most; the merged lists are far shorter, so size from the candidate count
-            rc = bm_reads_upload(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n);
-            if (!rc) rc = bm_map_device(c, &p);
-            if (!rc) rc = bm_locate_device(c, &p, 1);
-            if (!rc) rc = bm_locate_count(c, &n_locs);
-            if (!rc) { locs.resize(n_locs + 1); rc = bm_locate_download(c, loc_off.data(), locs.data(), n_locs + 1); }
-            if (!rc) rc = bm_map_download(c, nullptr, nullptr, 0, stats);
-            (void)cap;
-        } else {
-            rc = bm_reads_upload(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n);
-            if (!rc) rc = bm_map_device(c, &p);
-            if (!rc) rc = bm_locate_device(c, &p, 0);
-            if (!rc) rc = bm_locate_count(c, &n_locs);
-            if (!rc) { locs.resize(n_locs + 1); rc = bm_locate_download(c, loc_off.data(), locs.data(), n_locs + 1); }
-            if (!rc) rc = bm_align_device(c, &p);                                       // K4 (:560-589)
-            uint64_t used = 0;
-            aln.resize(n_locs + 1);
-            if (!rc) rc = bm_align_download(c, aln.data(), nullptr, 0, &used);
-            cigar.resize(used + 1);
-            if (!rc && used) rc = bm_align_download(c, aln.data(), cigar.data(), used, &used);
-            if (!rc) rc = bm_map_download(c, nullptr, nullptr, 0, stats);
-        }
-        if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n"; return; }
-        qm->mapped_reads += (unsigned)stats[0]; qm->num_buckets_orig += (unsigned)stats[1]; qm->num_buckets_rev_comp += (unsigned)stats[2];
-        qm->num_records += n;
-        const double t1 = now_s();
-        device_s += t1 - t0;
-
-        // SAM records in read order (:535-604)
-        for (uint32_t i = 0; i < n; i++) {
-            if (loc_off[i] == loc_off[i + 1]) continue;
-            const uint8_t* s = &b.seq[b.off[i]];
-            const size_t len = (size_t)(b.off[i + 1] - b.off[i]);
-            seq_text.resize(len);
-            for (size_t t = 0; t < len; t++) seq_text[t] = dna4_char(s[t]);
-            for (uint32_t j = loc_off[i]; j < loc_off[i + 1]; j++) {
-                const bm_loc& l = locs[j];
-                size_t map_qual, ref_offset;
-                if (!align_) {
-                    map_qual = std::min((unsigned int)60, 6 * l.votes);                  // :591
-                    ref_offset = (unsigned int)(bucket_offsets[l.bucket] + l.offset);    // :592
-                } else {
-                    if (!aln[j].kept) continue;                                          // :571-573
-                    map_qual = (uint8_t)aln[j].map_qual;                                 // mapq is a uint8_t field in SAM
-                    ref_offset = (unsigned int)(aln[j].begin + bucket_offsets[l.bucket] + l.offset);   // :576
-                }
-                out.buf += b.ids[i]; out.buf += '\t';
-                out.num(l.is_original ? 0 : 16); out.buf += '\t';
-                out.buf += bucket_name[l.bucket]; out.buf += '\t';
-                out.num(ref_offset + 1); out.buf += '\t';
-                out.num(map_qual); out.buf += '\t';
-                if (align_ && aln[j].cigar_len) {
-                    for (uint32_t t = 0; t < aln[j].cigar_len; t++) {
-                        const uint32_t op = cigar[aln[j].cigar_off + t];
-                        out.num(op >> 4); out.buf += "MID"[op & 15u];
+    const bool align = align_;
+    std::thread writer([&] {
+        static const char* kDecode = nullptr;
+        static char decode[256];
+        if (!kDecode) { for (int v = 0; v < 256; v++) decode[v] = dna4_char((uint8_t)v); kDecode = decode; }
+        work* w;
+        while (done_q.pop(w) && w) {
+            const double t1 = now_s();
+            const read_batch& b = w->b;
+            const uint32_t n = b.size();
+            // SAM records in read order (:535-604)
+            for (uint32_t i = 0; i < n; i++) {
+                if (w->loc_off[i] == w->loc_off[i + 1]) continue;
+                const uint8_t* s = &b.seq[b.off[i]];
+                const size_t len = (size_t)(b.off[i + 1] - b.off[i]);
+                seq_text.resize(len);
+                for (size_t t = 0; t < len; t++) seq_text[t] = kDecode[s[t]];
+                for (uint32_t j = w->loc_off[i]; j < w->loc_off[i + 1]; j++) {
+                    const bm_loc& l = w->locs[j];
+                    size_t map_qual, ref_offset;
+                    if (!align) {
+                        map_qual = std::min((unsigned int)60, 6 * l.votes);                  // :591
+                        ref_offset = (unsigned int)(bucket_offsets[l.bucket] + l.offset);    // :592
+                    } else {
+                        if (!w->aln[j].kept) continue;                                       // :571-573
+                        map_qual = (uint8_t)w->aln[j].map_qual;                              // mapq is a uint8_t field in SAM
+                        ref_offset = (unsigned int)(w->aln[j].begin + bucket_offsets[l.bucket] + l.offset);   // :576
                     }
-                } else out.buf += '*';
-                out.buf += "\t*\t0\t0\t";
-                out.buf += seq_text; out.buf += '\t';
-                out.buf.append((const char*)&b.qual[b.off[i]], len);
-                out.buf += '\n';
-                mapped_locations++;
+                    out.buf.append(b.id(i), b.id_len(i)); out.buf += '\t';
+                    out.num(l.is_original ? 0 : 16); out.buf += '\t';
+                    out.buf += bucket_name[l.bucket]; out.buf += '\t';
+                    out.num(ref_offset + 1); out.buf += '\t';
+                    out.num(map_qual); out.buf += '\t';
+                    if (align && w->aln[j].cigar_len) {
+                        for (uint32_t t = 0; t < w->aln[j].cigar_len; t++) {
+                            const uint32_t op = w->cigar[w->aln[j].cigar_off + t];
+                            out.num(op >> 4); out.buf += "MID"[op & 15u];
+                        }
+                    } else out.buf += '*';
+                    out.buf += "\t*\t0\t0\t";
+                    out.buf += seq_text; out.buf += '\t';
+                    out.buf.append((const char*)&b.qual[b.off[i]], len);
+                    out.buf += '\n';
+                    mapped_locations++;
+                }
+                out.maybe_flush();
             }
-            out.maybe_flush();
+            read_id += n;
+            output_s += now_s() - t1;
+            free_q.push(w);
         }
-        read_id += n;
-        output_s += now_s() - t1;
+    });
+
+    bool failed = false;
+    {
+        work* w;
+        while (parsed_q.pop(w) && w) {
+            read_batch& b = w->b;
+            const uint32_t n = b.size();
+            const double t0 = now_s();
+            uint64_t stats[8] = {0};
+            uint64_t n_locs = 0;
+            w->loc_off.resize((size_t)n + 1);
+            rc = BM_OK;
+            bool done = false;
+            if (!align_) {
+                // one call: H2D chunks overlapped with the mapper.  The merged lists are almost always one record per
+                // read; if this batch needs more room than 4 per read the staged calls below size the buffer exactly.
+                const size_t cap = (size_t)4 * n + 1024;
+                w->locs.resize(cap);
+                int r1 = bm_map_locate(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n, 1, w->loc_off.data(), w->locs.data(),
+                                       cap, stats);
+                if (r1 == BM_OK) { n_locs = w->loc_off[n]; done = true; }
+            }
+            if (!done) {
+                rc = bm_reads_upload(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n);
+                if (!rc) rc = bm_map_device(c, &p);
+                if (!rc) rc = bm_locate_device(c, &p, align_ ? 0 : 1);
+                if (!rc) rc = bm_locate_count(c, &n_locs);
+                if (!rc) { w->locs.resize(n_locs + 1); rc = bm_locate_download(c, w->loc_off.data(), w->locs.data(), n_locs + 1); }
+                if (align_) {
+                    if (!rc) rc = bm_align_device(c, &p);                                   // K4 (:560-589)
+                    uint64_t used = 0;
+                    w->aln.resize(n_locs + 1);
+                    if (!rc) rc = bm_align_download(c, w->aln.data(), nullptr, 0, &used);
+                    w->cigar.resize(used + 1);
+                    if (!rc && used) rc = bm_align_download(c, w->aln.data(), w->cigar.data(), used, &used);
+                }
+                if (!rc) rc = bm_map_download(c, nullptr, nullptr, 0, stats);
+            }
+            if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n"; failed = true; break; }
+            qm->mapped_reads += (unsigned)stats[0]; qm->num_buckets_orig += (unsigned)stats[1]; qm->num_buckets_rev_comp += (unsigned)stats[2];
+            qm->num_records += n;
+            device_s += now_s() - t0;
+            done_q.push(w);
+        }
     }
+    done_q.push(nullptr);
+    writer.join();
+    if (failed) { free_q.push(nullptr); work* w; while (parsed_q.pop(w) && w) free_q.push(w); }
+    else free_q.push(nullptr);
+    reader.join();
+    if (failed) return;
     out.flush();
 
     // the reference's phase log (q_gram_mapper.h:548-555, bucket_locator.h:698-702,606-610), filled with device times
@@ -231,6 +295,8 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
     const float es = (float)(ms[BM_K_ALIGN] * 1e-3 + output_s);
     std::cerr << "[BENCHMARK]\tTotal time used for alignment verification and output: " << es << " s ("
               << es / mapped_locations * 1000 * 1000 << " μs per pairwise alignment).\n";
+    std::cerr << "[BENCHMARK]\tHost pipeline: FASTQ parsing " << (float)parse_s << " s, device passes " << (float)device_s
+              << " s, SAM rendering " << (float)output_s << " s on three threads; wall " << (float)(now_s() - t_pipe) << " s.\n";
     std::cerr << "[BENCHMARK]\tDevice pipeline (H2D + kernels + D2H): " << (float)device_s << " s for " << read_id
               << " reads (" << (float)(read_id / (device_s > 0 ? device_s : 1)) << " reads/s).\n";
     _m->reset();                                                                       // :627

@@ -40,7 +40,7 @@ struct cmd_arguments {                     // main.cpp:12-39
     unsigned int bucket_len = 65536;
     long seed_x = -1, seed_y = -1;
     int device = -1;
-    unsigned int batch_reads = 1u << 20;
+    unsigned int batch_reads = 1u << 18;
 #ifdef BM_ALIGN
     bool align = true;
 #else
