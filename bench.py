@@ -126,6 +126,25 @@ def simulate(cfg, packed, n_reads, seed, n_span=None):
                                   cfg["indel"], cfg["indel"], seed)[:3]
 
 
+def bind_to_gpu_numa_node(device):
+    """run this rank (and first-touch its pinned buffers) on the CPUs next to its GPU: on a two-socket box a rank that
+    lands on the far socket pushes every host<->device byte across the socket link"""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device)
+        try:
+            pynvml.nvmlDeviceSetCpuAffinity(h)
+        except Exception:
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+            cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+        return sorted(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -279,6 +298,8 @@ def main():
     real_stdout = os.dup(1)
     os.dup2(2, 1)
     torch.cuda.set_device(local)
+    all_cpus = os.sched_getaffinity(0)
+    bind_to_gpu_numa_node(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -486,6 +507,7 @@ def main():
         "mapped": {"reads_with_candidate": int(mstats[0]), "cand_fwd": int(mstats[1]), "cand_rev": int(mstats[2])},
     }
     if rank == 0 and world == 1 and not a.no_cpu:
+        os.sched_setaffinity(0, all_cpus)            # the CPU baseline may use every host core
         rows = ctx.index_download()
         ncores = os.cpu_count() or 1
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
