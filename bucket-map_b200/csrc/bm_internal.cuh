@@ -246,6 +246,17 @@ __device__ __forceinline__ uint32_t sample_index(uint32_t i, uint32_t n, uint32_
     return (uint32_t)floor(__dmul_rn((double)(int)i, delta));
 }
 
+// position of the x-th (0-based) set bit of m (x < popc(m)): binary search on popcounts (__fns is a slow library loop)
+__device__ __forceinline__ uint32_t select_bit(uint32_t m, uint32_t x) {
+    uint32_t pos = 0, c;
+    c = __popc(m & 0xFFFFu); if (x >= c) { x -= c; pos = 16; m >>= 16; }
+    c = __popc(m & 0xFFu);   if (x >= c) { x -= c; pos += 8; m >>= 8; }
+    c = __popc(m & 0xFu);    if (x >= c) { x -= c; pos += 4; m >>= 4; }
+    c = __popc(m & 0x3u);    if (x >= c) { x -= c; pos += 2; m >>= 2; }
+    if (x >= (m & 1u)) pos += 1;
+    return pos;
+}
+
 // position of the x-th (0-based) set bit over the chunk masks
 __device__ __forceinline__ uint32_t select_good(const uint32_t* mask, uint32_t nchunk, uint32_t x) {
     uint32_t c = 0;
@@ -254,7 +265,7 @@ __device__ __forceinline__ uint32_t select_good(const uint32_t* mask, uint32_t n
         if (x < n) break;
         x -= n;
     }
-    return c * 32 + __fns(mask[c], 0, (int)x + 1);
+    return c * 32 + select_bit(mask[c], x);
 }
 
 __device__ __forceinline__ void stage_segment(const SegStage& st, const uint8_t* __restrict__ seq,

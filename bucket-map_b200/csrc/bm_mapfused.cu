@@ -10,8 +10,8 @@
 //      the k-mer tests of :437-442 are an OR over k-q+1 neighbouring bits plus a prefix-sum difference.
 //   2. the Sampler picks S good k-mers (utils.h:160-178); their hashes (both strands) and q-gram row ids go to shared
 //      memory.
-//   3. per strand: S coarse rows, 8 B per lane, all loads in flight together; missed samples per group of buckets are
-//      counted with a carry-save adder tree on bit planes (7 inputs -> 3 bits in 4 full adders).
+//   3. per strand: S coarse rows, 8 B per lane, all loads in flight together; the samples that hit each group of buckets
+//      are counted with a carry-save adder tree on bit planes (7 inputs -> 3 bits in 4 full adders).
 //   4. groups with < F coarse misses (rare) are recounted exactly from the .qgram matrix; best_results()' answer
 //      (:90-102) is written as the candidate list.
 //
@@ -140,6 +140,7 @@ k_map_fused(const FusedArgs a) {
     uint32_t q2 = 0, q1 = 0;                          // phred rank of this lane's position in chunks c-2, c-1
     uint32_t mn2 = 0xFFFFFFFFu, mn1 = 0xFFFFFFFFu;    // lowest phred rank inside chunks c-2, c-1
     uint32_t GA = 0, GB = 0;
+    uint32_t klo = 0, khi = 0, kA = 0, kB = 0;        // lane c keeps the plane / mask words of chunk c (c < 32)
     uint32_t nb = 'A', nq = 33;                       // bytes of the NEXT chunk, requested one step ahead
     if (lane < n) { nb = a.seq[off + lane]; nq = a.qual[off + lane]; }
     for (uint32_t c = 0; c <= nbch + 1; c++) {
@@ -150,7 +151,8 @@ k_map_fused(const FusedArgs a) {
         const uint32_t r = rank_dna4_lut(cb), qv = cq - 33u;   // positions >= n: rank 0, phred 0
         const uint32_t lo0 = __ballot_sync(0xFFFFFFFFu, r & 1u), hi0 = __ballot_sync(0xFFFFFFFFu, r & 2u);
         const uint32_t mn0 = __reduce_min_sync(0xFFFFFFFFu, (i < n) ? qv : 0xFFFFFFFFu);
-        if (lane == 0) { lo[c] = lo0; hi[c] = hi0; }
+        if (c < 32) { if (lane == c) { klo = lo0; khi = hi0; } }
+        else if (lane == 0) { lo[c] = lo0; hi[c] = hi0; }
         uint32_t Dc = 0;                               // ... of chunk c-1
         if (c >= 1) {                                  // q-grams starting in chunk c-1 (windows reach into chunk c)
             const uint32_t lw = __funnelshift_r(lo1, lo0, lane) & qmask, hw = __funnelshift_r(hi1, hi0, lane) & qmask;
@@ -175,26 +177,60 @@ k_map_fused(const FusedArgs a) {
                 qok = qok && qs >= a.minq;
             }
             const uint32_t b = __ballot_sync(0xFFFFFFFFu, qok), m = __ballot_sync(0xFFFFFFFFu, qok && dist);   // :437-442
-            if (lane == 0) { mA[c - 2] = m; mB[c - 2] = b; }
+            if (c - 2 < 32) { if (lane == c - 2) { kA = m; kB = b; } }
+            else if (lane == 0) { mA[c - 2] = m; mB[c - 2] = b; }
             GA += __popc(m); GB += __popc(b);
         }
         lo1 = lo0; hi1 = hi0; Dp = Dc;
         q2 = q1; q1 = qv; mn2 = mn1; mn1 = mn0;
     }
+    if (lane <= nbch + 1) { lo[lane] = klo; hi[lane] = khi; }      // chunks 0..31: one store per lane
+    if (lane < nchunk) { mA[lane] = kA; mB[lane] = kB; }
     __syncwarp();
 
-    // ---- 2a. the locator's P samples: quality filter only (bucket_locator.h:315-341) ---------------------------------------
-    if (a.P) {
-        if (GB == 0) {                                 // :328-330: no good k-mer -> all k-mers
-            for (uint32_t c = lane; c < nchunk; c += 32) {
-                const uint32_t rem = nk - c * 32;
-                mB[c] = rem >= 32 ? 0xFFFFFFFFu : ((1u << rem) - 1u);
-            }
-            GB = nk;
-            __syncwarp();
+    // ---- 2. samples: the locator's P (quality filter only, bucket_locator.h:315-341) and the mapper's S
+    //         (q_gram_mapper.h:445-469).  With S, P <= 16 the two samplers run side by side in the two half-warps.
+    if (a.P && GB == 0) {                              // :328-330: no good k-mer -> all k-mers
+        for (uint32_t c = lane; c < nchunk; c += 32) {
+            const uint32_t rem = nk - c * 32;
+            mB[c] = rem >= 32 ? 0xFFFFFFFFu : ((1u << rem) - 1u);
         }
+        GB = nk;
+        __syncwarp();
+    }
+    const bool ok = GA >= a.min_good && GA > 0;
+    const uint32_t Q = (q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * q)) - 1u);
+    uint32_t gathered = 0;
+    if (lane == 0) a.segok[seg] = ok ? 1 : 0;
+    if (a.P && a.P <= 16 && S <= 16) {
+        const bool isB = lane >= 16;
+        const uint32_t s = lane & 15;
+        const bool want = isB ? (s < a.P) : (ok && s < S);
+        uint32_t pos = 0, h = 0xFFFFFFFFu;             // segment shorter than k: no usable locator sample
+        if (want && nk) {
+            pos = select_good(isB ? mB : mA, nchunk, sample_index(s, isB ? a.P : S, isB ? GB : GA));
+            h = hash_from_planes(lo, hi, pos, k);
+        }
+        if (isB && want) {
+            a.sidx[(size_t)seg * a.P + s] = (uint16_t)pos;
+            a.shash[(size_t)seg * a.P + s] = h;
+        }
+        if (!ok) {
+            if (lane < 2) a.cand_cnt[2 * seg + lane] = 0;
+            return;
+        }
+        if (!isB && want) {
+            const uint32_t hr = bm_revcomp_hash(h, k);
+            hsh[s] = h; hsh[S + s] = hr;
+            for (uint32_t i = 0; i < NQ; i++) {
+                const int32_t r0 = __ldg(a.k2i + ((h >> (2 * i)) & Q)), r1 = __ldg(a.k2i + ((hr >> (2 * i)) & Q));
+                rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1;
+                gathered += (r0 >= 0) + (r1 >= 0);
+            }
+        }
+    } else {
         for (uint32_t s = lane; s < a.P; s += 32) {
-            uint32_t pos = 0, h = 0xFFFFFFFFu;         // segment shorter than k: no usable sample
+            uint32_t pos = 0, h = 0xFFFFFFFFu;
             if (nk) {
                 pos = select_good(mB, nchunk, sample_index(s, a.P, GB));
                 h = hash_from_planes(lo, hi, pos, k);
@@ -202,26 +238,20 @@ k_map_fused(const FusedArgs a) {
             a.sidx[(size_t)seg * a.P + s] = (uint16_t)pos;
             a.shash[(size_t)seg * a.P + s] = h;
         }
-    }
-
-    // ---- 2b. the mapper's S samples (q_gram_mapper.h:445-469) ----------------------------------------------------------------
-    const bool ok = GA >= a.min_good && GA > 0;
-    if (lane == 0) a.segok[seg] = ok ? 1 : 0;
-    if (!ok) {
-        if (lane < 2) a.cand_cnt[2 * seg + lane] = 0;
-        return;
-    }
-    const uint32_t Q = (q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * q)) - 1u);
-    uint32_t gathered = 0;
-    for (uint32_t s = lane; s < S; s += 32) {
-        const uint32_t pos = select_good(mA, nchunk, sample_index(s, S, GA));
-        const uint32_t h = hash_from_planes(lo, hi, pos, k);
-        const uint32_t hr = bm_revcomp_hash(h, k);
-        hsh[s] = h; hsh[S + s] = hr;
-        for (uint32_t i = 0; i < NQ; i++) {
-            const int32_t r0 = __ldg(a.k2i + ((h >> (2 * i)) & Q)), r1 = __ldg(a.k2i + ((hr >> (2 * i)) & Q));
-            rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1;
-            gathered += (r0 >= 0) + (r1 >= 0);
+        if (!ok) {
+            if (lane < 2) a.cand_cnt[2 * seg + lane] = 0;
+            return;
+        }
+        for (uint32_t s = lane; s < S; s += 32) {
+            const uint32_t pos = select_good(mA, nchunk, sample_index(s, S, GA));
+            const uint32_t h = hash_from_planes(lo, hi, pos, k);
+            const uint32_t hr = bm_revcomp_hash(h, k);
+            hsh[s] = h; hsh[S + s] = hr;
+            for (uint32_t i = 0; i < NQ; i++) {
+                const int32_t r0 = __ldg(a.k2i + ((h >> (2 * i)) & Q)), r1 = __ldg(a.k2i + ((hr >> (2 * i)) & Q));
+                rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1;
+                gathered += (r0 >= 0) + (r1 >= 0);
+            }
         }
     }
     __syncwarp();
@@ -243,20 +273,21 @@ k_map_fused(const FusedArgs a) {
 #pragma unroll
             for (int i = 0; i < NP; i++) { px[i] = 0u; py[i] = 0u; }
             for (uint32_t s0 = 0; s0 < S; s0 += 16) {
-                uint32_t mx[16], my[16];               // 1 = no bucket of the group holds the sample
+                uint32_t mx[16], my[16];               // 1 = some bucket of the group holds the sample
 #pragma unroll
                 for (int b = 0; b < 16; b++) {
-                    mx[b] = 0u; my[b] = 0u;            // no sample: nothing missed
-                    if (s0 + b < S) {
-                        uint2 v = make_uint2(0u, 0u);
-                        if (act) v = __ldg(colp + (size_t)hs[s0 + b] * a.Wcs2);
-                        mx[b] = ~v.x; my[b] = ~v.y;
+                    mx[b] = 0u; my[b] = 0u;            // no sample / no such word: no hit
+                    if (s0 + b < S && act) {
+                        const uint2 v = __ldg(colp + (size_t)hs[s0 + b] * a.Wcs2);
+                        mx[b] = v.x; my[b] = v.y;
                     }
                 }
                 add16<NP>(px, mx);
                 add16<NP>(py, my);
             }
-            const uint32_t passx = act ? below<NP>(px, a.F) : 0u, passy = act ? below<NP>(py, a.F) : 0u;
+            // px, py count HITS per group: fewer than F misses <=> at least S-F+1 hits
+            const uint32_t need = (S >= a.F) ? S - a.F + 1u : 0u;
+            const uint32_t passx = act ? ~below<NP>(px, need) : 0u, passy = act ? ~below<NP>(py, need) : 0u;
             // On a repeat-rich reference a read made of repeat k-mers passes the coarse vote almost everywhere; recounting
             // group after group would then cost more than gathering the full-width rows once: such lists go to K2.
             npass += __reduce_add_sync(0xFFFFFFFFu, __popc(passx) + __popc(passy));
