@@ -95,7 +95,7 @@ struct bm_ctx {
     // genome k-mer position index for the locator (bm_locidx.cu): start positions of all k-mers of the reference sorted
     // by (hash, position) + 4^k+1 run offsets; gidx_k = the k it was built for (0: not resident)
     DevBuf d_gidx_pos, d_gidx_off;
-    uint32_t gidx_k = 0;
+    uint32_t gidx_k = 0, gidx_lb = 0, gidx_bshift = 0;   // hash offsets are kept per genome block: 2^lb blocks of 2^bshift bases
     int gidx_mode = 1;            // 0 never, 1 when it fits (bm_locator_index)
     bool use_gidx = false;
 

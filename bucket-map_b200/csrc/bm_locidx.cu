@@ -14,6 +14,8 @@
 // Built once per (reference, k) on the device: hash every position, radix-sort (hash, position) pairs, mark run starts.
 // 4 B per base for `pos` (6.8 GB on the 1.7 Gbp reference) + 4^k * 4 B for `off`; ~27 GB of scratch during the build.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <thrust/iterator/reverse_iterator.h>
 
 #include "bm_internal.cuh"
 
@@ -42,20 +44,28 @@ __global__ void k_gidx_keys(const uint8_t* __restrict__ packed, uint64_t n_pos, 
     for (; i < n_pos; i += stride) { keys[i] = genome_kmer(packed, i, k); vals[i] = (uint32_t)i; }
 }
 
-// off[h] = first sorted entry with hash >= h; runs of absent hashes are filled by the thread at the next run start
-__global__ void k_gidx_offsets(const uint32_t* __restrict__ keys, uint64_t n_pos, uint32_t n_codes, uint32_t* __restrict__ off) {
+// Offsets over the composite key (hash << lb) | (position >> bshift): the genome is cut into <= 2^lb blocks, so that the
+// run of one hash inside the one or two blocks a bucket touches is a handful of entries instead of ~n_bases / 4^k.
+// off[c] = first sorted entry with composite key >= c; runs of absent keys are filled by the thread at the next run start.
+__device__ __forceinline__ uint32_t comp_key(uint32_t h, uint32_t pos, uint32_t lb, uint32_t bshift) {
+    return (h << lb) | (pos >> bshift);
+}
+// run starts: off[c] = index of the first entry with composite key c (the table is pre-filled with 0xFFFFFFFF and
+// off[n_comp] = n_pos); a reverse running minimum then turns it into "first entry with key >= c" for absent keys too
+__global__ void k_gidx_mark(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ pos, uint64_t n_pos,
+                            uint32_t n_comp, uint32_t lb, uint32_t bshift, uint32_t* __restrict__ off) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    if (i == 0) off[n_comp] = (uint32_t)n_pos;
     for (; i < n_pos; i += stride) {
-        const uint32_t h = keys[i];
-        const uint32_t lo = (i == 0) ? 0u : keys[i - 1] + 1u;
-        if (i == 0 || h >= lo) for (uint32_t g = lo; g <= h; g++) off[g] = (uint32_t)i;
-        if (i + 1 == n_pos) for (uint32_t g = h + 1; g <= n_codes; g++) off[g] = (uint32_t)n_pos;
+        const uint32_t h = comp_key(keys[i], pos[i], lb, bshift);
+        if (i == 0 || h != comp_key(keys[i - 1], pos[i - 1], lb, bshift)) off[h] = (uint32_t)i;
     }
 }
+struct MinOp { __device__ __forceinline__ uint32_t operator()(uint32_t a, uint32_t b) const { return a < b ? a : b; } };
 
 struct IdxArgs {
-    const uint32_t* pos; const uint32_t* off;
+    const uint32_t* pos; const uint32_t* off; uint32_t lb, bshift;
     const uint64_t* bstart; const uint32_t* blen; uint32_t n_emit;
     const uint32_t* cand; const uint32_t* cseg; const uint32_t* seg_len; const uint16_t* sidx; const uint32_t* shash;
     uint32_t n_cand, k, P; int A; uint32_t min_votes;
@@ -107,11 +117,13 @@ k_locate_idx(const IdxArgs a) {
                 if (reverse) h = bm_revcomp_hash(h, k);
                 cur = a.sidx[(size_t)seg * P + si];
                 if (reverse) cur = slen - k - cur;
-                const uint32_t o0 = __ldg(a.off + h), o1 = __ldg(a.off + h + 1);
+                // the run of h inside the genome block(s) the bucket's k-mer starts fall into
+                const uint64_t end = start + npos;
+                const uint32_t c0 = comp_key(h, (uint32_t)start, a.lb, a.bshift), c1 = comp_key(h, (uint32_t)(end - 1), a.lb, a.bshift);
+                const uint32_t o0 = __ldg(a.off + c0), o1 = __ldg(a.off + c1 + 1);
                 if (o0 != o1) {
                     x0 = lb_pos(a.pos, o0, o1, start);
                     x1 = x0;
-                    const uint64_t end = start + npos;
                     while (x1 < o1 && (uint64_t)__ldg(a.pos + x1) < end) x1++;
                 }
             }
@@ -164,11 +176,18 @@ int bm_internal_gidx_prepare(bm_ctx* c, uint32_t k) {
     if (c->gidx_k == k && c->d_gidx_pos.p && c->d_gidx_off.p) { c->use_gidx = true; return BM_OK; }
     c->d_gidx_pos.release(); c->d_gidx_off.release(); c->gidx_k = 0;
     const uint64_t n_pos = c->n_bases - k + 1;
-    const uint32_t n_codes = 1u << (2 * k);
+    const uint32_t lb = (30 - 2 * k) < 6 ? (30 - 2 * k) : 6;              // log2 of the genome blocks per hash (table <= 4 GB)
+    uint32_t bshift = 0;
+    while (((c->n_bases - 1) >> bshift) >= (1ull << lb)) bshift++;
+    const uint32_t n_codes = 1u << (2 * k + lb);                          // composite keys
     size_t tmp = 0;
     {
         cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
         BM_CK(c, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (uint64_t)n_pos, 0, (int)(2 * k), c->stream));
+        auto rit = thrust::make_reverse_iterator((uint32_t*)nullptr);
+        size_t tmp2 = 0;
+        BM_CK(c, cub::DeviceScan::InclusiveScan(nullptr, tmp2, rit, rit, MinOp(), (int)(n_codes + 1), c->stream));
+        if (tmp2 > tmp) tmp = tmp2;                   // one scratch buffer serves the sort, then the scan
     }
     size_t fr = 0, tot = 0;
     BM_CK(c, cudaMemGetInfo(&fr, &tot));
@@ -188,14 +207,23 @@ int bm_internal_gidx_prepare(bm_ctx* c, uint32_t k) {
     }
     int rc = BM_OK;
     {
-        KScope ks(c, BM_K_GIDX, 2);
+        KScope ks(c, BM_K_GIDX, 2);   // k_gidx_keys + k_gidx_mark (the sort and the scan are library kernels)
         const uint32_t blocks = (uint32_t)c->sm_count * 16;
         k_gidx_keys<<<blocks, 256, 0, c->stream>>>(c->d_packed.as<uint8_t>(), n_pos, k, k0.as<uint32_t>(), v0.as<uint32_t>());
         cub::DoubleBuffer<uint32_t> dk(k0.as<uint32_t>(), k1.as<uint32_t>()), dv(v0.as<uint32_t>(), v1.as<uint32_t>());
         cudaError_t se = cub::DeviceRadixSort::SortPairs(t.p, tmp, dk, dv, (uint64_t)n_pos, 0, (int)(2 * k), c->stream);
         if (se == cudaSuccess) {
-            k_gidx_offsets<<<blocks, 256, 0, c->stream>>>(dk.Current(), n_pos, n_codes, c->d_gidx_off.as<uint32_t>());
-            se = cudaGetLastError();
+            uint32_t* off = c->d_gidx_off.as<uint32_t>();
+            se = cudaMemsetAsync(off, 0xFF, ((size_t)n_codes + 1) * 4, c->stream);
+            if (se == cudaSuccess) {
+                k_gidx_mark<<<blocks, 256, 0, c->stream>>>(dk.Current(), dv.Current(), n_pos, n_codes, lb, bshift, off);
+                se = cudaGetLastError();
+            }
+            if (se == cudaSuccess) {                  // reverse inclusive min-scan, in place; the sort's scratch is free again
+                auto rit = thrust::make_reverse_iterator(off + (size_t)n_codes + 1);
+                size_t tmp2 = tmp;
+                se = cub::DeviceScan::InclusiveScan(t.p, tmp2, rit, rit, MinOp(), (int)(n_codes + 1), c->stream);
+            }
         }
         if (se == cudaSuccess) se = cudaStreamSynchronize(c->stream);
         if (se != cudaSuccess) {
@@ -209,7 +237,7 @@ int bm_internal_gidx_prepare(bm_ctx* c, uint32_t k) {
     }
     k0.release(); k1.release(); v0.release(); v1.release(); t.release();
     if (rc) { c->d_gidx_off.release(); return rc; }
-    c->gidx_k = k; c->use_gidx = true;
+    c->gidx_k = k; c->gidx_lb = lb; c->gidx_bshift = bshift; c->use_gidx = true;
     return BM_OK;
 }
 
@@ -217,7 +245,7 @@ int bm_internal_gidx_prepare(bm_ctx* c, uint32_t k) {
 // in over_list)
 int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* over_list, uint32_t* d_n_over, uint32_t* n_over) {
     IdxArgs a;
-    a.pos = c->d_gidx_pos.as<uint32_t>(); a.off = c->d_gidx_off.as<uint32_t>();
+    a.pos = c->d_gidx_pos.as<uint32_t>(); a.off = c->d_gidx_off.as<uint32_t>(); a.lb = c->gidx_lb; a.bshift = c->gidx_bshift;
     a.bstart = c->d_bstart.as<uint64_t>(); a.blen = c->d_blen.as<uint32_t>(); a.n_emit = c->n_emit;
     a.cand = c->d_cand.as<uint32_t>(); a.cseg = c->d_cseg.as<uint32_t>(); a.seg_len = c->d_seg_len.as<uint32_t>();
     a.sidx = c->d_lsamp_idx.as<uint16_t>(); a.shash = c->d_lsamp_hash.as<uint32_t>();

@@ -52,7 +52,7 @@ void lane_share_index(bm_ctx* l, bm_ctx* c) {
     l->ktable_logg = c->ktable_logg; l->krows_logg = c->krows_logg;
     l->ktable_mode = c->d_krows.p ? 1 : 0;          // never build in the lane: use the parent's table or none
     l->ktable_max_bytes = c->ktable_max_bytes;
-    l->d_gidx_pos.view_of(c->d_gidx_pos); l->d_gidx_off.view_of(c->d_gidx_off); l->gidx_k = c->gidx_k;
+    l->d_gidx_pos.view_of(c->d_gidx_pos); l->d_gidx_off.view_of(c->d_gidx_off); l->gidx_k = c->gidx_k; l->gidx_lb = c->gidx_lb; l->gidx_bshift = c->gidx_bshift;
     l->gidx_mode = (c->d_gidx_pos.p && c->d_gidx_off.p) ? 1 : 0;
     l->ktiming = c->ktiming;
 }
