@@ -498,7 +498,7 @@ def main():
                                              "qualities + S coarse k-mer rows per strand (row bytes in use, not the "
                                              "padded stride) + 4 B per .qgram word read for the exact recount of "
                                              "passing groups; the kernel is issue-bound after these reductions (ncu: "
-                                             "IPC 2.75 of 4, DRAM ~50 %), see DESIGN.md section 4",
+                                             "IPC 2.7 of 4, DRAM ~55 %), see DESIGN.md section 4",
                      "reference_cascade_equivalent_gbs": (rows_gathered * W) / (vote_ms / vote_n * 1e-3) / 1e9 if vote_n else None},
         "roofline_qgram_path": dict(alt, peak=peak, frac=alt["achieved"] / peak) if alt else None,
         "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
