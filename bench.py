@@ -484,6 +484,8 @@ def main():
         "clocks": clk,
         "roofline": {"kernel": "k_map_fused" if ktable_k else "k_map_vote", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": (achieved / peak) if achieved else None, "traffic": traffic,
+                     "traffic_gbs": (traffic / (vote_ms / vote_n * 1e-3) / 1e9) if (traffic and vote_n) else None,
+                     "traffic_frac": (traffic / (vote_ms / vote_n * 1e-3) / 1e9 / peak) if (traffic and vote_n) else None,
                      "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes,
                      "ms_per_launch": vote_ms / vote_n if vote_n else None,
                      "rows_gathered_per_read": rows_gathered / max(1, n_reads),
@@ -497,8 +499,10 @@ def main():
                                              "bytes k_map_fused's loads ask for (counted in-kernel): the read's bases and "
                                              "qualities + S coarse k-mer rows per strand (row bytes in use, not the "
                                              "padded stride) + 4 B per .qgram word read for the exact recount of "
-                                             "passing groups; the kernel is issue-bound after these reductions (ncu: "
-                                             "IPC 2.7 of 4, DRAM ~55 %), see DESIGN.md section 4",
+                                             "passing groups; after these reductions the kernel sits at ~0.7 of both "
+                                             "limits at once (ncu: IPC 2.7 of 4 issue slots; DRAM traffic 19.6 kB per "
+                                             "read = traffic_frac of the measured copy peak: scattered 4-B words and "
+                                             "204-B rows cost whole sectors), see DESIGN.md section 4",
                      "reference_cascade_equivalent_gbs": (rows_gathered * W) / (vote_ms / vote_n * 1e-3) / 1e9 if vote_n else None},
         "roofline_qgram_path": dict(alt, peak=peak, frac=alt["achieved"] / peak) if alt else None,
         "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
