@@ -335,7 +335,11 @@ def main():
     n_reads = len(off) - 1
     setup_s = time.perf_counter() - t0
 
+    gatherer = None
+
     def barrier():
+        if gatherer is not None:
+            gatherer.wait()                      # collectives are issued by one thread at a time
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -349,16 +353,26 @@ def main():
         """N>1: location records of every rank -> rank 0 (NCCL gather; pinned host copy on a side stream)"""
         if world > 1:
             counts, locs = bmd.device_results(ctx, local)
-            return gatherer.gather(counts, locs)
+            gatherer.gather(counts, locs)
         return None
 
     # ---- device-resident steps ------------------------------------------------------------------------------------
     ctx.reads_upload(P, seq, qual, off)
 
+    trace = {} if os.environ.get("BM_GATHER_TRACE") else None
+
     def step_resident():
-        ctx.map_device(P)
-        ctx.locate_device(P, True)
-        gather()
+        if trace is None:
+            ctx.map_device(P)
+            ctx.locate_device(P, True)
+            gather()
+            return
+        t0 = time.perf_counter(); ctx.map_device(P)
+        t1 = time.perf_counter(); ctx.locate_device(P, True)
+        t2 = time.perf_counter(); gather()
+        t3 = time.perf_counter()
+        for k, v in (("map", t1 - t0), ("locate", t2 - t1), ("gather", t3 - t2)):
+            trace[k] = trace.get(k, 0.0) + v * 1e3
 
     for _ in range(a.warmup):
         step_resident()
@@ -367,6 +381,8 @@ def main():
     lidx_ms = ctx.kernel_stats()["locator_index"][0]    # one-off, inside the first (untimed) locator call
     ktable_k, ktable_bytes = ctx.index_kmer_table_info()
     ctx.kernel_stats_reset()
+    if trace is not None:
+        trace.clear(); bmd.TRACE.clear()
     barrier()
     clocks = ClockSampler(local)
     clocks.start()
@@ -384,6 +400,8 @@ def main():
     else:
         barrier()
     clk = clocks.stop()
+    if trace is not None:
+        print("[trace] rank %d host ms (warmup+timed): %s | gather phases: %s" % (rank, trace, bmd.TRACE), file=sys.stderr)
     kst = ctx.kernel_stats()
     _, _, mstats = ctx.map_download()
     tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
@@ -407,7 +425,7 @@ def main():
         if world > 1:
             counts = (t_ooff[1:] - t_ooff[:-1]).to(torch.int32).cuda(non_blocking=True)
             lb = t_olocs[:n_locs].cuda(non_blocking=True)
-            return gatherer.gather(counts, lb)
+            gatherer.gather(counts, lb)
         return None
 
     if world > 1:
@@ -474,7 +492,7 @@ def main():
                    "reads_per_gpu_per_step": n_reads,
                    "read_len": cfg["read_len"], "flags": "-k 9 -l 12 -s 15 -e 0.4 -p 10 -f %g" % cfg["frac"],
                    "parallelism": f"reads sharded x{world}, index replicated",
-                   "timing": "CUDA events on the library stream" if world == 1 else "wall clock between device-synchronised barriers (NCCL gather of the records to rank 0's device inside the step), max over ranks",
+                   "timing": "CUDA events on the library stream" if world == 1 else "wall clock between device-synchronised barriers (NCCL send/recv of each batch's records to rank 0's device inside the step), max over ranks",
                    "l2": "inputs larger than L2 (bit matrix %d MB vs 126 MB L2)" % (n_rows * W >> 20),
                    "locator": "genome k-mer position index (K3i)" if a.lidx else "bucket text scan (K3)",
                    "step": "bm_map_device + bm_locate_device(filter_best=1)" + (" + NCCL gather" if world > 1 else "")},

@@ -5,11 +5,19 @@ or loaded on rank 0, and one variable-length gather of the fixed-size location r
 inside the per-read work, so there is nothing to fuse.  Works with the nccl backend (device tensors that alias the
 library's buffers) and with gloo (CPU tensors; used by the world_size-2 CPU tests).
 """
+import contextlib
+import os
+import threading
+import time
+
 import numpy as np
 import torch
 import torch.distributed as dist
 
 from . import LOC_DTYPE
+
+
+TRACE = {} if os.environ.get("BM_GATHER_TRACE") else None     # per-phase host milliseconds of LocationGatherer.gather
 
 
 class _DevMem:
@@ -44,56 +52,112 @@ def broadcast_index(ctx, k2i, q, n_rows, NB, device, src=0, group=None, chunk=1 
 
 class LocationGatherer:
     """Variable-length gather of per-read location lists to rank `dst`, in global read order (shards are contiguous, so
-    rank order is read order).  Buffers persist across calls: one fixed-capacity padded send buffer per rank, one
-    [world, cap] receive buffer on dst (grown on demand), so a step costs one tiny all_gather of the record counts, one
-    gather of the per-read counts, one gather of the records -- NCCL over NVLink when the tensors are on the GPU, gloo
-    on CPU tensors in the tests -- then a device-side prefix sum / compaction and, on CUDA, an asynchronous copy of the
-    result into pinned host memory on a side stream (wait() before reading it; host_copy=False leaves the gathered
-    records on dst's device)."""
+    rank order is read order; shards may differ in size).  Every rank copies its records into a persistent send buffer
+    and sends dst a two-word header (records, reads); dst reads the headers -- its only host synchronisation, the
+    other ranks have none -- and receives each rank's per-read counts and records directly at their final offsets in
+    the result, so there is no padding and no compaction pass.  Point-to-point sends / receives: NCCL over NVLink when
+    the tensors are on the GPU, gloo on CPU tensors in the tests.  A prefix sum gives loc_off; on CUDA the result is
+    copied into pinned host memory on a side stream (wait() before reading it; host_copy=False leaves it on dst's
+    device).  `dst` is a global rank.
+
+    gather() runs the exchange on the calling thread.  gather_async() stages the records (after which the library may
+    overwrite its result buffers) and hands the exchange to a worker thread; wait() joins it.  Note that on the device
+    the exchange does not overlap a running mapper kernel, whatever the stream priorities: the mapper fills every SM
+    and the small NCCL / copy kernels are only dispatched once its grid is exhausted (measured).
+    Collectives are issued by one thread at a time, in call order, on every rank."""
 
     def __init__(self, dst=0, group=None, host_copy=True):
         self.dst, self.group, self.host_copy = dst, group, host_copy
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
-        self.cap = 0
-        self.send = self.recv = self.cnt_recv = None
+        self.send = self.cnt_send = None
         self.side = None
         self.h_off = self.h_locs = None
         self.result = None
+        self.worker = None
+        self.worker_error = None
+        self.hp = None                # high-priority CUDA stream of the staging copies and the exchange
 
-    def _ensure(self, cap, n_reads, device, rec):
-        if cap > self.cap or self.send is None or self.send.device != device:
-            self.cap = int(cap * 1.25) + 1024
-            self.send = torch.zeros((self.cap, rec), dtype=torch.uint8, device=device)
-            self.recv = (torch.empty((self.world, self.cap, rec), dtype=torch.uint8, device=device)
-                         if self.rank == self.dst else None)
-        if self.rank == self.dst and (self.cnt_recv is None or self.cnt_recv.shape[1] != n_reads
-                                      or self.cnt_recv.device != device):
-            self.cnt_recv = torch.empty((self.world, n_reads), dtype=torch.int32, device=device)
+    def _stream(self, device):
+        """Everything the gatherer enqueues runs on one high-priority stream (and NCCL's stream is created with high
+        priority, see init_process_group in bench.py): the block scheduler otherwise dispatches the small copy / NCCL /
+        compaction kernels only after the whole grid of a mapper kernel that was launched before them."""
+        if device.type != "cuda":
+            return contextlib.nullcontext()
+        if self.hp is None:
+            self.hp = torch.cuda.Stream(device, priority=-1)
+        return torch.cuda.stream(self.hp)
 
-    def gather(self, counts, locs_bytes):
-        """counts: int32 [n_reads_local] (equal n_reads_local on every rank, or use gather_variable-based
-        gather_locations); locs_bytes: uint8 [n_locs_local, rec].  Returns (loc_off, locs) handles on dst -- device
-        tensors whose pinned host copies are filled asynchronously -- and None elsewhere."""
-        device, rec = counts.device, locs_bytes.shape[1]
-        n = torch.tensor([locs_bytes.shape[0]], dtype=torch.int64, device=device)
-        sizes = [torch.zeros_like(n) for _ in range(self.world)]
-        dist.all_gather(sizes, n, group=self.group)
-        sizes = torch.cat(sizes).tolist()
-        self._ensure(max(sizes), counts.shape[0], device, rec)
-        self.send[:locs_bytes.shape[0]] = locs_bytes
-        if self.rank == self.dst:
-            dist.gather(counts, list(self.cnt_recv.unbind(0)), dst=self.dst, group=self.group)
-            dist.gather(self.send, list(self.recv.unbind(0)), dst=self.dst, group=self.group)
-        else:
-            dist.gather(counts, None, dst=self.dst, group=self.group)
-            dist.gather(self.send, None, dst=self.dst, group=self.group)
+    # -- step 1, on the caller's thread: the rank's records into persistent send buffers ------------------------------
+    def _stage(self, counts, locs_bytes):
+        device, rec, n = counts.device, locs_bytes.shape[1], locs_bytes.shape[0]
+        if self.send is None or self.send.device != device or self.send.shape[0] < n or self.send.shape[1] != rec:
+            self.send = torch.zeros((int(n * 1.25) + 1024, rec), dtype=torch.uint8, device=device)
+        if self.cnt_send is None or self.cnt_send.device != device or self.cnt_send.shape[0] != counts.shape[0]:
+            self.cnt_send = torch.empty(counts.shape[0], dtype=torch.int32, device=device)
+        with self._stream(device):
+            if device.type == "cuda":
+                self.hp.wait_stream(torch.cuda.current_stream(device))     # counts / locs_bytes were produced there
+            self.send[:n] = locs_bytes
+            self.cnt_send.copy_(counts)
+            if device.type == "cuda":
+                counts.record_stream(self.hp); locs_bytes.record_stream(self.hp)
+                self.hp.synchronize()                  # the caller's buffers may be reused from here on
+        return n
+
+    # -- step 2: headers to dst, then every rank's counts and records straight into their place in dst's result ----------
+    def _exchange(self, n):
+        with self._stream(self.send.device):
+            return self._exchange_on_stream(n)
+
+    def _p2p(self, ops):
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()                         # stream-level on NCCL, blocking on gloo
+
+    def _exchange_on_stream(self, n):
+        device, rec = self.send.device, self.send.shape[1]
+        n_reads = self.cnt_send.shape[0]
+        t0 = time.perf_counter()
+        hdr = torch.tensor([n, n_reads], dtype=torch.int64, device=device)
+        if self.rank != self.dst:
+            # no host synchronisation on this side: three sends are enqueued and the rank goes on with its next batch
+            self._p2p([dist.P2POp(dist.isend, hdr, self.dst, self.group)])
+            ops = [dist.P2POp(dist.isend, self.cnt_send, self.dst, self.group)] if n_reads else []
+            if n:
+                ops.append(dist.P2POp(dist.isend, self.send[:n], self.dst, self.group))
+            self._p2p(ops)
+            self.result = None
             return None
-        total = sum(sizes)
-        off = torch.zeros(self.cnt_recv.numel() + 1, dtype=torch.int64, device=device)
-        torch.cumsum(self.cnt_recv.view(-1), 0, out=off[1:])
-        locs = torch.cat([self.recv[r, :sizes[r]] for r in range(self.world)]) if total else self.recv[0, :0]
+        hdrs = torch.zeros((self.world, 2), dtype=torch.int64, device=device)
+        hdrs[self.dst] = hdr
+        self._p2p([dist.P2POp(dist.irecv, hdrs[r], r, self.group) for r in range(self.world) if r != self.dst])
+        h = hdrs.tolist()                        # the one host synchronisation of the exchange (dst only)
+        t1 = time.perf_counter()
+        sizes, reads = [int(x[0]) for x in h], [int(x[1]) for x in h]
+        total, total_reads = sum(sizes), sum(reads)
+        cnt = torch.empty(total_reads, dtype=torch.int32, device=device)
+        locs = torch.empty((total, rec), dtype=torch.uint8, device=device)
+        ops, o, l = [], 0, 0
+        for r in range(self.world):
+            if r == self.dst:
+                cnt[o:o + reads[r]] = self.cnt_send
+                locs[l:l + sizes[r]] = self.send[:n]
+            else:
+                if reads[r]:
+                    ops.append(dist.P2POp(dist.irecv, cnt[o:o + reads[r]], r, self.group))
+                if sizes[r]:
+                    ops.append(dist.P2POp(dist.irecv, locs[l:l + sizes[r]], r, self.group))
+            o += reads[r]; l += sizes[r]
+        self._p2p(ops)
+        off = torch.zeros(total_reads + 1, dtype=torch.int64, device=device)
+        torch.cumsum(cnt, 0, out=off[1:])
+        if TRACE is not None:
+            t2 = time.perf_counter()
+            for k, v in (("headers", t1 - t0), ("enqueue", t2 - t1)):
+                TRACE[k] = TRACE.get(k, 0.0) + v * 1e3
+            TRACE["n"] = TRACE.get("n", 0) + 1
         if device.type == "cuda" and not self.host_copy:
-            self.result = None                     # results stay on dst's device, like a single GPU's resident results
+            self.result = (off, locs, False)       # results stay on dst's device, like a single GPU's resident results
             return (off, locs)
         if device.type == "cuda":
             if self.side is None:
@@ -107,18 +171,57 @@ class LocationGatherer:
                 self.h_off[:off.numel()].copy_(off, non_blocking=True)
                 self.h_locs[:total].copy_(locs, non_blocking=True)
                 off.record_stream(self.side); locs.record_stream(self.side)
-            self.result = (self.h_off[:off.numel()], self.h_locs[:total])
+            self.result = (self.h_off[:off.numel()], self.h_locs[:total], True)
         else:
-            self.result = (off, locs)
-        return self.result
+            self.result = (off, locs, True)
+        return self.result[:2]
+
+    def gather(self, counts, locs_bytes):
+        """counts: int32 [n_reads_local] (equal n_reads_local on every rank, or use gather_variable-based
+        gather_locations); locs_bytes: uint8 [n_locs_local, rec].  Returns (loc_off, locs) handles on dst -- device
+        tensors, or their pinned host copies filled asynchronously -- and None elsewhere."""
+        self._join()
+        return self._exchange(self._stage(counts, locs_bytes))
+
+    def gather_async(self, counts, locs_bytes):
+        """as gather(), with the exchange on a worker thread; returns once the records are staged.  wait() (or the next
+        gather) joins the worker."""
+        self._join()
+        n = self._stage(counts, locs_bytes)
+        device = self.send.device
+
+        def run():
+            try:
+                if device.type == "cuda":
+                    torch.cuda.set_device(device)
+                self._exchange(n)
+            except BaseException as e:      # surfaced by _join on the caller's thread
+                self.worker_error = e
+
+        self.worker = threading.Thread(target=run, name="bm-gather", daemon=True)
+        self.worker.start()
+
+    def _join(self):
+        if self.worker is not None:
+            self.worker.join()
+            self.worker = None
+        if self.worker_error is not None:
+            e, self.worker_error = self.worker_error, None
+            raise e
 
     def wait(self):
-        """host arrays (loc_off uint32[n_total+1], locs LOC_DTYPE[n]) of the last gather on dst"""
-        if self.result is None:
+        """joins a pending gather_async; on dst returns the host arrays (loc_off uint32[n_total+1], locs LOC_DTYPE[n]) of
+        the last gather when it kept a host copy, else None"""
+        self._join()
+        if self.hp is not None:
+            self.hp.synchronize()                     # device-resident results are complete from here on
+        if self.result is None or not self.result[2]:
             return None
+        if self.hp is not None:
+            self.hp.synchronize()
         if self.side is not None:
             self.side.synchronize()
-        off, locs = self.result
+        off, locs = self.result[:2]
         return (off.numpy().astype(np.uint32),
                 locs.numpy().reshape(-1, LOC_DTYPE.itemsize).view(LOC_DTYPE).reshape(-1))
 

@@ -43,8 +43,8 @@ def _worker(rank, world, port, n_reads, out_dir):
     my_locs = locs[off[lo]:off[hi]]
     my_bytes = torch.from_numpy(my_locs.view(np.uint8).reshape(-1, bm.LOC_DTYPE.itemsize).copy())
     res = bmd.gather_locations(my_counts, my_bytes, dst=0)
-    if n_reads % world == 0:
-        # equal shards: the persistent-buffer gatherer the bench uses gives the same, twice in a row
+    if True:
+        # the persistent-buffer gatherer the bench uses gives the same, twice in a row (shards of any size)
         g = bmd.LocationGatherer(dst=0)
         for _ in range(2):
             r2 = g.gather(my_counts, my_bytes)
@@ -52,6 +52,23 @@ def _worker(rank, world, port, n_reads, out_dir):
         if rank == 0:
             o2, l2 = g.wait()
             assert np.array_equal(o2, res[0]) and np.array_equal(l2, res[1])
+        # the overlapped form: records are staged before gather_async returns (the caller's buffers are then scribbled
+        # over, as the library does with the next batch); a growing batch re-sizes the agreed capacity
+        for rep in (1, 3, 2):
+            c_rep, b_rep = my_counts.repeat(rep), my_bytes.repeat(rep, 1)
+            g.gather_async(c_rep, b_rep)
+            c_rep.zero_(); b_rep.fill_(255)
+            got = g.wait()
+            assert (got is None) == (rank != 0)
+            if rank == 0:
+                # expected: every rank's shard repeated rep times, in rank order
+                exp_cnt, exp_locs = [], []
+                for r in range(world):
+                    rlo, rhi = bmd.shard_bounds(n_reads, r, world)
+                    exp_cnt.append(np.tile(counts[rlo:rhi], rep))
+                    exp_locs.append(np.tile(locs[off[rlo]:off[rhi]], rep))
+                exp_off = np.concatenate([[0], np.cumsum(np.concatenate(exp_cnt))]).astype(np.uint32)
+                assert np.array_equal(got[0], exp_off) and np.array_equal(got[1], np.concatenate(exp_locs))
     if rank == 0:
         g_off, g_locs = res
         np.save(os.path.join(out_dir, "off.npy"), g_off)
