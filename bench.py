@@ -12,11 +12,13 @@ best-location merge K3b) over one batch of synthetic reads.  Workload at any N: 
             loads ask for, counted in the kernel; time = CUDA events around each launch inside the timed region.
             roofline_qgram_path: the same for k_map_vote, the full-width q-gram row gather used when the coarse k-mer
             table is off or does not fit (measured in the same run, outside the timed region)
-  cpu_baseline / --impl reference: the CPU restatement of the reference (oracle/, "port") on the host cores, on a
-            bounded sample of the same workload
-
-The reference itself (SeqAn3-based, single-threaded) cannot be built here; `--impl reference` times
-oracle/_ref when it exists, else the oracle port with all host threads.
+  cpu_baseline / --impl reference: the reference's CPU implementation of the path on the host cores, on a bounded
+            sample of the same workload: oracle/_ref (the reference's own main.cpp and headers, built from
+            /root/reference against the test-only seqan3 shim; "reference") as one single-threaded process per core,
+            else the plain C++ restatement under oracle/ with all host threads ("port")
+  N > 1     reads sharded over the ranks, index replicated; each step ends with the gather of the location records
+            to rank 0's device (bucket-map_b200/dist.py); wall clock between device-synchronised barriers, max over
+            ranks
 """
 import argparse
 import json
