@@ -66,7 +66,7 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
     static const bool trace = getenv("BM_PIPE_TRACE") != nullptr;
     const auto t_begin = std::chrono::steady_clock::now();
     auto since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count(); };
-    double t_enq = 0, t_h2d = 0, t_fin = 0, t_loc = 0;
+    double t_pre = 0, t_first = 0, t_enq = 0, t_h2d = 0, t_fin = 0, t_loc = 0;
     if (!c->copy_stream) BM_CK(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
 
     // Chunk schedule: large chunks first (every chunk costs five small table copies on top of its two large ones, and the
@@ -86,35 +86,50 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
         BM_CK(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         c->chunk_ev.push_back(e);
     }
-    int r = bm_internal_reads_begin(c, p, read_off, n_reads);
-    if (r) return r;
-    // segments are at most read_len long (q_gram_mapper.h:521), which bounds the sampler's shared memory up front
-    const uint32_t msl = p->read_len;
-    r = bm_internal_map_begin(c, p, c->n_seg_total, msl);   // K0 + buffers for the whole batch
-    if (r) return r;
+    // The link is the bottleneck: the bases and qualities of a chunk need nothing from the host-side tables, so their
+    // copies are enqueued first (chunk 0's before anything else is prepared) and the segment tables of the chunk are
+    // built while they are in flight.
+    const uint64_t base = read_off[0];
+    if (read_off[n_reads] < base) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
+    BM_CK(c, c->d_seq.ensure(read_off[n_reads] - base + 16));
+    BM_CK(c, c->d_qual.ensure(read_off[n_reads] - base + 16));
     // the copy stream must not overwrite buffers an earlier call's kernels may still read
     BM_CK(c, cudaStreamSynchronize(c->stream));
-
-    const uint64_t base = read_off[0];
-    uint8_t *d_seq = c->d_seq.as<uint8_t>(), *d_qual = c->d_qual.as<uint8_t>();
     if (wait_for) {
         int st;
         while ((st = wait_for->h2d_state.load(std::memory_order_acquire)) == 0) std::this_thread::yield();
         if (st < 0) BM_FAIL(c, BM_E_ARG, "bm_map_locate: the first lane failed");
         BM_CK(c, cudaStreamWaitEvent(c->copy_stream, wait_for->h2d_done, 0));
     }
+    auto copy_text = [&](uint32_t j) -> int {
+        const uint32_t r0 = bounds[j], r1 = bounds[j + 1];
+        if (read_off[r0] < base || read_off[r1] < read_off[r0] || read_off[r1] > read_off[n_reads])
+            BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
+        const uint64_t b0 = read_off[r0] - base, nb = read_off[r1] - read_off[r0];
+        if (nb) {
+            BM_CK(c, cudaMemcpyAsync(c->d_seq.as<uint8_t>() + b0, seq + base + b0, nb, cudaMemcpyHostToDevice, c->copy_stream));
+            BM_CK(c, cudaMemcpyAsync(c->d_qual.as<uint8_t>() + b0, qual + base + b0, nb, cudaMemcpyHostToDevice, c->copy_stream));
+        }
+        return BM_OK;
+    };
+    int r = copy_text(0);
+    if (r) return r;
+    r = bm_internal_reads_begin(c, p, read_off, n_reads);
+    if (r) { cudaStreamSynchronize(c->copy_stream); return r; }
+    // segments are at most read_len long (q_gram_mapper.h:521), which bounds the sampler's shared memory up front
+    const uint32_t msl = p->read_len;
+    r = bm_internal_map_begin(c, p, c->n_seg_total, msl);   // K0 + buffers for the whole batch
+    if (r) { cudaStreamSynchronize(c->copy_stream); return r; }
+    t_pre = since();
     for (uint32_t j = 0; j < n_chunks; j++) {
         const uint32_t r0 = bounds[j], r1 = bounds[j + 1];
         const uint32_t s0 = c->n_seg;
+        if (j == 1) t_first = since();
+        if (j) { r = copy_text(j); if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; } }
         r = bm_internal_build_segments(c, p, read_off, r0, r1);
         if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; }
         const uint32_t s1 = c->n_seg;
-        const uint64_t b0 = read_off[r0] - base, nb = read_off[r1] - read_off[r0];
         cudaStream_t cs = c->copy_stream;
-        if (nb) {
-            BM_CK(c, cudaMemcpyAsync(d_seq + b0, seq + base + b0, nb, cudaMemcpyHostToDevice, cs));
-            BM_CK(c, cudaMemcpyAsync(d_qual + b0, qual + base + b0, nb, cudaMemcpyHostToDevice, cs));
-        }
         // read r1's offset / first segment are rewritten by the next chunk with the same values
         BM_CK(c, cudaMemcpyAsync(c->d_read_off.as<uint64_t>() + r0, c->h_off_rel.as<uint64_t>() + r0, (size_t)(r1 - r0 + 1) * 8,
                                  cudaMemcpyHostToDevice, cs));
@@ -147,8 +162,8 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
     if (stats) BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 8 * 8, cudaMemcpyDeviceToHost, c->stream));
     if (!publish && !wait_for) {
         r = bm_locate_download(c, loc_off, locs, loc_cap);
-        if (trace) fprintf(stderr, "[pipe] reads %u: enqueued %.2f  h2d done %.2f  map+finish %.2f  locate %.2f  download %.2f ms\n",
-                           n_reads, t_enq, t_h2d, t_fin, t_loc, since());
+        if (trace) fprintf(stderr, "[pipe] reads %u: loop entered %.2f  first chunk enqueued %.2f  all enqueued %.2f  h2d done %.2f  map+finish %.2f  locate %.2f  download %.2f ms\n",
+                           n_reads, t_pre, t_first, t_enq, t_h2d, t_fin, t_loc, since());
         return r;
     }
     // one of two lanes: lane 0 announces how many records it has, lane 1 appends its own behind them
