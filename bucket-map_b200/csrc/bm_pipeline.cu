@@ -59,6 +59,18 @@ void lane_share_index(bm_ctx* l, bm_ctx* c) {
 }  // namespace
 
 namespace {
+// segment tables of reads [r0, r1) when every read is one segment (q_gram_mapper.h:517-522 with |read| <= 2r)
+__global__ void k_unit_segments(const uint64_t* __restrict__ read_off, uint32_t r0, uint32_t r1, uint32_t read_len,
+                                uint32_t* __restrict__ seg_read, uint32_t* __restrict__ seg_start,
+                                uint32_t* __restrict__ seg_len, uint32_t* __restrict__ read_seg0) {
+    const uint32_t i = r0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= r1) return;
+    const uint64_t len = read_off[i + 1] - read_off[i];
+    seg_read[i] = i; seg_start[i] = 0u; seg_len[i] = len < read_len ? (uint32_t)len : read_len;
+    read_seg0[i] = i;
+    if (i + 1 == r1) read_seg0[r1] = r1;
+}
+
 int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
                  uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats,
                  LaneLink* publish, LaneLink* wait_for, uint64_t* n_out) {
@@ -120,6 +132,9 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
     const uint32_t msl = p->read_len;
     r = bm_internal_map_begin(c, p, c->n_seg_total, msl);   // K0 + buffers for the whole batch
     if (r) { cudaStreamSynchronize(c->copy_stream); return r; }
+    // no read longer than 2r in the batch: one segment per read, segment index == read index, and the four segment
+    // tables (16 B per read of link time) are written by a kernel from the read offsets instead of being copied
+    const bool unit_segments = c->n_seg_total == n_reads;
     t_pre = since();
     for (uint32_t j = 0; j < n_chunks; j++) {
         const uint32_t r0 = bounds[j], r1 = bounds[j + 1];
@@ -133,9 +148,10 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
         // read r1's offset / first segment are rewritten by the next chunk with the same values
         BM_CK(c, cudaMemcpyAsync(c->d_read_off.as<uint64_t>() + r0, c->h_off_rel.as<uint64_t>() + r0, (size_t)(r1 - r0 + 1) * 8,
                                  cudaMemcpyHostToDevice, cs));
-        BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.as<uint32_t>() + r0, c->h_read_seg0.as<uint32_t>() + r0, (size_t)(r1 - r0 + 1) * 4,
-                                 cudaMemcpyHostToDevice, cs));
-        if (s1 > s0) {
+        if (!unit_segments)
+            BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.as<uint32_t>() + r0, c->h_read_seg0.as<uint32_t>() + r0, (size_t)(r1 - r0 + 1) * 4,
+                                     cudaMemcpyHostToDevice, cs));
+        if (s1 > s0 && !unit_segments) {
             const size_t n4 = (size_t)(s1 - s0) * 4;
             BM_CK(c, cudaMemcpyAsync(c->d_seg_read.as<uint32_t>() + s0, c->h_seg_read.as<uint32_t>() + s0, n4, cudaMemcpyHostToDevice, cs));
             BM_CK(c, cudaMemcpyAsync(c->d_seg_start.as<uint32_t>() + s0, c->h_seg_start.as<uint32_t>() + s0, n4, cudaMemcpyHostToDevice, cs));
@@ -143,6 +159,12 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
         }
         BM_CK(c, cudaEventRecord(c->chunk_ev[j], cs));
         BM_CK(c, cudaStreamWaitEvent(c->stream, c->chunk_ev[j], 0));
+        if (unit_segments && r1 > r0) {
+            k_unit_segments<<<(r1 - r0 + 255) / 256, 256, 0, c->stream>>>(
+                c->d_read_off.as<uint64_t>(), r0, r1, p->read_len, c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(),
+                c->d_seg_len.as<uint32_t>(), c->d_read_seg0.as<uint32_t>());
+            BM_CK(c, cudaGetLastError());
+        }
         r = bm_internal_map_range(c, p, s0, s1, msl);                               // K2a + K2 on this chunk
         if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; }
     }
