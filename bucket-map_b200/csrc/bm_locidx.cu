@@ -121,10 +121,24 @@ k_locate_idx(const IdxArgs a) {
                 const uint64_t end = start + npos;
                 const uint32_t c0 = comp_key(h, (uint32_t)start, a.lb, a.bshift), c1 = comp_key(h, (uint32_t)(end - 1), a.lb, a.bshift);
                 const uint32_t o0 = __ldg(a.off + c0), o1 = __ldg(a.off + c1 + 1);
-                if (o0 != o1) {
+                if (o1 - o0 > 4u) {
                     x0 = lb_pos(a.pos, o0, o1, start);
                     x1 = x0;
                     while (x1 < o1 && (uint64_t)__ldg(a.pos + x1) < end) x1++;
+                } else if (o0 != o1) {
+                    // the usual case, a handful of entries in the block(s): fetch them side by side instead of a
+                    // binary search and a walk of dependent loads; the entries inside [start, end) are contiguous
+                    uint32_t v[4];
+#pragma unroll
+                    for (uint32_t t = 0; t < 4; t++) v[t] = (o0 + t < o1) ? __ldg(a.pos + o0 + t) : 0xFFFFFFFFu;
+                    uint32_t below = 0, inside = 0;
+#pragma unroll
+                    for (uint32_t t = 0; t < 4; t++) {
+                        const bool live = o0 + t < o1;
+                        below += (live && (uint64_t)v[t] < start) ? 1u : 0u;
+                        inside += (live && (uint64_t)v[t] >= start && (uint64_t)v[t] < end) ? 1u : 0u;
+                    }
+                    x0 = o0 + below; x1 = x0 + inside;
                 }
             }
         }
