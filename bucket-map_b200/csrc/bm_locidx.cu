@@ -87,7 +87,7 @@ constexpr uint32_t kMaxP = 64;
 
 __global__ void __launch_bounds__(kIdxThreads)
 k_locate_idx(const IdxArgs a) {
-    __shared__ uint32_t s_x0[kCandPerCta][kMaxP], s_x1[kCandPerCta][kMaxP], s_cur[kCandPerCta][kMaxP];
+    __shared__ uint32_t s_x0[kCandPerCta][kMaxP], s_x1[kCandPerCta][kMaxP], s_cur[kCandPerCta][kMaxP], s_p0[kCandPerCta][kMaxP];
     __shared__ int32_t s_vp[kCandPerCta][kVCi];
     __shared__ uint32_t s_vc[kCandPerCta][kVCi];
     const uint32_t tid = threadIdx.x, grp = tid / kSub, sub = tid % kSub;
@@ -109,7 +109,7 @@ k_locate_idx(const IdxArgs a) {
         }
     }
     for (uint32_t i = sub; i < P; i += kSub) {                          // bucket_locator.h:233-243
-        uint32_t x0 = 0, x1 = 0, cur = 0;
+        uint32_t x0 = 0, x1 = 0, cur = 0, p0 = 0;                       // p0: the run's last entry, the first one voted on
         if (valid && !phantom && npos) {
             const uint32_t si = reverse ? P - 1 - i : i;
             uint32_t h = a.shash[(size_t)seg * P + si];
@@ -125,6 +125,7 @@ k_locate_idx(const IdxArgs a) {
                     x0 = lb_pos(a.pos, o0, o1, start);
                     x1 = x0;
                     while (x1 < o1 && (uint64_t)__ldg(a.pos + x1) < end) x1++;
+                    if (x1 > x0) p0 = __ldg(a.pos + x1 - 1);
                 } else if (o0 != o1) {
                     // the usual case, a handful of entries in the block(s): fetch them side by side instead of a
                     // binary search and a walk of dependent loads; the entries inside [start, end) are contiguous
@@ -136,13 +137,15 @@ k_locate_idx(const IdxArgs a) {
                     for (uint32_t t = 0; t < 4; t++) {
                         const bool live = o0 + t < o1;
                         below += (live && (uint64_t)v[t] < start) ? 1u : 0u;
-                        inside += (live && (uint64_t)v[t] >= start && (uint64_t)v[t] < end) ? 1u : 0u;
+                        const bool in = live && (uint64_t)v[t] >= start && (uint64_t)v[t] < end;
+                        inside += in ? 1u : 0u;
+                        if (in) p0 = v[t];                              // ascending: the last one inside stays
                     }
                     x0 = o0 + below; x1 = x0 + inside;
                 }
             }
         }
-        s_x0[grp][i] = x0; s_x1[grp][i] = x1; s_cur[grp][i] = cur;
+        s_x0[grp][i] = x0; s_x1[grp][i] = x1; s_cur[grp][i] = cur; s_p0[grp][i] = p0;
     }
     __syncwarp();
     if (sub != 0 || !valid) return;
@@ -154,7 +157,8 @@ k_locate_idx(const IdxArgs a) {
         const uint32_t x0 = s_x0[grp][i], x1 = s_x1[grp][i], cur = s_cur[grp][i];
         const bool first_mode = nv == 0;
         for (uint32_t x = x1; x > x0 && !over; x--) {                   // equal_range order: largest offset first
-            const int32_t position = (int32_t)((uint32_t)((uint64_t)__ldg(a.pos + x - 1) - start) - cur);
+            const uint32_t gp = (x == x1) ? s_p0[grp][i] : __ldg(a.pos + x - 1);
+            const int32_t position = (int32_t)((uint32_t)((uint64_t)gp - start) - cur);
             uint32_t e = 0;
             bool voted = false;
             if (first_mode) {
