@@ -32,7 +32,7 @@ oracle/libbm_oracle.so: oracle/bm_oracle.cpp oracle/bm_oracle.h
 	$(CXX) -O3 -std=c++17 -fPIC -shared -pthread -o $@ oracle/bm_oracle.cpp
 
 HOST_SRCS := $(wildcard $(PKG)/host/*.cpp)
-HOST_HDRS := $(wildcard $(PKG)/host/*.h)
+HOST_HDRS := $(wildcard $(PKG)/host/*.hpp) include/bucketmap_b200.h
 
 tools: $(PKG)/bin/bucketmap $(PKG)/bin/bucketmap_align
 

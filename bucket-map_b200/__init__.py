@@ -13,9 +13,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbucketmap_b200.so")
 
 (K_ROWPOP, K_INDEX, K_SAMPLE, K_MAP, K_LOCSAMPLE, K_LOCATE, K_MERGE, K_ALIGN, K_AUX, K_KTABLE, K_GIDX, K_LOCSCAN,
- K_MAPOVER, K_COUNT) = range(14)
+ K_MAPOVER, K_PACK, K_COUNT) = range(15)
 KERNEL_NAMES = ["rowpop", "index_build", "map_sample", "map_vote", "loc_sample", "locate", "merge", "align", "aux",
-                "kmer_table", "locator_index", "locate_scan", "map_vote_handover"]
+                "kmer_table", "locator_index", "locate_scan", "map_vote_handover", "pack_reads"]
 
 
 class Params(C.Structure):
@@ -53,6 +53,14 @@ SIGNATURES = {
     "bm_index_kmer_table": (C.c_int, [_vp, C.c_int, C.c_uint64]),
     "bm_index_kmer_table_info": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
     "bm_map_handover": (C.c_int, [_vp, C.c_int]),
+    "bm_index_fine_table": (C.c_int, [_vp, C.c_int]),
+    "bm_index_fine_table_info": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
+    "bm_pack_layout": (C.c_int, [_vp, C.c_uint32, _vp]),
+    "bm_pack_reads": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _vp, _vp,
+                                C.POINTER(C.c_uint32)]),
+    "bm_reads_upload_packed": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, _vp, C.c_uint32]),
+    "bm_map_locate_packed": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, _vp, C.c_uint32, C.c_int, _vp, _vp,
+                                       C.c_uint64, _vp]),
     "bm_index_free": (C.c_int, [_vp]),
     "bm_locator_index": (C.c_int, [_vp, C.c_int]),
     "bm_index_alloc": (C.c_int, [_vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32]),
@@ -101,6 +109,24 @@ def load_library(path=LIB_PATH):
 
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(_vp)
+
+
+def pack_reads(lib, seq, qual, read_off, k, b, threads=1):
+    """host-side packer (bm_pack_layout + bm_pack_reads): returns (planes uint64, qk uint32, pl_off uint32, n_low)"""
+    n = len(read_off) - 1
+    read_off = np.ascontiguousarray(read_off, np.uint64)
+    pl_off = np.empty(n + 1, np.uint32)
+    rc = lib.bm_pack_layout(_ptr(read_off), n, _ptr(pl_off))
+    if rc:
+        raise BucketMapError(f"bm_pack_layout failed ({rc})")
+    planes = np.zeros(int(pl_off[n]) + 1, np.uint64)
+    qk = np.zeros(int(pl_off[n]) + 1, np.uint32)
+    low = C.c_uint32()
+    rc = lib.bm_pack_reads(_ptr(seq), _ptr(qual), _ptr(read_off), _ptr(pl_off), 0, n, k, b, _ptr(planes), _ptr(qk),
+                           C.byref(low))
+    if rc:
+        raise BucketMapError(f"bm_pack_reads failed ({rc})")
+    return planes, qk, pl_off, low.value
 
 
 def default_params(lib, bucket_len, **kw):
@@ -186,6 +212,16 @@ class Context:
         self._ck(self.lib.bm_index_kmer_table_info(self.h, C.byref(k), C.byref(n)), "bm_index_kmer_table_info")
         return k.value, n.value
 
+    def index_fine_table(self, mode):
+        """0: passing groups are recounted from the .qgram words; 1 (default): from the full-resolution k-mer table when
+        it fits"""
+        self._ck(self.lib.bm_index_fine_table(self.h, mode), "bm_index_fine_table")
+
+    def index_fine_table_info(self):
+        k, n = C.c_uint32(), C.c_uint64()
+        self._ck(self.lib.bm_index_fine_table_info(self.h, C.byref(k), C.byref(n)), "bm_index_fine_table_info")
+        return k.value, n.value
+
     def map_handover(self, max_groups):
         """lists with more than max_groups passing coarse groups go to the full-width gather (-1: default)"""
         self._ck(self.lib.bm_map_handover(self.h, max_groups), "bm_map_handover")
@@ -216,6 +252,14 @@ class Context:
         self.n_reads = len(read_off) - 1
         self._ck(self.lib.bm_reads_upload(self.h, C.byref(P), _ptr(seq), _ptr(qual), _ptr(read_off), self.n_reads),
                  "bm_reads_upload")
+        n = C.c_uint32()
+        self._ck(self.lib.bm_reads_segments(self.h, C.byref(n), None, None, None), "bm_reads_segments")
+        self.n_seg = n.value
+
+    def reads_upload_packed(self, P, planes, qk, pl_off, read_off):
+        self.n_reads = len(read_off) - 1
+        self._ck(self.lib.bm_reads_upload_packed(self.h, C.byref(P), _ptr(planes), _ptr(qk), _ptr(pl_off), _ptr(read_off),
+                                                 self.n_reads), "bm_reads_upload_packed")
         n = C.c_uint32()
         self._ck(self.lib.bm_reads_segments(self.h, C.byref(n), None, None, None), "bm_reads_segments")
         self.n_seg = n.value
@@ -299,6 +343,16 @@ class Context:
         self._ck(self.lib.bm_map_locate(self.h, C.byref(P), _ptr(seq), _ptr(qual), _ptr(read_off), n,
                                         int(filter_best), _ptr(out_off), _ptr(out_locs), len(out_locs), _ptr(stats)),
                  "bm_map_locate")
+        self.n_reads = n
+        return int(out_off[n]), stats
+
+    def map_locate_packed_into(self, P, planes, qk, pl_off, read_off, out_off, out_locs, filter_best=True):
+        """bm_map_locate_packed with caller-provided (ideally pinned) arrays.  Returns (n_locs, stats)."""
+        n = len(read_off) - 1
+        stats = np.zeros(8, np.uint64)
+        self._ck(self.lib.bm_map_locate_packed(self.h, C.byref(P), _ptr(planes), _ptr(qk), _ptr(pl_off), _ptr(read_off), n,
+                                               int(filter_best), _ptr(out_off), _ptr(out_locs), len(out_locs),
+                                               _ptr(stats)), "bm_map_locate_packed")
         self.n_reads = n
         return int(out_off[n]), stats
 

@@ -23,7 +23,7 @@ constexpr uint32_t kCigTmp = 16;       // ops kept per alignment in the first pa
 
 struct AlignArgs {
     const uint8_t* packed; const uint64_t* bstart; const uint32_t* blen;
-    const uint8_t* seq; const uint64_t* read_off; uint32_t n_reads;
+    ReadPlanes rp; const uint64_t* read_off; uint32_t n_reads;
     const uint32_t* loc_off; const bm_loc* locs;
     float indel_rate; uint32_t quality_threshold;
     unsigned long long* scratch; uint32_t chunk_n;
@@ -70,7 +70,8 @@ k_align(AlignArgs a, uint32_t first, uint32_t count) {
     const uint32_t id = MODE ? a.over_list[first + t] : first + t;
     const bm_loc l = a.locs[id];
     const uint32_t r = read_of_loc(a.loc_off, a.n_reads, id);
-    const uint8_t* q = a.seq + a.read_off[r];
+    const uint2* qpl = a.rp.pl + a.rp.pl_off[r];            // bit planes of the whole read (32 bases per chunk)
+    const uint32_t qch = a.rp.pl_off[r + 1] - a.rp.pl_off[r];
     const uint32_t m = (uint32_t)(a.read_off[r + 1] - a.read_off[r]);
     const uint32_t blen = a.blen[l.bucket];
     bm_aln out;
@@ -90,15 +91,14 @@ k_align(AlignArgs a, uint32_t first, uint32_t count) {
     unsigned long long P0[NW], P1[NW], P2[NW], P3[NW];
 #pragma unroll
     for (int w = 0; w < NW; w++) {
-        unsigned long long p0 = 0, p1 = 0, p2 = 0, p3 = 0;
         const uint32_t lim = (m > 64u * w) ? min(64u, m - 64u * w) : 0u;
-        for (uint32_t b = 0; b < lim; b++) {
-            const uint32_t c = bm_rank_dna4(q[64 * w + b]);
-            const unsigned long long bit = 1ull << b;
-            p0 |= (c == 0) ? bit : 0ull; p1 |= (c == 1) ? bit : 0ull;
-            p2 |= (c == 2) ? bit : 0ull; p3 |= (c == 3) ? bit : 0ull;
-        }
-        P0[w] = p0; P1[w] = p1; P2[w] = p2; P3[w] = p3;
+        const unsigned long long mask = lim == 64u ? ~0ull : ((1ull << lim) - 1ull);
+        uint2 c0 = make_uint2(0u, 0u), c1 = make_uint2(0u, 0u);
+        if (2u * w < qch) c0 = __ldg(qpl + 2 * w);
+        if (2u * w + 1u < qch) c1 = __ldg(qpl + 2 * w + 1);
+        const unsigned long long lo = (unsigned long long)c0.x | ((unsigned long long)c1.x << 32);
+        const unsigned long long hi = (unsigned long long)c0.y | ((unsigned long long)c1.y << 32);
+        P0[w] = ~lo & ~hi & mask; P1[w] = lo & ~hi & mask; P2[w] = ~lo & hi & mask; P3[w] = lo & hi & mask;
     }
     unsigned long long Pv[NW], Mv[NW];
     int bs[NW];
@@ -169,7 +169,8 @@ k_align(AlignArgs a, uint32_t first, uint32_t count) {
         bool mism = true;
         if (j > 0) {
             const uint32_t tc = rev ? 3u - bm_gbase(a.packed, tbase + (n - j)) : bm_gbase(a.packed, tbase + (j - 1));
-            mism = bm_rank_dna4(q[i - 1]) != tc;
+            const uint2 qc = __ldg(qpl + ((i - 1) >> 5));
+            mism = ((((qc.y >> ((i - 1) & 31u)) & 1u) << 1) | ((qc.x >> ((i - 1) & 31u)) & 1u)) != tc;
         }
         if (j > 0 && cur == dg + (mism ? 1 : 0)) { op = 0; nxt = dg; }
         else {
@@ -267,7 +268,8 @@ int bm_align_device(bm_ctx* c, const bm_params* p) {
     BM_CK(c, cudaMemsetAsync((uint32_t*)c->d_cigar_cnt.p + n_aln, 0, 4, c->stream));
     AlignArgs a;
     a.packed = c->d_packed.as<uint8_t>(); a.bstart = c->d_bstart.as<uint64_t>(); a.blen = c->d_blen.as<uint32_t>();
-    a.seq = c->d_seq.as<uint8_t>(); a.read_off = c->d_read_off.as<uint64_t>(); a.n_reads = c->n_reads;
+    a.rp = ReadPlanes{c->d_pl.as<uint2>(), nullptr, c->d_pl_off.as<uint32_t>()};
+    a.read_off = c->d_read_off.as<uint64_t>(); a.n_reads = c->n_reads;
     a.loc_off = c->d_loc_off.as<uint32_t>(); a.locs = c->d_locs.as<bm_loc>();
     a.indel_rate = p->indel_rate; a.quality_threshold = p->quality_threshold;
     a.scratch = nullptr; a.chunk_n = 0;

@@ -9,7 +9,7 @@
 
 extern "C" {
 
-int bm_version(void) { return 100; }
+int bm_version(void) { return 200; }
 
 int bm_ctx_create(int device, bm_ctx** out) {
     if (!out) return BM_E_ARG;
@@ -43,12 +43,12 @@ void bm_ctx_destroy(bm_ctx* c) {
                       &c->d_cres_votes, &c->d_cseg, &c->d_loc_cnt, &c->d_loc_off, &c->d_locs, &c->d_locs2,
                       &c->d_loc_off2, &c->d_vote_scratch, &c->d_locs3, &c->d_loc_pool, &c->d_loc_flags, &c->d_read_seg0, &c->d_aln, &c->d_cigar_fixed, &c->d_cigar_cnt,
                       &c->d_cigar_off, &c->d_cigar, &c->d_aln_scratch, &c->d_flush, &c->d_krows, &c->d_distok_p, &c->d_gidx_pos,
-                      &c->d_gidx_off, &c->d_loc_over, &c->d_map_over};
+                      &c->d_gidx_off, &c->d_loc_over, &c->d_map_over, &c->d_frows, &c->d_pl, &c->d_qk, &c->d_pl_off};
     if (c->lane_ev) cudaEventDestroy(c->lane_ev);
     if (c->lane) { bm_ctx_destroy(c->lane); c->lane = nullptr; cudaSetDevice(c->device); }
     for (DevBuf* b : bufs) b->release();
     c->h_lane_off.release();
-    for (HostBuf* h : {&c->h_read_seg0, &c->h_seg_read, &c->h_seg_start, &c->h_seg_len, &c->h_off_rel}) h->release();
+    for (HostBuf* h : {&c->h_read_seg0, &c->h_seg_read, &c->h_seg_start, &c->h_seg_len, &c->h_off_rel, &c->h_pl_off}) h->release();
     for (auto e : c->chunk_ev) cudaEventDestroy(e);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     for (auto& p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
@@ -130,6 +130,7 @@ static void sample_det(uint32_t n, uint32_t ub, std::vector<uint32_t>& out) {
 int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads) {
     if (p->read_len == 0 || p->num_segment_samples == 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad parameters");
     c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
+    c->lsamp_k = c->lsamp_P = c->lsamp_b = 0;
     if (read_off[n_reads] < read_off[0]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
     const uint64_t nbytes = read_off[n_reads] - read_off[0];
     // long reads (> 2r) are cut into num_segment_samples segments; without one the table has one entry per read
@@ -139,14 +140,25 @@ int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_
     for (uint32_t i = 0; i < n_reads; i++) n_long += (read_off[i + 1] - read_off[i]) > two_r;
     const uint64_t seg_cap = n_reads + n_long * (p->num_segment_samples - 1);
     if (seg_cap > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: too many segments in one batch");
+    // chunks of the packed form: ceil(len/32) per read
+    uint64_t n_chunks = 0;
+    for (uint32_t i = 0; i < n_reads; i++) n_chunks += (read_off[i + 1] - read_off[i] + 31) / 32;
+    if (n_chunks > 0xFFFFFFF0ull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: more than 2^32 chunks of 32 bases in one batch");
+    c->n_pl_chunks = n_chunks;
+    BM_CK(c, c->h_pl_off.ensure((size_t)(n_reads + 1) * 4));
+    BM_CK(c, c->d_pl_off.ensure((size_t)(n_reads + 1) * 4));
+    BM_CK(c, c->d_pl.ensure((size_t)(n_chunks + 2) * 8));
+    BM_CK(c, c->d_qk.ensure((size_t)(n_chunks + 2) * 4));
     BM_CK(c, c->h_off_rel.ensure((size_t)(n_reads + 1) * 8));
     BM_CK(c, c->h_read_seg0.ensure((size_t)(n_reads + 1) * 4));
     BM_CK(c, c->h_seg_read.ensure((size_t)(seg_cap + 1) * 4));
     BM_CK(c, c->h_seg_start.ensure((size_t)(seg_cap + 1) * 4));
     BM_CK(c, c->h_seg_len.ensure((size_t)(seg_cap + 1) * 4));
     BM_CK(c, c->d_read_seg0.ensure((size_t)(n_reads + 1) * 4));
-    BM_CK(c, c->d_seq.ensure(nbytes + 16));
-    BM_CK(c, c->d_qual.ensure(nbytes + 16));
+    if (c->want_ascii) {
+        BM_CK(c, c->d_seq.ensure(nbytes + 16));
+        BM_CK(c, c->d_qual.ensure(nbytes + 16));
+    }
     BM_CK(c, c->d_read_off.ensure((size_t)(n_reads + 1) * 8));
     BM_CK(c, c->d_seg_read.ensure((size_t)(seg_cap + 1) * 4));
     BM_CK(c, c->d_seg_start.ensure((size_t)(seg_cap + 1) * 4));
@@ -164,11 +176,15 @@ int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* re
     const uint64_t base = read_off[0];
     const uint32_t rl = p->read_len;
     uint32_t n_seg = c->n_seg, mx = c->max_seg_len, mxr = c->max_read_len;
+    uint32_t* pl_off = c->h_pl_off.as<uint32_t>();
+    uint32_t plo = r0 ? pl_off[r0] : 0u;
     std::vector<uint32_t> st;
     for (uint32_t i = r0; i < r1; i++) {
         if (read_off[i + 1] < read_off[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
         off_rel[i] = read_off[i] - base;
         const uint64_t len64 = read_off[i + 1] - read_off[i];
+        pl_off[i] = plo;
+        plo += (uint32_t)((len64 + 31) / 32);
         if (len64 > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31");
         const uint32_t len = (uint32_t)len64;
         if (len > mxr) mxr = len;
@@ -187,6 +203,7 @@ int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* re
         }
     }
     off_rel[r1] = read_off[r1] - base;
+    pl_off[r1] = plo;
     seg0[r1] = n_seg;
     c->n_seg = n_seg; c->max_seg_len = mx; c->max_read_len = mxr;
     return BM_OK;
@@ -194,30 +211,68 @@ int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* re
 
 extern "C" {
 
+static int upload_tables(bm_ctx* c, uint32_t n_reads) {
+    const uint32_t n_seg = c->n_seg;
+    BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.p, c->h_read_seg0.p, (size_t)(n_reads + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    BM_CK(c, cudaMemcpyAsync(c->d_read_off.p, c->h_off_rel.p, (size_t)(n_reads + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    BM_CK(c, cudaMemcpyAsync(c->d_pl_off.p, c->h_pl_off.p, (size_t)(n_reads + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    if (n_seg) {
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_read.p, c->h_seg_read.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_start.p, c->h_seg_start.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->d_seg_len.p, c->h_seg_len.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    return BM_OK;
+}
+
 int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
                     uint32_t n_reads) {
     if (!c) return BM_E_ARG;
     if (!p || !read_off || (n_reads && (!seq || !qual))) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad arguments");
     cudaSetDevice(c->device);
     // read i = seq[read_off[i], read_off[i+1]); read_off[0] may be non-zero (a slice of a larger batch)
+    c->want_ascii = true;
     int r = bm_internal_reads_begin(c, p, read_off, n_reads);
     if (r) return r;
     r = bm_internal_build_segments(c, p, read_off, 0, n_reads);
     if (r) return r;
     const uint64_t base = read_off[0], nbytes = c->n_read_bytes;
-    const uint32_t n_seg = c->n_seg;
-    BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.p, c->h_read_seg0.p, (size_t)(n_reads + 1) * 4, cudaMemcpyHostToDevice, c->stream));
     if (nbytes) {
         BM_CK(c, cudaMemcpyAsync(c->d_seq.p, seq + base, nbytes, cudaMemcpyHostToDevice, c->stream));
         BM_CK(c, cudaMemcpyAsync(c->d_qual.p, qual + base, nbytes, cudaMemcpyHostToDevice, c->stream));
     }
-    BM_CK(c, cudaMemcpyAsync(c->d_read_off.p, c->h_off_rel.p, (size_t)(n_reads + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-    if (n_seg) {
-        BM_CK(c, cudaMemcpyAsync(c->d_seg_read.p, c->h_seg_read.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
-        BM_CK(c, cudaMemcpyAsync(c->d_seg_start.p, c->h_seg_start.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
-        BM_CK(c, cudaMemcpyAsync(c->d_seg_len.p, c->h_seg_len.p, (size_t)n_seg * 4, cudaMemcpyHostToDevice, c->stream));
-    }
+    r = upload_tables(c, n_reads);
+    if (r) return r;
+    r = bm_internal_pack_range(c, p, 0, n_reads);              // ASCII -> bit planes + k-mer quality plane
+    if (r) return r;
     BM_CK(c, cudaStreamSynchronize(c->stream));   // the caller's buffers may be reused after return
+    c->ascii_resident = true; c->have_qk = true; c->pack_k = p->k; c->pack_b = p->avg_base_quality;
+    c->have_reads = true;
+    return BM_OK;
+}
+
+// the batch already in the device form (bm_pack_layout / bm_pack_reads made it on the host)
+int bm_reads_upload_packed(bm_ctx* c, const bm_params* p, const uint64_t* planes, const uint32_t* qk,
+                           const uint32_t* pl_off, const uint64_t* read_off, uint32_t n_reads) {
+    if (!c) return BM_E_ARG;
+    if (!p || !read_off || !pl_off || (n_reads && !planes)) BM_FAIL(c, BM_E_ARG, "bm_reads_upload_packed: bad arguments");
+    cudaSetDevice(c->device);
+    c->want_ascii = false;
+    int r = bm_internal_reads_begin(c, p, read_off, n_reads);
+    if (r) return r;
+    r = bm_internal_build_segments(c, p, read_off, 0, n_reads);
+    if (r) return r;
+    const uint32_t* hpl = c->h_pl_off.as<uint32_t>();
+    for (uint32_t i = 0; i <= n_reads; i++)
+        if (pl_off[i] - pl_off[0] != hpl[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload_packed: pl_off is not the layout of bm_pack_layout");
+    const uint64_t nch = c->n_pl_chunks;
+    if (nch) {
+        BM_CK(c, cudaMemcpyAsync(c->d_pl.p, planes + pl_off[0], nch * 8, cudaMemcpyHostToDevice, c->stream));
+        if (qk) BM_CK(c, cudaMemcpyAsync(c->d_qk.p, qk + pl_off[0], nch * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    r = upload_tables(c, n_reads);
+    if (r) return r;
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->ascii_resident = false; c->have_qk = qk != nullptr; c->pack_k = p->k; c->pack_b = p->avg_base_quality;
     c->have_reads = true;
     return BM_OK;
 }

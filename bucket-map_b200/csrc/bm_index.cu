@@ -94,7 +94,8 @@ __global__ void k_distok(const int32_t* __restrict__ k2i, const uint32_t* __rest
 // (4 coarse bits) and 8 neighbouring lanes assemble one coarse word.  Reads ~1.3x (4^k x Wp) bytes, writes 4^k x 128 B.
 __global__ void __launch_bounds__(256)
 k_kmer_coarse(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ k2i, uint32_t NQ,
-              uint32_t Q, uint64_t n_kmers, uint32_t* __restrict__ crows, uint32_t Wcs, uint32_t logg) {
+              uint32_t Q, uint64_t n_kmers, uint32_t* __restrict__ crows, uint32_t Wcs, uint32_t logg,
+              uint4* __restrict__ frows /* full-resolution rows (4^k x Wp16) or nullptr */) {
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t nbits = 128u >> logg;          // coarse bits per 16-B column: 4 (G=32), 8 (G=16), 16 (G=8)
     const uint32_t lpw = 32u / nbits;             // lanes that share one coarse word: 8, 4, 2
@@ -123,6 +124,7 @@ k_kmer_coarse(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const 
                         v.x &= t.x; v.y &= t.y; v.z &= t.z; v.w &= t.w;
                     }
                 }
+                if (frows && act) frows[(x0 + j) * Wp16 + c] = v;
                 const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
                 uint32_t nib = 0;
 #pragma unroll
@@ -165,7 +167,7 @@ int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32
         if (k2i[i] >= 0) { if ((uint32_t)k2i[i] >= n_rows) BM_FAIL(c, BM_E_ARG, "kmer_to_index entry >= n_rows"); cnt++; }
     }
     (void)cnt;
-    c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0;
+    c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0; c->frows_k = 0; c->fine_tried_k = 0;
     c->q = q; c->n_rows = n_rows; c->NB = NB;
     c->W = (NB + 7) >> 3; c->Wp = (c->W + 63u) & ~63u;
     BM_CK(c, c->d_k2i.ensure(n_codes * 4));
@@ -212,29 +214,48 @@ int bm_internal_index_prepare(bm_ctx* c, float d) {
 // or when 4^k rows do not fit the memory budget: the mapper then gathers the k-q+1 q-gram rows per sample over the full
 // row width.  Both ways are CUDA paths with identical results.
 int bm_internal_kmer_table_prepare(bm_ctx* c, uint32_t k) {
-    c->use_ktable = false;
+    c->use_ktable = false; c->use_ftable = false;
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "no index resident (bm_index_build / bm_index_load first)");
     if (c->ktable_mode == 0 || k < c->q || k < 3 || k > 15 || c->n_rows == 0) {
-        if (c->ktable_mode == 0 && c->d_krows.p) { c->d_krows.release(); c->krows_k = 0; }
+        if (c->ktable_mode == 0 && c->d_krows.p) { c->d_krows.release(); c->krows_k = 0; c->d_frows.release(); c->frows_k = 0; }
         return BM_OK;
     }
-    if (c->krows_k == k && c->krows_logg == c->ktable_logg && c->d_krows.p) { c->use_ktable = true; return BM_OK; }
+    if (c->ftable_mode == 0 && c->d_frows.p) { c->d_frows.release(); c->frows_k = 0; }
+    const bool fine_ok = c->ftable_mode == 0 || (c->frows_k == k && c->d_frows.p) || c->fine_tried_k == k;
+    if (c->krows_k == k && c->krows_logg == c->ktable_logg && c->d_krows.p && fine_ok) {
+        c->use_ktable = true; c->use_ftable = c->ftable_mode != 0 && c->frows_k == k && c->d_frows.p;
+        return BM_OK;
+    }
     const uint64_t n_kmers = 1ull << (2 * k);
     const uint32_t Wp32 = c->Wp / 4;
     const uint32_t logg = c->ktable_logg;                          // buckets per coarse bit = 1 << logg
     c->Wc = ((Wp32 << (5 - logg)) + 31) / 32;
     c->Wcs = (c->Wc + 15u) & ~15u;
     const uint64_t bytes = n_kmers * c->Wcs * 4;
-    c->d_krows.release(); c->krows_k = 0;
+    c->d_krows.release(); c->krows_k = 0; c->d_frows.release(); c->frows_k = 0;
+    // The locator's genome k-mer index needs ~16 B per base of scratch while it is built: build it BEFORE the tables take
+    // their memory (it is wanted at the first locator call anyway), so that the fine table can use what is left.
+    if (c->gidx_mode && c->d_packed.p) { int r = bm_internal_gidx_prepare(c, k); if (r) return r; }
     uint64_t budget = c->ktable_max_bytes;
-    if (!budget) {
-        size_t fr = 0, tot = 0;
-        BM_CK(c, cudaMemGetInfo(&fr, &tot));
-        budget = fr / 2;                          // leave the other half to read batches, candidates and scratch
-    }
+    size_t fr = 0, tot = 0;
+    BM_CK(c, cudaMemGetInfo(&fr, &tot));
+    if (!budget) budget = fr / 2;                 // leave the other half to read batches, candidates and scratch
     if (bytes > budget) return BM_OK;
     cudaError_t e = c->d_krows.ensure_exact(bytes);
     if (e != cudaSuccess) { cudaGetLastError(); return BM_OK; }   // does not fit after all: q-gram gather
+    // full-resolution table: only when it fits beside the coarse one with room for batches, results and scratch
+    // (24 GB, or a quarter of the card) -- and for the locator index if that is still to come
+    uint4* frows = nullptr;
+    c->fine_tried_k = k;
+    if (c->ftable_mode) {
+        const uint64_t fbytes = n_kmers * (uint64_t)c->Wp;
+        BM_CK(c, cudaMemGetInfo(&fr, &tot));
+        uint64_t reserve = (uint64_t)24 << 30;
+        if (reserve < tot / 8) reserve = tot / 8;
+        if (c->gidx_mode && !c->d_gidx_pos.p && c->n_bases) reserve += c->n_bases * 20 + (n_kmers << 8);
+        if (fbytes + reserve <= fr && c->d_frows.ensure_exact(fbytes) == cudaSuccess) frows = c->d_frows.as<uint4>();
+        else cudaGetLastError();
+    }
     BM_CK(c, cudaMemsetAsync(c->d_krows.p, 0, bytes, c->stream));   // stride padding words
     {
         KScope ks(c, BM_K_KTABLE);
@@ -242,10 +263,11 @@ int bm_internal_kmer_table_prepare(bm_ctx* c, uint32_t k) {
         const uint32_t blocks = (uint32_t)(want < (uint64_t)c->sm_count * 64 ? want : (uint64_t)c->sm_count * 64);
         k_kmer_coarse<<<blocks, 256, 0, c->stream>>>(c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_k2i.as<int32_t>(),
                                                      k - c->q + 1, (c->q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * c->q)) - 1u),
-                                                     n_kmers, c->d_krows.as<uint32_t>(), c->Wcs, logg);
+                                                     n_kmers, c->d_krows.as<uint32_t>(), c->Wcs, logg, frows);
     }
     BM_CK(c, cudaGetLastError());
     c->krows_k = k; c->krows_logg = logg; c->use_ktable = true;
+    if (frows) { c->frows_k = k; c->use_ftable = true; }
     return BM_OK;
 }
 
@@ -257,7 +279,27 @@ int bm_index_kmer_table(bm_ctx* c, int mode, uint64_t max_bytes) {
         BM_FAIL(c, BM_E_ARG, "bm_index_kmer_table: mode must be 0 (off), 1 (when it fits) or a group size 8/16/32");
     c->ktable_logg = (mode == 8) ? 3 : (mode == 32) ? 5 : 4;
     c->ktable_mode = mode ? 1 : 0; c->ktable_max_bytes = max_bytes;
-    if (mode == 0 || (max_bytes && c->d_krows.cap > max_bytes)) { cudaSetDevice(c->device); c->d_krows.release(); c->krows_k = 0; }
+    if (mode == 0 || (max_bytes && c->d_krows.cap > max_bytes)) {
+        cudaSetDevice(c->device);
+        c->d_krows.release(); c->krows_k = 0; c->d_frows.release(); c->frows_k = 0;
+    }
+    c->fine_tried_k = 0;
+    return BM_OK;
+}
+
+int bm_index_fine_table(bm_ctx* c, int mode) {
+    if (!c) return BM_E_ARG;
+    if (mode != 0 && mode != 1) BM_FAIL(c, BM_E_ARG, "bm_index_fine_table: mode must be 0 (off) or 1 (when it fits)");
+    c->ftable_mode = mode; c->fine_tried_k = 0;
+    if (!mode) { cudaSetDevice(c->device); c->d_frows.release(); c->frows_k = 0; }
+    return BM_OK;
+}
+
+int bm_index_fine_table_info(bm_ctx* c, uint32_t* k, uint64_t* bytes) {
+    if (!c) return BM_E_ARG;
+    const bool on = c->d_frows.p && c->frows_k;
+    if (k) *k = on ? c->frows_k : 0;
+    if (bytes) *bytes = on ? ((1ull << (2 * c->frows_k)) * (uint64_t)c->Wp) : 0;
     return BM_OK;
 }
 
@@ -358,7 +400,7 @@ int bm_index_alloc(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, u
 int bm_index_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
     if (!c) return BM_E_ARG;
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_index_device: no index resident");
-    c->zeros_for_d = -1.f; c->krows_k = 0;                       // the caller may overwrite the rows: recompute zeros on next use
+    c->zeros_for_d = -1.f; c->krows_k = 0; c->frows_k = 0; c->fine_tried_k = 0;   // the caller may overwrite the rows: recompute on next use
     if (dptr) *dptr = c->d_rows.p;
     if (bytes) *bytes = (uint64_t)c->n_rows * c->Wp;
     return BM_OK;
@@ -376,7 +418,7 @@ int bm_ref_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
 int bm_index_free(bm_ctx* c) {
     if (!c) return BM_E_ARG;
     cudaSetDevice(c->device);
-    c->d_krows.release();
+    c->d_krows.release(); c->d_frows.release(); c->frows_k = 0; c->fine_tried_k = 0;
     c->d_rows.release(); c->d_zeros.release(); c->d_distok.release(); c->d_distok_p.release(); c->d_k2i.release(); c->d_stage.release();
     c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0; c->have_map = false;
     return BM_OK;

@@ -99,9 +99,28 @@ struct bm_ctx {
     int gidx_mode = 1;            // 0 never, 1 when it fits (bm_locator_index)
     bool use_gidx = false;
 
-    // read batch
+    // full-resolution k-mer table (optional, bm_index_fine_table): the same AND as the coarse table but one bit per bucket,
+    // 4^k rows of Wp bytes (54.8 GB on the 1.7 Gbp reference).  The fused mapper recounts a passing group from ONE word
+    // per sample of this table instead of k-q+1 scattered .qgram words.  Built together with the coarse table when it
+    // fits beside everything else; frows_k = the k it was built for (0: not resident).
+    DevBuf d_frows;
+    uint32_t frows_k = 0, fine_tried_k = 0;   // fine_tried_k: the k a build was last attempted for (not retried per call)
+    int ftable_mode = 1;          // 0 never, 1 when it fits
+    bool use_ftable = false;
+
+    // read batch.  Canonical device form (what every kernel reads): base bit planes, 32 bases per chunk -- chunk c of
+    // read i is d_pl[pl_off[i] + c] = {low bits, high bits} of the ranks of bases 32c..32c+31 (A0 C1 G2 T3, bit t = base
+    // 32c+t, bases past the end 0) -- and, when some read of the batch has a base below -b, the k-mer quality plane
+    // d_qk (bit t of chunk c: the k bases from 32c+t on have phred sum >= b*k, quality_filter.h:531-534).  ASCII batches
+    // (d_seq, d_qual) are turned into this form by k_pack_reads right after their copy.
     DevBuf d_seq, d_qual, d_read_off, d_seg_read, d_seg_start, d_seg_len, d_read_seg0;
-    HostBuf h_read_seg0, h_seg_read, h_seg_start, h_seg_len, h_off_rel;   // pinned; filled by bm_internal_build_segments
+    DevBuf d_pl, d_qk, d_pl_off;
+    HostBuf h_read_seg0, h_seg_read, h_seg_start, h_seg_len, h_off_rel, h_pl_off;   // pinned; filled by bm_internal_build_segments
+    bool have_qk = false;         // false: every k-mer window of the batch passes the quality test (d_qk unused)
+    bool ascii_resident = false;  // d_seq / d_qual hold the batch (it came as ASCII): the planes can be re-derived
+    bool want_ascii = true;       // the batch being set up arrives as ASCII (sizes d_seq / d_qual)
+    uint32_t pack_k = 0, pack_b = 0;   // the (k, b) d_qk was computed for
+    uint64_t n_pl_chunks = 0;
     uint32_t n_reads = 0, n_seg = 0, n_seg_total = 0, max_seg_len = 0, max_read_len = 0;
     uint64_t n_read_bytes = 0;
     bool have_reads = false;
@@ -182,6 +201,10 @@ int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* 
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
 // reads: size the batch buffers (host tables + device), then append the segment table of reads [r0, r1)
 int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads);
+// k_pack_reads over reads [r0, r1) of the resident ASCII batch (d_seq, d_qual, d_read_off, d_pl_off) on c->stream
+int bm_internal_pack_range(bm_ctx* c, const bm_params* p, uint32_t r0, uint32_t r1);
+// makes sure the quality plane of the resident batch matches (k, b) of this call (re-packs an ASCII batch if not)
+int bm_internal_pack_check(bm_ctx* c, const bm_params* p);
 int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t r0, uint32_t r1);
 // mapper in three steps so that K2a/K2 can run on a segment range as soon as its bytes are resident
 int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uint32_t max_seg_len);
@@ -220,10 +243,28 @@ __device__ __forceinline__ uint32_t bm_gbase(const uint8_t* __restrict__ p, uint
     return (p[i >> 2] >> ((i & 3) << 1)) & 3u;
 }
 
+// the resident read batch as the kernels see it
+struct ReadPlanes {
+    const uint2* pl;          // {lo, hi} per chunk of 32 bases
+    const uint32_t* qk;       // k-mer quality plane per chunk, or nullptr: every window passes
+    const uint32_t* pl_off;   // first chunk of read i; pl_off[i+1] - pl_off[i] = ceil(len_i / 32)
+};
+
+// chunk c (segment positions 32c .. 32c+31) of the segment that starts at base s of the read with chunks [c0, c1)
+__device__ __forceinline__ void seg_chunk(const ReadPlanes& rp, uint32_t c0, uint32_t c1, uint32_t s, uint32_t c,
+                                          uint32_t& lo, uint32_t& hi, uint32_t& qk) {
+    const uint32_t i = c0 + (s >> 5) + c, sh = s & 31u;
+    uint2 a = make_uint2(0u, 0u), b = make_uint2(0u, 0u);
+    uint32_t qa = 0u, qb = 0u;
+    if (i < c1) { a = __ldg(rp.pl + i); qa = rp.qk ? __ldg(rp.qk + i) : 0xFFFFFFFFu; }
+    if (sh && i + 1 < c1) { b = __ldg(rp.pl + i + 1); qb = rp.qk ? __ldg(rp.qk + i + 1) : 0xFFFFFFFFu; }
+    lo = __funnelshift_r(a.x, b.x, sh); hi = __funnelshift_r(a.y, b.y, sh); qk = __funnelshift_r(qa, qb, sh);
+}
+
 // shared by K2a and K3a: stage one segment in shared memory and evaluate its k-mers
 struct SegStage {
     uint8_t* base;    // 2-bit ranks, one per byte
-    uint8_t* qual;    // phred ranks (char - 33)
+    uint32_t* qkm;    // k-mer quality bits, one word per chunk of 32 k-mer positions
     uint32_t* mask;   // one ballot word per chunk of 32 k-mer positions
 };
 
@@ -232,12 +273,6 @@ __device__ __forceinline__ uint32_t kmer_hash_at(const uint8_t* sb, uint32_t j, 
     for (uint32_t t = 0; t < k; t++) h = (h << 2) | sb[j + t];
     return h;
 }
-__device__ __forceinline__ uint32_t kmer_qual_at(const uint8_t* sq, uint32_t j, uint32_t k) {
-    uint32_t s = 0;   // views::kmer_quality (quality_filter.h:531-534): window sum of phred ranks
-    for (uint32_t t = 0; t < k; t++) s += sq[j + t];
-    return s;
-}
-
 // utils.h:160-178 with upper_bound = G-1 (see bm_api.cu sample_det for the ub==0 convention)
 __device__ __forceinline__ uint32_t sample_index(uint32_t i, uint32_t n, uint32_t G) {
     if (G <= 1) return 0;
@@ -268,14 +303,20 @@ __device__ __forceinline__ uint32_t select_good(const uint32_t* mask, uint32_t n
     return c * 32 + select_bit(mask[c], x);
 }
 
-__device__ __forceinline__ void stage_segment(const SegStage& st, const uint8_t* __restrict__ seq,
-                                              const uint8_t* __restrict__ qual, uint64_t off, uint32_t n, uint32_t lane) {
-    for (uint32_t i = lane; i < n; i += 32) {
-        st.base[i] = (uint8_t)bm_rank_dna4(seq[off + i]);
-        st.qual[i] = (uint8_t)(qual[off + i] - 33);
+// segment (read chunks [c0, c1), start s, n bases) -> ranks, one per byte, and the k-mer quality words
+__device__ __forceinline__ void stage_segment(const SegStage& st, const ReadPlanes& rp, uint32_t c0, uint32_t c1,
+                                              uint32_t s, uint32_t n, uint32_t lane) {
+    const uint32_t nch = (n + 31) / 32;
+    for (uint32_t c = 0; c < nch; c++) {
+        uint32_t lo, hi, qk;
+        seg_chunk(rp, c0, c1, s, c, lo, hi, qk);          // the same words in every lane (broadcast loads)
+        const uint32_t i = c * 32 + lane;
+        if (i < n) st.base[i] = (uint8_t)((((hi >> lane) & 1u) << 1) | ((lo >> lane) & 1u));
+        if (lane == 0) st.qkm[c] = qk;
     }
     __syncwarp();
 }
+__device__ __forceinline__ bool kmer_qual_ok(const SegStage& st, uint32_t j) { return (st.qkm[j >> 5] >> (j & 31u)) & 1u; }
 
 __device__ __forceinline__ uint4 bm_ldg_stream(const uint4* p) {
     uint4 v;

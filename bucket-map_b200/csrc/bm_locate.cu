@@ -35,29 +35,27 @@ constexpr int kSampWarps = 4;
 
 // ---- K3a: P sampled (index, hash) pairs per segment (bucket_locator.h:315-341) -------------------------------------------
 __global__ void __launch_bounds__(kSampWarps * 32)
-k_loc_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, const uint64_t* __restrict__ read_off,
-             const uint32_t* __restrict__ seg_read, const uint32_t* __restrict__ seg_start,
+k_loc_sample(const ReadPlanes rp, const uint32_t* __restrict__ seg_read, const uint32_t* __restrict__ seg_start,
              const uint32_t* __restrict__ seg_len, uint32_t n_seg, uint32_t max_seg_len, uint32_t k, uint32_t P,
-             uint32_t minq, uint16_t* __restrict__ sidx, uint32_t* __restrict__ shash) {
+             uint16_t* __restrict__ sidx, uint32_t* __restrict__ shash) {
     extern __shared__ __align__(16) uint8_t smem[];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t seg = blockIdx.x * kSampWarps + warp;
     if (seg >= n_seg) return;
     const uint32_t nchunk_max = (max_seg_len + 31) / 32 + 1;
-    const uint32_t per_warp = ((2 * max_seg_len + 3) & ~3u) + nchunk_max * 4;
+    const uint32_t per_warp = ((max_seg_len + 3) & ~3u) + 2 * nchunk_max * 4;
     SegStage st;
     st.base = smem + (size_t)warp * per_warp;
-    st.qual = st.base + max_seg_len;
-    st.mask = reinterpret_cast<uint32_t*>(st.base + ((2 * max_seg_len + 3) & ~3u));
-    const uint32_t n = seg_len[seg];
-    const uint64_t off = read_off[seg_read[seg]] + seg_start[seg];
-    stage_segment(st, seq, qual, off, n, lane);
+    st.qkm = reinterpret_cast<uint32_t*>(st.base + ((max_seg_len + 3) & ~3u));
+    st.mask = st.qkm + nchunk_max;
+    const uint32_t n = seg_len[seg], rd = seg_read[seg];
+    stage_segment(st, rp, rp.pl_off[rd], rp.pl_off[rd + 1], seg_start[seg], n, lane);
     const uint32_t nk = (n >= k) ? n - k + 1 : 0;
     const uint32_t nchunk = (nk + 31) / 32;
     uint32_t G = 0;
     for (uint32_t c = 0; c < nchunk; c++) {
         uint32_t j = c * 32 + lane;
-        bool good = j < nk && kmer_qual_at(st.qual, j, k) >= minq;      // :323-325 (quality only)
+        bool good = j < nk && kmer_qual_ok(st, j);                      // :323-325 (quality only)
         uint32_t m = __ballot_sync(0xFFFFFFFFu, good);
         if (lane == 0) st.mask[c] = m;
         G += __popc(m);
@@ -498,6 +496,7 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
     if (posbits + kSlotBits > 32) BM_FAIL(c, BM_E_LIMIT, "bucket length too large for the locator (max 2^20 bases)");
     cudaSetDevice(c->device);
     c->have_locs = false; c->have_aln = false;
+    { int rp = bm_internal_pack_check(c, p); if (rp) return rp; }
     const uint32_t n_seg = c->n_seg, n_reads = c->n_reads;
     const uint64_t n_cand = c->n_cand;
 
@@ -511,13 +510,13 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
     const bool have_samples = c->lsamp_k == k && c->lsamp_P == P && c->lsamp_b == p->avg_base_quality;
     if (n_seg && !have_samples) {
         const uint32_t msl = c->max_seg_len ? c->max_seg_len : 1;
-        size_t smem = (size_t)kSampWarps * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
+        size_t smem = (size_t)kSampWarps * ((((size_t)msl + 3) & ~(size_t)3) + 2 * ((msl + 31) / 32 + 1) * 4);
         if (smem > 48 * 1024)
             BM_CK(c, cudaFuncSetAttribute(k_loc_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         KScope ks(c, BM_K_LOCSAMPLE);
+        const ReadPlanes rp{c->d_pl.as<uint2>(), c->have_qk ? c->d_qk.as<uint32_t>() : nullptr, c->d_pl_off.as<uint32_t>()};
         k_loc_sample<<<(n_seg + kSampWarps - 1) / kSampWarps, kSampWarps * 32, smem, c->stream>>>(
-            c->d_seq.as<uint8_t>(), c->d_qual.as<uint8_t>(), c->d_read_off.as<uint64_t>(), c->d_seg_read.as<uint32_t>(),
-            c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), n_seg, msl, k, P, p->avg_base_quality * k,
+            rp, c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), n_seg, msl, k, P,
             c->d_lsamp_idx.as<uint16_t>(), c->d_lsamp_hash.as<uint32_t>());
     }
     BM_CK(c, cudaGetLastError());

@@ -23,26 +23,24 @@ constexpr int kWarpsPerCta = 4;
 // ---- K2a: good k-mers -> S samples -> row ids of both strands ------------------------------------------------------------
 // q_gram_mapper.h:431-469.  rowidx[((2*seg+strand)*S + s)*NQ + i] = kmer_to_index[(h_s >> 2i) & Q]  (or -1)
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
-k_map_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, const uint64_t* __restrict__ read_off,
-             const uint32_t* __restrict__ seg_read, const uint32_t* __restrict__ seg_start,
+k_map_sample(const ReadPlanes rp, const uint32_t* __restrict__ seg_read, const uint32_t* __restrict__ seg_start,
              const uint32_t* __restrict__ seg_len, uint32_t seg0, uint32_t n_seg, uint32_t max_seg_len,
              const int32_t* __restrict__ k2i, const uint32_t* __restrict__ distok, uint32_t k, uint32_t q, uint32_t S,
-             uint32_t minq, uint32_t min_good, uint32_t ktable, int32_t* __restrict__ rowidx, uint8_t* __restrict__ segok,
+             uint32_t min_good, uint32_t ktable, int32_t* __restrict__ rowidx, uint8_t* __restrict__ segok,
              unsigned long long* __restrict__ stats) {
     extern __shared__ __align__(16) uint8_t smem[];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t seg = seg0 + blockIdx.x * kWarpsPerCta + warp;   // segments [seg0, n_seg) of the batch
     if (seg >= n_seg) return;
     const uint32_t nchunk_max = (max_seg_len + 31) / 32 + 1;
-    const uint32_t per_warp = ((2 * max_seg_len + 3) & ~3u) + nchunk_max * 4;
+    const uint32_t per_warp = ((max_seg_len + 3) & ~3u) + 2 * nchunk_max * 4;
     SegStage st;
     st.base = smem + (size_t)warp * per_warp;
-    st.qual = st.base + max_seg_len;
-    st.mask = reinterpret_cast<uint32_t*>(st.base + ((2 * max_seg_len + 3) & ~3u));
+    st.qkm = reinterpret_cast<uint32_t*>(st.base + ((max_seg_len + 3) & ~3u));
+    st.mask = st.qkm + nchunk_max;
 
-    const uint32_t n = seg_len[seg];
-    const uint64_t off = read_off[seg_read[seg]] + seg_start[seg];
-    stage_segment(st, seq, qual, off, n, lane);
+    const uint32_t n = seg_len[seg], rd = seg_read[seg];
+    stage_segment(st, rp, rp.pl_off[rd], rp.pl_off[rd + 1], seg_start[seg], n, lane);
 
     const uint32_t NQ = k - q + 1, Q = (1u << (2 * q)) - 1u;
     const uint32_t nk = (n >= k) ? n - k + 1 : 0;
@@ -58,7 +56,7 @@ k_map_sample(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, 
                 uint32_t g = (h >> (2 * i)) & Q;
                 dist |= (__ldg(distok + (g >> 5)) >> (g & 31)) & 1u;
             }
-            good = dist && kmer_qual_at(st.qual, j, k) >= minq;   // :437-442
+            good = dist && kmer_qual_ok(st, j);                   // :437-442
         }
         uint32_t m = __ballot_sync(0xFFFFFFFFu, good);
         if (lane == 0) st.mask[c] = m;
@@ -286,7 +284,7 @@ __global__ void k_stats_fold(unsigned long long* __restrict__ stats) {
 __global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const uint32_t* __restrict__ cand_cnt,
                                const uint32_t* __restrict__ cand_off, uint32_t n_lists, uint32_t max_cand,
                                uint32_t* __restrict__ cand, uint32_t* __restrict__ cand_list,
-                               unsigned long long* __restrict__ stats) {
+                               unsigned long long* __restrict__ stats, uint32_t count_reads) {
     uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t nd[2] = {0, 0};
     if (2 * seg < n_lists) {
@@ -297,13 +295,24 @@ __global__ void k_cand_compact(const uint32_t* __restrict__ cand_fixed, const ui
         }
     }
     // the three counters of the batch: one atomic per warp, not per segment (3 M adds on one address cost ~0.5 ms)
-    const uint32_t s0 = __reduce_add_sync(0xFFFFFFFFu, (nd[0] + nd[1]) ? 1u : 0u);
+    // stats[0] counts READS with a candidate (q_gram_mapper.h:527-545); a segment is a read unless the batch holds reads
+    // longer than 2r (then k_count_mapped_reads counts them)
+    const uint32_t s0 = count_reads ? __reduce_add_sync(0xFFFFFFFFu, (nd[0] + nd[1]) ? 1u : 0u) : 0u;
     const uint32_t s1 = __reduce_add_sync(0xFFFFFFFFu, nd[0]), s2 = __reduce_add_sync(0xFFFFFFFFu, nd[1]);
     if ((threadIdx.x & 31) == 0) {
         if (s0) atomicAdd(stats + 0, (unsigned long long)s0);
         if (s1) atomicAdd(stats + 1, (unsigned long long)s1);
         if (s2) atomicAdd(stats + 2, (unsigned long long)s2);
     }
+}
+
+// reads (not segments) with at least one candidate, for batches with long reads (5 segments per read)
+__global__ void k_count_mapped_reads(const uint32_t* __restrict__ read_seg0, const uint32_t* __restrict__ cand_off,
+                                     uint32_t n_reads, unsigned long long* __restrict__ stats) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool has = r < n_reads && cand_off[2 * read_seg0[r + 1]] > cand_off[2 * read_seg0[r]];
+    const uint32_t s0 = __reduce_add_sync(0xFFFFFFFFu, has ? 1u : 0u);
+    if ((threadIdx.x & 31) == 0 && s0) atomicAdd(stats + 0, (unsigned long long)s0);
 }
 
 template <int NQ>
@@ -340,7 +349,10 @@ int bm_map_device(bm_ctx* c, const bm_params* p) {
     if (!c) return BM_E_ARG;
     if (!p) BM_FAIL(c, BM_E_ARG, "bm_map_device: null parameters");
     if (!c->have_reads) BM_FAIL(c, BM_E_ARG, "bm_map_device: no read batch resident");
-    int r = bm_internal_map_begin(c, p, c->n_seg, c->max_seg_len);
+    cudaSetDevice(c->device);
+    int r = bm_internal_pack_check(c, p);                 // the k-mer quality plane is per (-l, -b)
+    if (r) return r;
+    r = bm_internal_map_begin(c, p, c->n_seg, c->max_seg_len);
     if (r) return r;
     r = bm_internal_map_range(c, p, 0, c->n_seg, c->max_seg_len);
     if (r) return r;
@@ -413,7 +425,7 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
         c->lsamp_k = p->k; c->lsamp_P = p->locator_samples; c->lsamp_b = p->avg_base_quality;
     }
     const uint32_t msl = max_seg_len ? max_seg_len : 1;
-    size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
+    size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)msl + 3) & ~(size_t)3) + 2 * ((msl + 31) / 32 + 1) * 4);
     if (smem_a > 48 * 1024)
         BM_CK(c, cudaFuncSetAttribute(k_map_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a));
     return BM_OK;
@@ -428,14 +440,14 @@ int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     uint32_t min_good = 0;
     while ((double)min_good < 0.2 * (double)S) min_good++;
     const uint32_t msl = max_seg_len ? max_seg_len : 1;
-    size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)2 * msl + 3) & ~(size_t)3) + ((msl + 31) / 32 + 1) * 4);
+    size_t smem_a = (size_t)kWarpsPerCta * ((((size_t)msl + 3) & ~(size_t)3) + 2 * ((msl + 31) / 32 + 1) * 4);
     const uint32_t blocks_a = (seg1 - seg0 + kWarpsPerCta - 1) / kWarpsPerCta;
     {
         KScope ks(c, BM_K_SAMPLE);
+        const ReadPlanes rp{c->d_pl.as<uint2>(), c->have_qk ? c->d_qk.as<uint32_t>() : nullptr, c->d_pl_off.as<uint32_t>()};
         k_map_sample<<<blocks_a, kWarpsPerCta * 32, smem_a, c->stream>>>(
-            c->d_seq.as<uint8_t>(), c->d_qual.as<uint8_t>(), c->d_read_off.as<uint64_t>(),
-            c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), seg0, seg1, msl,
-            c->d_k2i.as<int32_t>(), c->d_distok.as<uint32_t>(), p->k, p->q, S, p->avg_base_quality * p->k, min_good,
+            rp, c->d_seg_read.as<uint32_t>(), c->d_seg_start.as<uint32_t>(), c->d_seg_len.as<uint32_t>(), seg0, seg1, msl,
+            c->d_k2i.as<int32_t>(), c->d_distok.as<uint32_t>(), p->k, p->q, S, min_good,
             0u, c->d_rowidx.as<int32_t>(), c->d_segok.as<uint8_t>(), c->d_stats.as<unsigned long long>());
     }
     BM_CK(c, cudaGetLastError());
@@ -504,7 +516,11 @@ int bm_internal_map_finish(bm_ctx* c, const bm_params* p) {
             k_cand_compact<<<(n_seg + 255) / 256, 256, 0, c->stream>>>(
                 c->d_cand_fixed.as<uint32_t>(), c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists,
                 p->max_candidates, c->d_cand.as<uint32_t>(), c->d_cseg.as<uint32_t>(),
-                c->d_stats.as<unsigned long long>());
+                c->d_stats.as<unsigned long long>(), n_seg == c->n_reads ? 1u : 0u);
+            if (n_seg != c->n_reads && c->n_reads)
+                k_count_mapped_reads<<<(c->n_reads + 255) / 256, 256, 0, c->stream>>>(
+                    c->d_read_seg0.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), c->n_reads,
+                    c->d_stats.as<unsigned long long>());
         }
         BM_CK(c, cudaGetLastError());
     } else {

@@ -2,20 +2,20 @@
 //
 // One warp per segment does everything q_gram_mapper::query_sequence does for it (q_gram_mapper.h:414-480) and, because
 // the locator samples the same k-mers of the same segment with the quality filter alone (bucket_locator.h:315-341), the
-// locator's P samples as well:
+// locator's P samples as well.  The segment arrives as bit planes (bm_reads.cu): 12 bytes per 32 bases.
 //
-//   1. streaming pass over the segment, 32 positions per step, everything in registers: base ranks become two ballot
-//      bit planes, phred ranks a warp prefix sum; with a two-step lag the lane that owns position j reads its q-gram
-//      window out of the planes by funnel shift, looks up ONE bit of the (plane-ordered) distinguishability table, and
-//      the k-mer tests of :437-442 are an OR over k-q+1 neighbouring bits plus a prefix-sum difference.
-//   2. the Sampler picks S good k-mers (utils.h:160-178); their hashes (both strands) and q-gram row ids go to shared
-//      memory.
+//   1. lane c takes chunk c of the segment (planes + k-mer quality word) into shared memory; per chunk, the lane that
+//      owns position j funnel-shifts its q-gram window out of the planes and looks up ONE bit of the (plane-ordered)
+//      distinguishability table, a ballot makes it a word; is_highly_distinguishable (:189-196) is then an OR of k-q+1
+//      shifted copies of those words and the k-mer tests of :437-442 two ANDs, 32 k-mers per lane operation.
+//   2. the Sampler picks S good k-mers (utils.h:160-178); their hashes (both strands) go to shared memory.
 //   3. per strand: S coarse rows, 8 B per lane, all loads in flight together; the samples that hit each group of buckets
 //      are counted with a carry-save adder tree on bit planes (7 inputs -> 3 bits in 4 full adders).
-//   4. groups with < F coarse misses (rare) are recounted exactly from the .qgram matrix; best_results()' answer
+//   4. groups with < F coarse misses (rare) are recounted exactly -- from ONE word per sample of the full-resolution
+//      k-mer table when it is resident, else from the k-q+1 .qgram words of every sample; best_results()' answer
 //      (:90-102) is written as the candidate list.
 //
-// No intermediate arrays: the read bytes come in, candidate lists and locator samples go out.
+// No intermediate arrays: the packed read comes in, candidate lists and locator samples go out.
 #include "bm_internal.cuh"
 
 namespace {
@@ -23,13 +23,13 @@ namespace {
 constexpr int kFW = 4;   // warps per CTA
 
 struct FusedArgs {
-    const uint8_t* seq; const uint8_t* qual; const uint64_t* read_off;
+    ReadPlanes rp;
     const uint32_t* seg_read; const uint32_t* seg_start; const uint32_t* seg_len;
     uint32_t seg0, n_seg, NC;                 // NC: plane/mask words per warp in shared memory
     const int32_t* k2i; const uint32_t* distok_p;
-    uint32_t k, q, NQ, S, minq, bq, min_good;
+    uint32_t k, q, NQ, S, min_good;
     const uint2* crows; uint32_t Wcs2, Wc, gshift;
-    const uint32_t* rows32; uint32_t Wp32, NB, F, max_cand;
+    const uint32_t* rows32; const uint32_t* frows32; uint32_t Wp32, NB, F, max_cand;   // frows32: fine k-mer table or nullptr
     uint32_t* cand_fixed; uint32_t* cand_cnt; uint8_t* segok; unsigned long long* stats;
     uint32_t P; uint16_t* sidx; uint32_t* shash;
     uint32_t max_pass; int32_t* rowidx; uint32_t* over_list; uint32_t* n_over;   // hand-over to K2 (repeats)
@@ -75,17 +75,6 @@ __device__ __forceinline__ uint32_t below(const uint32_t (&p)[NP], uint32_t F) {
     return (F >> NP) ? 0xFFFFFFFFu : lt;
 }
 
-// bm_rank_dna4 (seqan3 dna4 char_to_rank incl. IUPAC first-base convention) as two 32-bit tables of 2-bit entries
-// indexed by the low 5 bits of a letter: C,Y,S,B -> 1; G,K -> 2; T,U -> 3; everything else 0
-__device__ __forceinline__ uint32_t rank_dna4_lut(uint32_t c) {
-    // letters @ABCDEFGHIJKLMNO (0..15): B=2:1 C=3:1 G=7:2 K=11:2      PQRSTUVWXYZ (16..26): S=19:1 T=20:3 U=21:3 Y=25:1
-    constexpr uint32_t LO = (1u << 4) | (1u << 6) | (2u << 14) | (2u << 22);
-    constexpr uint32_t HI = (1u << 6) | (3u << 8) | (3u << 10) | (1u << 18);
-    const uint32_t t = (c & 0x10u) ? HI : LO;
-    const uint32_t r = (t >> ((c & 15u) * 2u)) & 3u;
-    return ((c & 0xC0u) == 0x40u) ? r : 0u;           // only 0x40..0x7F are letters (either case)
-}
-
 // zero bit between neighbouring bits of a 16-bit value
 __device__ __forceinline__ uint32_t spread16(uint32_t x) {
     x = (x | (x << 8)) & 0x00FF00FFu;
@@ -121,71 +110,51 @@ k_map_fused(const FusedArgs a) {
     const uint32_t seg = a.seg0 + blockIdx.x * kFW + warp;
     if (seg >= a.n_seg) return;
     const uint32_t S = a.S, NQ = a.NQ, k = a.k, q = a.q;
-    uint32_t* lo = sm + (size_t)warp * (4 * a.NC + 2 * S + 2 * S * NQ);
+    uint32_t* lo = sm + (size_t)warp * (5 * a.NC + 2 * S + 2 * S * NQ);
     uint32_t* hi = lo + a.NC;
-    uint32_t* mA = hi + a.NC;                 // mapper: quality AND distinguishability
+    uint32_t* Dq = hi + a.NC;                 // q-gram distinguishability bits
+    uint32_t* mA = Dq + a.NC;                 // mapper: quality AND distinguishability
     uint32_t* mB = mA + a.NC;                 // locator: quality only
     uint32_t* hsh = mB + a.NC;                // [2][S] sample hashes, forward then reverse complement
-    int32_t* rid = reinterpret_cast<int32_t*>(hsh + 2 * S);   // [2][S][NQ] q-gram row ids
+    int32_t* rid = reinterpret_cast<int32_t*>(hsh + 2 * S);   // [2][S][NQ] q-gram row ids (only without the fine table)
 
-    const uint32_t n = a.seg_len[seg];
-    const uint64_t off = a.read_off[a.seg_read[seg]] + a.seg_start[seg];
+    const uint32_t n = a.seg_len[seg], rd = a.seg_read[seg], sstart = a.seg_start[seg];
+    const uint32_t c0 = __ldg(a.rp.pl_off + rd), c1 = __ldg(a.rp.pl_off + rd + 1);
     const uint32_t nk = (n >= k) ? n - k + 1 : 0;
     const uint32_t nchunk = (nk + 31) / 32, nbch = (n + 31) / 32;
-    const uint32_t qmask = (1u << q) - 1u, nqmask = (1u << NQ) - 1u;
+    const uint32_t nqg = (n >= q) ? n - q + 1 : 0, nqch = (nqg + 31) / 32;      // q-gram start positions
+    const uint32_t qmask = (1u << q) - 1u;
 
-    // ---- 1. streaming pass ---------------------------------------------------------------------------------------------
-    uint32_t lo1 = 0, hi1 = 0;                        // planes of chunk c-1
-    uint32_t Dp = 0;                                  // q-gram distinguishability bits of chunk c-2
-    uint32_t q2 = 0, q1 = 0;                          // phred rank of this lane's position in chunks c-2, c-1
-    uint32_t mn2 = 0xFFFFFFFFu, mn1 = 0xFFFFFFFFu;    // lowest phred rank inside chunks c-2, c-1
-    uint32_t GA = 0, GB = 0;
-    uint32_t klo = 0, khi = 0, kA = 0, kB = 0;        // lane c keeps the plane / mask words of chunk c (c < 32)
-    uint32_t nb = 'A', nq = 33;                       // bytes of the NEXT chunk, requested one step ahead
-    if (lane < n) { nb = a.seq[off + lane]; nq = a.qual[off + lane]; }
-    for (uint32_t c = 0; c <= nbch + 1; c++) {
-        const uint32_t i = c * 32 + lane;
-        const uint32_t cb = nb, cq = nq;
-        nb = 'A'; nq = 33;
-        if (i + 32 < n) { nb = a.seq[off + i + 32]; nq = a.qual[off + i + 32]; }
-        const uint32_t r = rank_dna4_lut(cb), qv = cq - 33u;   // positions >= n: rank 0, phred 0
-        const uint32_t lo0 = __ballot_sync(0xFFFFFFFFu, r & 1u), hi0 = __ballot_sync(0xFFFFFFFFu, r & 2u);
-        const uint32_t mn0 = __reduce_min_sync(0xFFFFFFFFu, (i < n) ? qv : 0xFFFFFFFFu);
-        if (c < 32) { if (lane == c) { klo = lo0; khi = hi0; } }
-        else if (lane == 0) { lo[c] = lo0; hi[c] = hi0; }
-        uint32_t Dc = 0;                               // ... of chunk c-1
-        if (c >= 1) {                                  // q-grams starting in chunk c-1 (windows reach into chunk c)
-            const uint32_t lw = __funnelshift_r(lo1, lo0, lane) & qmask, hw = __funnelshift_r(hi1, hi0, lane) & qmask;
-            const uint32_t idx = (hw << q) | lw;
-            Dc = __ballot_sync(0xFFFFFFFFu, (__ldg(a.distok_p + (idx >> 5)) >> (idx & 31)) & 1u);
-        }
-        if (c >= 2 && c - 2 < nchunk) {                // k-mers starting in chunk c-2
-            const uint32_t j = (c - 2) * 32 + lane;
-            const bool dist = (__funnelshift_r(Dp, Dc, lane) & nqmask) != 0u;     // q_gram_mapper.h:189-196
-            bool qok = j < nk;                         // views::kmer_quality window sum >= b*k (:437-442)
-            if (min(mn2, mn1) < a.bq) {                // else every base of both chunks has phred >= b: all windows pass
-                uint32_t Pi2 = q2, Pi1 = q1;           // inclusive prefix sums of the two chunks
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const uint32_t t2 = __shfl_up_sync(0xFFFFFFFFu, Pi2, o), t1 = __shfl_up_sync(0xFFFFFFFFu, Pi1, o);
-                    if (lane >= o) { Pi2 += t2; Pi1 += t1; }
-                }
-                const uint32_t tot2 = __shfl_sync(0xFFFFFFFFu, Pi2, 31);
-                const uint32_t e = lane + k - 1;
-                const uint32_t pa = __shfl_sync(0xFFFFFFFFu, Pi2, e & 31), pb = __shfl_sync(0xFFFFFFFFu, Pi1, e & 31);
-                const uint32_t qs = ((e < 32) ? pa : tot2 + pb) - (Pi2 - q2);
-                qok = qok && qs >= a.minq;
-            }
-            const uint32_t b = __ballot_sync(0xFFFFFFFFu, qok), m = __ballot_sync(0xFFFFFFFFu, qok && dist);   // :437-442
-            if (c - 2 < 32) { if (lane == c - 2) { kA = m; kB = b; } }
-            else if (lane == 0) { mA[c - 2] = m; mB[c - 2] = b; }
-            GA += __popc(m); GB += __popc(b);
-        }
-        lo1 = lo0; hi1 = hi0; Dp = Dc;
-        q2 = q1; q1 = qv; mn2 = mn1; mn1 = mn0;
+    // ---- 1a. the segment's chunks -> shared memory (chunk nbch is read by the funnel shifts of the last positions) --------
+    for (uint32_t c = lane; c <= nbch; c += 32) {
+        uint32_t l, h, qq;
+        seg_chunk(a.rp, c0, c1, sstart, c, l, h, qq);
+        lo[c] = l; hi[c] = h; mB[c] = qq;
     }
-    if (lane <= nbch + 1) { lo[lane] = klo; hi[lane] = khi; }      // chunks 0..31: one store per lane
-    if (lane < nchunk) { mA[lane] = kA; mB[lane] = kB; }
+    __syncwarp();
+    // ---- 1b. one distinguishability bit per q-gram start (q_gram_mapper.h:189-196, one table bit per q-gram) ---------------
+    for (uint32_t c = 0; c < nqch; c++) {
+        const uint32_t lw = __funnelshift_r(lo[c], lo[c + 1], lane) & qmask, hw = __funnelshift_r(hi[c], hi[c + 1], lane) & qmask;
+        const uint32_t idx = (hw << q) | lw;
+        const uint32_t Dc = __ballot_sync(0xFFFFFFFFu, (__ldg(a.distok_p + (idx >> 5)) >> (idx & 31)) & 1u);
+        if (lane == 0) Dq[c] = Dc;
+    }
+    if (lane == 0) Dq[nqch] = 0u;
+    __syncwarp();
+    // ---- 1c. good k-mers, 32 per lane operation: a k-mer is distinguishable if any of its k-q+1 q-grams is (:189-196) and
+    //          passes the quality test if its window's bit of the quality plane is set (:437-442)
+    uint32_t GA = 0, GB = 0;
+    for (uint32_t c = lane; c < nchunk; c += 32) {
+        const uint32_t d0 = Dq[c], d1 = Dq[c + 1];
+        uint32_t m = d0;
+        for (uint32_t i = 1; i < NQ; i++) m |= __funnelshift_r(d0, d1, i);
+        const uint32_t rem = nk - c * 32;
+        const uint32_t b = mB[c] & (rem >= 32 ? 0xFFFFFFFFu : ((1u << rem) - 1u));
+        m &= b;
+        mA[c] = m; mB[c] = b;
+        GA += __popc(m); GB += __popc(b);
+    }
+    GA = __reduce_add_sync(0xFFFFFFFFu, GA); GB = __reduce_add_sync(0xFFFFFFFFu, GB);
     __syncwarp();
 
     // ---- 2. samples: the locator's P (quality filter only, bucket_locator.h:315-341) and the mapper's S
@@ -199,6 +168,7 @@ k_map_fused(const FusedArgs a) {
         __syncwarp();
     }
     const bool ok = GA >= a.min_good && GA > 0;
+    const bool fine = a.frows32 != nullptr;
     const uint32_t Q = (q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * q)) - 1u);
     uint32_t gathered = 0;
     if (lane == 0) a.segok[seg] = ok ? 1 : 0;
@@ -224,7 +194,7 @@ k_map_fused(const FusedArgs a) {
             hsh[s] = h; hsh[S + s] = hr;
             for (uint32_t i = 0; i < NQ; i++) {
                 const int32_t r0 = __ldg(a.k2i + ((h >> (2 * i)) & Q)), r1 = __ldg(a.k2i + ((hr >> (2 * i)) & Q));
-                rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1;
+                if (!fine) { rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1; }
                 gathered += (r0 >= 0) + (r1 >= 0);
             }
         }
@@ -249,7 +219,7 @@ k_map_fused(const FusedArgs a) {
             hsh[s] = h; hsh[S + s] = hr;
             for (uint32_t i = 0; i < NQ; i++) {
                 const int32_t r0 = __ldg(a.k2i + ((h >> (2 * i)) & Q)), r1 = __ldg(a.k2i + ((hr >> (2 * i)) & Q));
-                rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1;
+                if (!fine) { rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1; }
                 gathered += (r0 >= 0) + (r1 >= 0);
             }
         }
@@ -315,7 +285,8 @@ k_map_fused(const FusedArgs a) {
                             uint32_t word = 0u;
                             if (si < S) {
                                 word = vmask;          // q_gram_mapper.h:399-407
-                                for (uint32_t i = 0; i < NQ; i++) {
+                                if (fine) { word &= __ldg(a.frows32 + (size_t)hs[si] * a.Wp32 + gi); nfine++; }
+                                else for (uint32_t i = 0; i < NQ; i++) {
                                     const int32_t r = rs[si * NQ + i];
                                     if (r >= 0) { word &= __ldg(a.rows32 + (size_t)r * a.Wp32 + gi); nfine++; }
                                 }
@@ -338,7 +309,12 @@ k_map_fused(const FusedArgs a) {
             }
         }
         if (handover) {
-            for (uint32_t t = lane; t < S * NQ; t += 32) a.rowidx[(size_t)list * S * NQ + t] = rs[t];
+            for (uint32_t t = lane; t < S * NQ; t += 32) {
+                int32_t r = 0;
+                if (fine) { const uint32_t si = t / NQ, i = t - si * NQ; r = __ldg(a.k2i + ((hs[si] >> (2 * i)) & Q)); }
+                else r = rs[t];
+                a.rowidx[(size_t)list * S * NQ + t] = r;
+            }
             if (lane == 0) { a.cand_cnt[list] = 0u; a.over_list[atomicAdd(a.n_over, 1u)] = list; }
             continue;
         }
@@ -352,7 +328,7 @@ k_map_fused(const FusedArgs a) {
         // stats[3], stats[4] by bm_internal_map_finish
         unsigned long long* slot = a.stats + 8 + 2 * (blockIdx.x % 60u);
         if (gathered) atomicAdd(slot, (unsigned long long)gathered);
-        atomicAdd(slot + 1, 2ull * S * a.Wc * 4ull + (unsigned long long)nfine * 4ull + 2ull * n);   // bytes loaded
+        atomicAdd(slot + 1, 2ull * S * a.Wc * 4ull + (unsigned long long)nfine * 4ull + (a.rp.qk ? 12ull : 8ull) * nbch);   // bytes loaded
     }
 }
 
@@ -372,13 +348,13 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     while ((double)min_good < 0.2 * (double)S) min_good++;
     const uint32_t msl = max_seg_len ? max_seg_len : 1;
     FusedArgs a;
-    a.seq = c->d_seq.as<uint8_t>(); a.qual = c->d_qual.as<uint8_t>(); a.read_off = c->d_read_off.as<uint64_t>();
+    a.rp = ReadPlanes{c->d_pl.as<uint2>(), c->have_qk ? c->d_qk.as<uint32_t>() : nullptr, c->d_pl_off.as<uint32_t>()};
     a.seg_read = c->d_seg_read.as<uint32_t>(); a.seg_start = c->d_seg_start.as<uint32_t>(); a.seg_len = c->d_seg_len.as<uint32_t>();
     a.seg0 = seg0; a.n_seg = seg1; a.NC = (msl + 31) / 32 + 3;
     a.k2i = c->d_k2i.as<int32_t>(); a.distok_p = c->d_distok_p.as<uint32_t>();
-    a.k = p->k; a.q = p->q; a.NQ = NQ; a.S = S; a.minq = p->avg_base_quality * p->k; a.bq = p->avg_base_quality; a.min_good = min_good;
+    a.k = p->k; a.q = p->q; a.NQ = NQ; a.S = S; a.min_good = min_good;
     a.crows = c->d_krows.as<uint2>(); a.Wcs2 = c->Wcs / 2; a.Wc = c->Wc; a.gshift = 5u - c->krows_logg;
-    a.rows32 = c->d_rows.as<uint32_t>(); a.Wp32 = c->Wp / 4; a.NB = c->NB; a.F = p->mapper_fault; a.max_cand = p->max_candidates;
+    a.rows32 = c->d_rows.as<uint32_t>(); a.frows32 = c->use_ftable ? c->d_frows.as<uint32_t>() : nullptr; a.Wp32 = c->Wp / 4; a.NB = c->NB; a.F = p->mapper_fault; a.max_cand = p->max_candidates;
     a.cand_fixed = c->d_cand_fixed.as<uint32_t>(); a.cand_cnt = c->d_cand_cnt.as<uint32_t>(); a.segok = c->d_segok.as<uint8_t>();
     a.stats = c->d_stats.as<unsigned long long>();
     a.P = (P && P <= 1024 && c->d_lsamp_idx.p && c->d_lsamp_hash.p) ? P : 0;
@@ -386,7 +362,7 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     const uint32_t n_groups = c->Wc * 32;             // coarse bits per row
     a.max_pass = c->map_max_pass >= 0 ? (uint32_t)c->map_max_pass : (n_groups / 8 > 16 ? n_groups / 8 : 16);
     a.rowidx = c->d_rowidx.as<int32_t>(); a.over_list = c->d_map_over.as<uint32_t>(); a.n_over = a.over_list + c->map_over_cap;
-    const size_t smem = (size_t)kFW * (4 * a.NC + 2 * S + 2 * S * NQ) * 4;
+    const size_t smem = (size_t)kFW * (5 * a.NC + 2 * S + 2 * S * NQ) * 4;
     const uint32_t blocks = (seg1 - seg0 + kFW - 1) / kFW;
     const int NP = (S <= 15) ? 4 : (S <= 63 ? 6 : 9);
     KScope ks(c, BM_K_MAP);

@@ -36,7 +36,14 @@ struct LaneLink {
     cudaEvent_t h2d_done = nullptr;
 };
 
-int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
+// the batch on the host: ASCII (seq, qual) or packed (planes, qk or nullptr, pl_off)
+struct HostReads {
+    const uint8_t* seq = nullptr; const uint8_t* qual = nullptr;
+    const uint64_t* planes = nullptr; const uint32_t* qk = nullptr; const uint32_t* pl_off = nullptr;
+    bool packed() const { return planes != nullptr; }
+};
+
+int pipeline_run(bm_ctx* c, const bm_params* p, const HostReads& src, const uint64_t* read_off,
                  uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats,
                  LaneLink* publish, LaneLink* wait_for, uint64_t* n_out);
 
@@ -50,6 +57,8 @@ void lane_share_index(bm_ctx* l, bm_ctx* c) {
     l->zeros_for_d = c->zeros_for_d; l->dist_threshold = c->dist_threshold; l->dist_valid = c->dist_valid;
     l->d_krows.view_of(c->d_krows); l->krows_k = c->krows_k; l->Wc = c->Wc; l->Wcs = c->Wcs;
     l->ktable_logg = c->ktable_logg; l->krows_logg = c->krows_logg;
+    l->d_frows.view_of(c->d_frows); l->frows_k = c->frows_k; l->fine_tried_k = c->fine_tried_k;
+    l->ftable_mode = (c->d_frows.p && c->frows_k) ? 1 : 0;
     l->ktable_mode = c->d_krows.p ? 1 : 0;          // never build in the lane: use the parent's table or none
     l->ktable_max_bytes = c->ktable_max_bytes;
     l->d_gidx_pos.view_of(c->d_gidx_pos); l->d_gidx_off.view_of(c->d_gidx_off); l->gidx_k = c->gidx_k; l->gidx_lb = c->gidx_lb; l->gidx_bshift = c->gidx_bshift;
@@ -71,7 +80,7 @@ __global__ void k_unit_segments(const uint64_t* __restrict__ read_off, uint32_t 
     if (i + 1 == r1) read_seg0[r1] = r1;
 }
 
-int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
+int pipeline_run(bm_ctx* c, const bm_params* p, const HostReads& src, const uint64_t* read_off,
                  uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats,
                  LaneLink* publish, LaneLink* wait_for, uint64_t* n_out) {
     cudaSetDevice(c->device);
@@ -103,8 +112,20 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
     // built while they are in flight.
     const uint64_t base = read_off[0];
     if (read_off[n_reads] < base) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
-    BM_CK(c, c->d_seq.ensure(read_off[n_reads] - base + 16));
-    BM_CK(c, c->d_qual.ensure(read_off[n_reads] - base + 16));
+    const bool packed = src.packed();
+    c->want_ascii = !packed;
+    if (packed) {
+        if (src.pl_off[n_reads] < src.pl_off[0]) BM_FAIL(c, BM_E_ARG, "bm_map_locate_packed: pl_off not monotone");
+        const uint64_t nch = src.pl_off[n_reads] - src.pl_off[0];
+        BM_CK(c, c->d_pl.ensure((nch + 2) * 8));
+        BM_CK(c, c->d_qk.ensure((nch + 2) * 4));
+    } else {
+        const uint64_t nb = read_off[n_reads] - base;
+        BM_CK(c, c->d_seq.ensure(nb + 16));
+        BM_CK(c, c->d_qual.ensure(nb + 16));
+        BM_CK(c, c->d_pl.ensure((nb / 32 + n_reads + 2) * 8));      // upper bound of sum ceil(len/32)
+        BM_CK(c, c->d_qk.ensure((nb / 32 + n_reads + 2) * 4));
+    }
     // the copy stream must not overwrite buffers an earlier call's kernels may still read
     BM_CK(c, cudaStreamSynchronize(c->stream));
     if (wait_for) {
@@ -118,9 +139,18 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
         if (read_off[r0] < base || read_off[r1] < read_off[r0] || read_off[r1] > read_off[n_reads])
             BM_FAIL(c, BM_E_ARG, "bm_reads_upload: read_off not monotone");
         const uint64_t b0 = read_off[r0] - base, nb = read_off[r1] - read_off[r0];
-        if (nb) {
-            BM_CK(c, cudaMemcpyAsync(c->d_seq.as<uint8_t>() + b0, seq + base + b0, nb, cudaMemcpyHostToDevice, c->copy_stream));
-            BM_CK(c, cudaMemcpyAsync(c->d_qual.as<uint8_t>() + b0, qual + base + b0, nb, cudaMemcpyHostToDevice, c->copy_stream));
+        if (packed) {
+            if (src.pl_off[r0] < src.pl_off[0] || src.pl_off[r1] < src.pl_off[r0])
+                BM_FAIL(c, BM_E_ARG, "bm_map_locate_packed: pl_off not monotone");
+            const uint64_t c0 = src.pl_off[r0] - src.pl_off[0], nc = src.pl_off[r1] - src.pl_off[r0];
+            if (nc) {
+                BM_CK(c, cudaMemcpyAsync(c->d_pl.as<uint64_t>() + c0, src.planes + src.pl_off[r0], nc * 8, cudaMemcpyHostToDevice, c->copy_stream));
+                if (src.qk)
+                    BM_CK(c, cudaMemcpyAsync(c->d_qk.as<uint32_t>() + c0, src.qk + src.pl_off[r0], nc * 4, cudaMemcpyHostToDevice, c->copy_stream));
+            }
+        } else if (nb) {
+            BM_CK(c, cudaMemcpyAsync(c->d_seq.as<uint8_t>() + b0, src.seq + base + b0, nb, cudaMemcpyHostToDevice, c->copy_stream));
+            BM_CK(c, cudaMemcpyAsync(c->d_qual.as<uint8_t>() + b0, src.qual + base + b0, nb, cudaMemcpyHostToDevice, c->copy_stream));
         }
         return BM_OK;
     };
@@ -128,6 +158,8 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
     if (r) return r;
     r = bm_internal_reads_begin(c, p, read_off, n_reads);
     if (r) { cudaStreamSynchronize(c->copy_stream); return r; }
+    c->ascii_resident = !packed; c->have_qk = !packed || src.qk != nullptr;
+    c->pack_k = p->k; c->pack_b = p->avg_base_quality;
     // segments are at most read_len long (q_gram_mapper.h:521), which bounds the sampler's shared memory up front
     const uint32_t msl = p->read_len;
     r = bm_internal_map_begin(c, p, c->n_seg_total, msl);   // K0 + buffers for the whole batch
@@ -148,6 +180,12 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
         // read r1's offset / first segment are rewritten by the next chunk with the same values
         BM_CK(c, cudaMemcpyAsync(c->d_read_off.as<uint64_t>() + r0, c->h_off_rel.as<uint64_t>() + r0, (size_t)(r1 - r0 + 1) * 8,
                                  cudaMemcpyHostToDevice, cs));
+        BM_CK(c, cudaMemcpyAsync(c->d_pl_off.as<uint32_t>() + r0, c->h_pl_off.as<uint32_t>() + r0, (size_t)(r1 - r0 + 1) * 4,
+                                 cudaMemcpyHostToDevice, cs));
+        if (packed && src.pl_off[r1] - src.pl_off[0] != c->h_pl_off.as<uint32_t>()[r1]) {
+            cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream);
+            BM_FAIL(c, BM_E_ARG, "bm_map_locate_packed: pl_off is not the layout of bm_pack_layout");
+        }
         if (!unit_segments)
             BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.as<uint32_t>() + r0, c->h_read_seg0.as<uint32_t>() + r0, (size_t)(r1 - r0 + 1) * 4,
                                      cudaMemcpyHostToDevice, cs));
@@ -165,7 +203,11 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
                 c->d_seg_len.as<uint32_t>(), c->d_read_seg0.as<uint32_t>());
             BM_CK(c, cudaGetLastError());
         }
-        r = bm_internal_map_range(c, p, s0, s1, msl);                               // K2a + K2 on this chunk
+        if (!packed) {                                                              // ASCII -> bit planes, on the device
+            r = bm_internal_pack_range(c, p, r0, r1);
+            if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; }
+        }
+        r = bm_internal_map_range(c, p, s0, s1, msl);                               // K2f (or K2a + K2) on this chunk
         if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; }
     }
     t_enq = since();
@@ -201,14 +243,14 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_
     }
     if ((uint64_t)lbase + n > loc_cap) BM_FAIL(c, BM_E_ARG, "bm_map_locate: location buffer too small");
     const void* off = c->locs_filtered ? c->d_loc_off2.p : c->d_loc_off.p;
-    const void* src = c->locs_filtered ? c->d_locs3.p : c->d_locs.p;
+    const void* lsrc = c->locs_filtered ? c->d_locs3.p : c->d_locs.p;
     uint32_t* off_dst = loc_off;
     if (wait_for) {                                 // offsets are rebased on the host: stage them
         BM_CK(c, c->h_lane_off.ensure((size_t)(n_reads + 1) * 4));
         off_dst = c->h_lane_off.as<uint32_t>();
     }
     BM_CK(c, cudaMemcpyAsync(off_dst, off, (size_t)(n_reads + 1) * 4, cudaMemcpyDeviceToHost, c->stream));
-    if (n) BM_CK(c, cudaMemcpyAsync(locs + lbase, src, (size_t)n * sizeof(bm_loc), cudaMemcpyDeviceToHost, c->stream));
+    if (n) BM_CK(c, cudaMemcpyAsync(locs + lbase, lsrc, (size_t)n * sizeof(bm_loc), cudaMemcpyDeviceToHost, c->stream));
     BM_CK(c, cudaStreamSynchronize(c->stream));
     if (wait_for) for (uint32_t i = 1; i <= n_reads; i++) loc_off[i] = off_dst[i] + (uint32_t)lbase;   // [0] is lane 0's last
     if (trace) fprintf(stderr, "[pipe] lane %d reads %u: enqueued %.2f  h2d done %.2f  map+finish %.2f  locate %.2f  download %.2f ms\n",
@@ -223,6 +265,26 @@ extern "C" int bm_pipeline_lanes(bm_ctx* c, uint32_t min_reads) {
     return BM_OK;
 }
 
+extern "C" int bm_map_locate_packed(bm_ctx* c, const bm_params* p, const uint64_t* planes, const uint32_t* qk,
+                                    const uint32_t* pl_off, const uint64_t* read_off, uint32_t n_reads, int filter_best,
+                                    uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats) {
+    if (!c) return BM_E_ARG;
+    if (!p || !read_off || !pl_off || (n_reads && !planes)) BM_FAIL(c, BM_E_ARG, "bm_map_locate_packed: bad arguments");
+    if (n_reads < kPipeMinReads) {
+        int r = bm_reads_upload_packed(c, p, planes, qk, pl_off, read_off, n_reads);
+        if (r) return r;
+        r = bm_map_device(c, p);
+        if (r) return r;
+        r = bm_locate_device(c, p, filter_best);
+        if (r) return r;
+        if (stats) BM_CK(c, cudaMemcpyAsync(stats, c->d_stats.p, 8 * 8, cudaMemcpyDeviceToHost, c->stream));
+        return bm_locate_download(c, loc_off, locs, loc_cap);
+    }
+    HostReads src;
+    src.planes = planes; src.qk = qk; src.pl_off = pl_off;
+    return pipeline_run(c, p, src, read_off, n_reads, filter_best, loc_off, locs, loc_cap, stats, nullptr, nullptr, nullptr);
+}
+
 extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
                              const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs,
                              uint64_t loc_cap, uint64_t* stats) {
@@ -230,8 +292,10 @@ extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, 
     if (!p || !read_off || (n_reads && (!seq || !qual))) BM_FAIL(c, BM_E_ARG, "bm_map_locate: bad arguments");
     if (n_reads < kPipeMinReads)
         return bm_internal_map_locate_serial(c, p, seq, qual, read_off, n_reads, filter_best, loc_off, locs, loc_cap, stats);
+    HostReads src;
+    src.seq = seq; src.qual = qual;
     if (n_reads < c->lane_min_reads || n_reads < 2 * kPipeMinReads || !loc_off || !locs || c->lanes_off)
-        return pipeline_run(c, p, seq, qual, read_off, n_reads, filter_best, loc_off, locs, loc_cap, stats, nullptr, nullptr, nullptr);
+        return pipeline_run(c, p, src, read_off, n_reads, filter_best, loc_off, locs, loc_cap, stats, nullptr, nullptr, nullptr);
 
     // ---- two lanes ----
     cudaSetDevice(c->device);
@@ -257,10 +321,10 @@ extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, 
     uint64_t st0[8] = {0}, st1[8] = {0}, n0 = 0, n1 = 0;
     int r1 = BM_OK;
     std::thread t([&] {
-        r1 = pipeline_run(l, p, seq, qual, read_off + h, n_reads - h, filter_best, loc_off + h, locs, loc_cap, st1, nullptr,
+        r1 = pipeline_run(l, p, src, read_off + h, n_reads - h, filter_best, loc_off + h, locs, loc_cap, st1, nullptr,
                           &link, &n1);
     });
-    int r0 = pipeline_run(c, p, seq, qual, read_off, h, filter_best, loc_off, locs, loc_cap, st0, &link, nullptr, &n0);
+    int r0 = pipeline_run(c, p, src, read_off, h, filter_best, loc_off, locs, loc_cap, st0, &link, nullptr, &n0);
     if (r0) { link.h2d_state.store(-1, std::memory_order_release); link.base.store(-2, std::memory_order_release); }
     t.join();
     // the lane's kernel launches and timings count as this context's

@@ -78,7 +78,7 @@ typedef struct bm_aln {
 
 /* kernel ids for bm_kernel_stats */
 enum { BM_K_ROWPOP = 0, BM_K_INDEX = 1, BM_K_SAMPLE = 2, BM_K_MAP = 3, BM_K_LOCSAMPLE = 4, BM_K_LOCATE = 5,
-       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_GIDX = 10, BM_K_LOCSCAN = 11, BM_K_MAPOVER = 12, BM_K_COUNT = 13 };
+       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_GIDX = 10, BM_K_LOCSCAN = 11, BM_K_MAPOVER = 12, BM_K_PACK = 13, BM_K_COUNT = 14 };
 
 /* ---- context -------------------------------------------------------------------------------------------------- */
 int  bm_ctx_create(int device, bm_ctx** out);
@@ -124,6 +124,13 @@ int bm_index_kmer_table(bm_ctx* ctx, int mode, uint64_t max_bytes);
 int bm_map_handover(bm_ctx* ctx, int max_groups);
 /* k the resident table was built for (0: none) and its size */
 int bm_index_kmer_table_info(bm_ctx* ctx, uint32_t* k, uint64_t* bytes);
+/* full-resolution k-mer table (no reference counterpart): the same precomputed AND, one bit per BUCKET, 4^k rows of
+ * roundup(W,64) bytes (54.8 GB on the 1.7 Gbp reference).  With it the exact recount of a passing group reads ONE 32-bit
+ * word per sample instead of the k-q+1 scattered .qgram words (each of which costs a 128-B DRAM line).  Built together
+ * with the coarse table, only when it fits beside it with room for batches and the locator index; mode 0: never,
+ * 1 (default): when it fits.  Results are identical either way. */
+int bm_index_fine_table(bm_ctx* ctx, int mode);
+int bm_index_fine_table_info(bm_ctx* ctx, uint32_t* k, uint64_t* bytes);
 /* mapper::reset (q_gram_mapper.h:374-378) */
 int bm_index_free(bm_ctx* ctx);
 /* multi-GPU replication (no reference counterpart: the reference is one process).  bm_index_alloc sizes an empty
@@ -134,9 +141,28 @@ int bm_index_device(bm_ctx* ctx, void** dptr, uint64_t* bytes);
 int bm_ref_device(bm_ctx* ctx, void** dptr, uint64_t* bytes);
 
 /* ---- reads ---------------------------------------------------------------------------------------------------- */
-/* H2D of one read batch + segment table (q_gram_mapper.h:509-523 / bucket_locator.h:302-313). */
+/* H2D of one read batch + segment table (q_gram_mapper.h:509-523 / bucket_locator.h:302-313).  The batch is turned into
+ * its device form on arrival (k_pack_reads): 2-bit base planes and one bit per k-mer window "phred sum >= b*k"
+ * (mapper/quality_filter.h:531-534 as used at q_gram_mapper.h:437-442 and bucket_locator.h:323-325), for p->k and
+ * p->avg_base_quality; a later call with other values re-derives the plane from the resident qualities. */
 int bm_reads_upload(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
                     const uint64_t* read_off, uint32_t n_reads);
+/* The packed form, made on the HOST by the FASTQ parser (the reference's parser does the same conversion: seqan3 reads
+ * FASTQ into dna4 / phred ranks, q_gram_mapper.h:493).  Layout: read i owns chunks [pl_off[i], pl_off[i+1]) with
+ * pl_off[i+1] - pl_off[i] = ceil(len_i / 32); chunk c of a read = one uint64: bits 0..31 the low bits and bits 32..63
+ * the high bits of the ranks (A0 C1 G2 T3, IUPAC as bm_reads_upload) of bases 32c..32c+31, bit t = base 32c+t, bases past
+ * the end 0.  qk (same indexing, one uint32 per chunk): bit t = the k bases starting at 32c+t have phred sum >= b*k.
+ *   bm_pack_layout   pl_off[0..n_reads] from read_off.
+ *   bm_pack_reads    packs reads [r0, r1) (callable from several host threads on disjoint ranges).  qual may be NULL
+ *                    (planes only); qk may be NULL (only *n_low is wanted).  *n_low = reads of the range with at least
+ *                    one k-mer window below b*k: when it is 0 for the whole batch the quality plane is all-pass and
+ *                    need not travel (pass qk = NULL to the calls below). */
+int bm_pack_layout(const uint64_t* read_off, uint32_t n_reads, uint32_t* pl_off);
+int bm_pack_reads(const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off, const uint32_t* pl_off,
+                  uint32_t r0, uint32_t r1, uint32_t k, uint32_t b, uint64_t* planes, uint32_t* qk, uint32_t* n_low);
+/* bm_reads_upload for a packed batch.  qk == NULL: every k-mer window passes the quality test for p->avg_base_quality. */
+int bm_reads_upload_packed(bm_ctx* ctx, const bm_params* p, const uint64_t* planes, const uint32_t* qk,
+                           const uint32_t* pl_off, const uint64_t* read_off, uint32_t n_reads);
 int bm_reads_segments(bm_ctx* ctx, uint32_t* n_seg, uint32_t* seg_read, uint32_t* seg_start, uint32_t* seg_len);
 
 /* ---- mapper (replaces q_gram_mapper::query_sequence/query + fault_tolerate_filter, q_gram_mapper.h:39-102,380-480) */
@@ -173,6 +199,10 @@ int bm_locate_device_buffers(bm_ctx* ctx, void** loc_off, void** locs, uint64_t*
 int bm_map_locate(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual,
                   const uint64_t* read_off, uint32_t n_reads, int filter_best, uint32_t* loc_off, bm_loc* locs,
                   uint64_t loc_cap, uint64_t* stats);
+/* bm_map_locate for a packed batch (92 instead of 608 bytes per 300-bp read over PCIe); same records */
+int bm_map_locate_packed(bm_ctx* ctx, const bm_params* p, const uint64_t* planes, const uint32_t* qk,
+                         const uint32_t* pl_off, const uint64_t* read_off, uint32_t n_reads, int filter_best,
+                         uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats);
 /* Opt-in: bm_map_locate cuts batches of at least min_reads reads (default and 0: never) in two halves that run on two
  * pipeline lanes at once, so that the locator / merge / result copy of one half run under the host->device copy of the
  * other.  Same records in the same order; after such a call no batch is resident in ctx.  Not faster on a PCIe-bound

@@ -499,12 +499,17 @@ void orc_map_segments_h(const orc_index* ix, const orc_params* p, const uint8_t*
         anded[t] = st.rows_anded;
     });
     uint64_t mapped = 0, so = 0, sr = 0, tot = 0; uint32_t pos = 0;
+    int64_t last_mapped_read = -1;
     for (uint32_t s = 0; s < n_seg; s++) {
         for (int d = 0; d < 2; d++) {
             cand_off[2 * s + d] = pos;
             for (uint32_t b : lists[2 * s + d]) cand[pos++] = b;
         }
-        if (!lists[2 * s].empty() || !lists[2 * s + 1].empty()) { mapped++; so += lists[2 * s].size(); sr += lists[2 * s + 1].size(); }
+        if (!lists[2 * s].empty() || !lists[2 * s + 1].empty()) {
+            /* q_gram_mapper.h:527-545: mapped_reads counts READS (the segments of a read are consecutive) */
+            if (last_mapped_read != (int64_t)seg_read[s]) { mapped++; last_mapped_read = (int64_t)seg_read[s]; }
+            so += lists[2 * s].size(); sr += lists[2 * s + 1].size();
+        }
     }
     cand_off[2 * n_seg] = pos;
     for (uint64_t a : anded) tot += a;

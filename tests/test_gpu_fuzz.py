@@ -46,9 +46,10 @@ def test_random_parameters_match_oracle(oracle, bm, ctx, idx, pk, kw):
     ctx.ref_upload(d.packed, d.n_bases, d.b_start, d.b_len, d.NB)
     ctx.index_load(k2i, d.q, rows, d.NB)
     try:
-        for tables in (1, 0):
-            ctx.index_kmer_table(tables)
-            ctx.locator_index(tables)
+        for tables in (1, 2, 0):                 # 2: coarse table without the full-resolution table
+            ctx.index_fine_table(0 if tables == 2 else 1)
+            ctx.index_kmer_table(1 if tables else 0)
+            ctx.locator_index(1 if tables else 0)
             goff, gcand, gstats = ctx.map_reads(P, d.seq, qual, d.read_off)
             assert np.array_equal(goff, coff) and np.array_equal(gcand, cand), (tables, pk)
             assert np.array_equal(gstats[:4], stats), (tables, pk)
@@ -59,5 +60,6 @@ def test_random_parameters_match_oracle(oracle, bm, ctx, idx, pk, kw):
             g3, gb = ctx.locate_download()
             assert np.array_equal(g3, foff) and np.array_equal(gb, best), (tables, pk)
     finally:
+        ctx.index_fine_table(1)
         ctx.index_kmer_table(1)
         ctx.locator_index(1)

@@ -44,11 +44,15 @@ def test_index_load_roundtrip(oracle, bm, ctx):
     (dict(read_len=300, sub=0.01, indel=0.001), dict(s=20, e=0.6, k=14, b=10)),
     (dict(read_len=800, n_reads=500), dict()),           # long reads: 5 segments each
 ])
-@pytest.mark.parametrize("ktable", [1, 0, 8, 32, -1, -2])   # -1 / -2: table on, every list / lists with > 1 passing group handed to K2
+# -1 / -2: table on, every list / lists with > 1 passing group handed to K2; -3: coarse table on, full-resolution table off
+# (passing groups recounted from the .qgram words)
+@pytest.mark.parametrize("ktable", [1, 0, 8, 32, -1, -2, -3])
 def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     d = dataset(**kw)
     handover = {-1: 0, -2: 1}.get(ktable, -1)
+    fine = 0 if ktable == -3 else 1
     ktable = 1 if ktable < 0 else ktable
+    ctx.index_fine_table(fine)
     ctx.index_kmer_table(ktable)
     ctx.map_handover(handover)
     k2i, n_rows, rows = _index(oracle, d, d.frac)
@@ -67,6 +71,9 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     assert np.array_equal(gstats[:4], stats)
     assert stats[0] > 0.9 * len(segs[0]) or kw.get("read_len") == 800
     tk, tbytes = ctx.index_kmer_table_info()
+    fk, fbytes = ctx.index_fine_table_info()
+    assert (fk, fbytes) == ((P.k, 4 ** P.k * ((((d.NB + 7) >> 3) + 63) & ~63)) if (ktable and fine) else (0, 0))
+    ctx.index_fine_table(1)
     ctx.index_kmer_table(1)   # session-wide context: back to the default for the tests that follow
     ctx.map_handover(-1)
     wp = (((d.NB + 7) >> 3) + 63) & ~63                       # padded row bytes
