@@ -231,7 +231,7 @@ int bm_internal_kmer_table_prepare(bm_ctx* c, uint32_t k) {
     const uint32_t logg = c->ktable_logg;                          // buckets per coarse bit = 1 << logg
     c->Wc = ((Wp32 << (5 - logg)) + 31) / 32;
     c->Wcs = (c->Wc + 15u) & ~15u;
-    const uint64_t bytes = n_kmers * c->Wcs * 4;
+    const uint64_t bytes = (n_kmers + 1) * c->Wcs * 4;             // + one all-zero row (the fused mapper's padding samples)
     c->d_krows.release(); c->krows_k = 0; c->d_frows.release(); c->frows_k = 0;
     // The locator's genome k-mer index needs ~16 B per base of scratch while it is built: build it BEFORE the tables take
     // their memory (it is wanted at the first locator call anyway), so that the fine table can use what is left.

@@ -16,6 +16,8 @@
 //      (:90-102) is written as the candidate list.
 //
 // No intermediate arrays: the packed read comes in, candidate lists and locator samples go out.
+#include <cstdlib>
+
 #include "bm_internal.cuh"
 
 namespace {
@@ -25,13 +27,16 @@ constexpr int kFW = 4;   // warps per CTA
 struct FusedArgs {
     ReadPlanes rp;
     const uint32_t* seg_read; const uint32_t* seg_start; const uint32_t* seg_len;
-    uint32_t seg0, n_seg, NC;                 // NC: plane/mask words per warp in shared memory
+    uint32_t seg0, n_seg, NC, S4, SW;         // NC: plane/mask words per warp in shared memory; S4: hash row stride; SW: words per warp
     const int32_t* k2i; const uint32_t* distok_p;
     uint32_t k, q, NQ, S, min_good;
-    const uint2* crows; uint32_t Wcs2, Wc, gshift;
+    const uint2* crows; uint32_t Wcs2, Wc, gshift, zero_row;   // zero_row: index of the all-zero row behind the coarse table
     const uint32_t* rows32; const uint32_t* frows32; uint32_t Wp32, NB, F, max_cand;   // frows32: fine k-mer table or nullptr
     uint32_t* cand_fixed; uint32_t* cand_cnt; uint8_t* segok; unsigned long long* stats;
     uint32_t P; uint16_t* sidx; uint32_t* shash;
+    uint32_t ldmode;
+    uint32_t fm[9];                           // bit planes of the hits a group needs: S - F + 1
+    uint32_t all_indexed;                     // every q-gram has a row (-f 1): no kmer_to_index look-ups needed for the counter
     uint32_t max_pass; int32_t* rowidx; uint32_t* over_list; uint32_t* n_over;   // hand-over to K2 (repeats)
 };
 
@@ -64,6 +69,22 @@ __device__ __forceinline__ void add16(uint32_t (&p)[NP], const uint32_t (&m)[16]
     add7<NP, 7>(p, m);
     add_w<NP>(p, m[14] ^ m[15], m[14] & m[15], 0u);
 }
+// hits of up to 15 samples per group as 4 bit planes: a carry-save tree of 11 full adders (m[15] is ignored)
+__device__ __forceinline__ void count15(const uint32_t (&m)[16], uint32_t (&p)[4]) {
+    uint32_t sa, ca, sb, cb, sc, cc, sd, cd, se, ce, sf, cf, cg, sh, ch, si, ci, cj;
+    fa(m[0], m[1], m[2], sa, ca);
+    fa(m[3], m[4], m[5], sb, cb);
+    fa(m[6], m[7], m[8], sc, cc);
+    fa(m[9], m[10], m[11], sd, cd);
+    fa(m[12], m[13], m[14], se, ce);
+    fa(sa, sb, sc, sf, cf);
+    fa(sd, se, sf, p[0], cg);
+    fa(ca, cb, cc, sh, ch);
+    fa(cd, ce, cf, si, ci);
+    fa(sh, si, cg, p[1], cj);
+    fa(ch, ci, cj, p[2], p[3]);
+}
+
 template <int NP>
 __device__ __forceinline__ uint32_t below(const uint32_t (&p)[NP], uint32_t F) {
     uint32_t lt = 0u, eq = 0xFFFFFFFFu;
@@ -75,6 +96,19 @@ __device__ __forceinline__ uint32_t below(const uint32_t (&p)[NP], uint32_t F) {
     return (F >> NP) ? 0xFFFFFFFFu : lt;
 }
 
+// groups with at least `need` hits, need given as one all-ones / all-zeros mask per bit plane (fm[i] = bit i of need):
+// the bit-sliced form of hits >= need, two logic operations per plane
+template <int NP>
+__device__ __forceinline__ uint32_t at_least(const uint32_t (&p)[NP], const uint32_t* fm) {
+    uint32_t lt = 0u, eq = 0xFFFFFFFFu;
+#pragma unroll
+    for (int i = NP - 1; i >= 0; i--) {
+        lt |= eq & ~p[i] & fm[i];
+        eq &= ~(p[i] ^ fm[i]);
+    }
+    return ~lt;
+}
+
 // zero bit between neighbouring bits of a 16-bit value
 __device__ __forceinline__ uint32_t spread16(uint32_t x) {
     x = (x | (x << 8)) & 0x00FF00FFu;
@@ -84,10 +118,22 @@ __device__ __forceinline__ uint32_t spread16(uint32_t x) {
     return x;
 }
 // seqan3 views::kmer_hash(ungapped{k}) of the k-mer at `pos`, from the two bit planes (bit t of a plane word = base t)
-__device__ __forceinline__ uint32_t hash_from_planes(const uint32_t* lo, const uint32_t* hi, uint32_t pos, uint32_t k) {
+__device__ __forceinline__ uint32_t hash_from_planes(const uint2* pl, uint32_t pos, uint32_t k) {
     const uint32_t c = pos >> 5, sh = pos & 31;
-    const uint32_t lw = __funnelshift_r(lo[c], lo[c + 1], sh), hw = __funnelshift_r(hi[c], hi[c + 1], sh);
+    const uint2 p0 = pl[c], p1 = pl[c + 1];
+    const uint32_t lw = __funnelshift_r(p0.x, p1.x, sh), hw = __funnelshift_r(p0.y, p1.y, sh);
     return (spread16(__brev(hw) >> (32 - k)) << 1) | spread16(__brev(lw) >> (32 - k));   // first base most significant
+}
+
+// one scattered 32-bit word of the full-resolution table (tuning: the L2 prefetch-size hint decides how much of the 128-B
+// line a miss brings in from DRAM)
+__device__ __forceinline__ uint32_t ld_word(const uint32_t* p, uint32_t mode) {
+    uint32_t v;
+    if (mode == 1) asm volatile("ld.global.nc.L2::64B.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    else if (mode == 2) asm volatile("ld.global.L2::64B.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    else if (mode == 3) asm volatile("ld.global.nc.L1::no_allocate.L2::64B.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    else v = __ldg(p);
+    return v;
 }
 
 // 32x32 bit-matrix transpose across the warp: lane i holds row i (bit j = column j) and ends up with column i
@@ -105,18 +151,18 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t x, uint32_t lane) {
 template <int NP, int MINB>
 __global__ void __launch_bounds__(kFW * 32, MINB)
 k_map_fused(const FusedArgs a) {
-    extern __shared__ uint32_t sm[];
+    extern __shared__ uint4 sm4[];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t seg = a.seg0 + blockIdx.x * kFW + warp;
     if (seg >= a.n_seg) return;
     const uint32_t S = a.S, NQ = a.NQ, k = a.k, q = a.q;
-    uint32_t* lo = sm + (size_t)warp * (5 * a.NC + 2 * S + 2 * S * NQ);
-    uint32_t* hi = lo + a.NC;
-    uint32_t* Dq = hi + a.NC;                 // q-gram distinguishability bits
+    // per-warp shared memory (a.SW words, a multiple of 4): [2][S4] sample hashes (16-B aligned rows) | planes | D | mA | mB | rid
+    uint32_t* hsh = reinterpret_cast<uint32_t*>(sm4) + (size_t)warp * a.SW;
+    uint2* pls = reinterpret_cast<uint2*>(hsh + 2 * a.S4);   // {lo, hi} bit planes of the segment, 32 bases per entry
+    uint32_t* Dq = reinterpret_cast<uint32_t*>(pls + a.NC);   // q-gram distinguishability bits
     uint32_t* mA = Dq + a.NC;                 // mapper: quality AND distinguishability
     uint32_t* mB = mA + a.NC;                 // locator: quality only
-    uint32_t* hsh = mB + a.NC;                // [2][S] sample hashes, forward then reverse complement
-    int32_t* rid = reinterpret_cast<int32_t*>(hsh + 2 * S);   // [2][S][NQ] q-gram row ids (only without the fine table)
+    int32_t* rid = reinterpret_cast<int32_t*>(mB + a.NC);     // [2][S][NQ] q-gram row ids (only without the fine table)
 
     const uint32_t n = a.seg_len[seg], rd = a.seg_read[seg], sstart = a.seg_start[seg];
     const uint32_t c0 = __ldg(a.rp.pl_off + rd), c1 = __ldg(a.rp.pl_off + rd + 1);
@@ -129,17 +175,33 @@ k_map_fused(const FusedArgs a) {
     for (uint32_t c = lane; c <= nbch; c += 32) {
         uint32_t l, h, qq;
         seg_chunk(a.rp, c0, c1, sstart, c, l, h, qq);
-        lo[c] = l; hi[c] = h; mB[c] = qq;
+        pls[c] = make_uint2(l, h); mB[c] = qq;
     }
     __syncwarp();
     // ---- 1b. one distinguishability bit per q-gram start (q_gram_mapper.h:189-196, one table bit per q-gram) ---------------
-    for (uint32_t c = 0; c < nqch; c++) {
-        const uint32_t lw = __funnelshift_r(lo[c], lo[c + 1], lane) & qmask, hw = __funnelshift_r(hi[c], hi[c + 1], lane) & qmask;
-        const uint32_t idx = (hw << q) | lw;
-        const uint32_t Dc = __ballot_sync(0xFFFFFFFFu, (__ldg(a.distok_p + (idx >> 5)) >> (idx & 31)) & 1u);
-        if (lane == 0) Dq[c] = Dc;
+    {
+        uint2 p0 = pls[0];
+        for (uint32_t c = 0; c < nqch; c += 4) {
+            uint32_t bit[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                bit[t] = 0u;
+                if (c + t < nqch) {
+                    const uint2 p1 = pls[c + t + 1];
+                    const uint32_t lw = __funnelshift_r(p0.x, p1.x, lane) & qmask, hw = __funnelshift_r(p0.y, p1.y, lane) & qmask;
+                    const uint32_t idx = hw * (qmask + 1u) + lw;
+                    bit[t] = (__ldg(a.distok_p + (idx >> 5)) >> (idx & 31)) & 1u;
+                    p0 = p1;
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const uint32_t Dc = __ballot_sync(0xFFFFFFFFu, bit[t]);
+                if (lane == (uint32_t)t && c + t < nqch) Dq[c + t] = Dc;
+            }
+        }
+        if (lane == 0) Dq[nqch] = 0u;
     }
-    if (lane == 0) Dq[nqch] = 0u;
     __syncwarp();
     // ---- 1c. good k-mers, 32 per lane operation: a k-mer is distinguishable if any of its k-q+1 q-grams is (:189-196) and
     //          passes the quality test if its window's bit of the quality plane is set (:437-442)
@@ -169,6 +231,7 @@ k_map_fused(const FusedArgs a) {
     }
     const bool ok = GA >= a.min_good && GA > 0;
     const bool fine = a.frows32 != nullptr;
+    if (lane >= S && lane < a.S4) { hsh[lane] = a.zero_row; hsh[a.S4 + lane] = a.zero_row; }   // S <= 15: see the coarse vote
     const uint32_t Q = (q >= 16) ? 0xFFFFFFFFu : ((1u << (2 * q)) - 1u);
     uint32_t gathered = 0;
     if (lane == 0) a.segok[seg] = ok ? 1 : 0;
@@ -179,7 +242,7 @@ k_map_fused(const FusedArgs a) {
         uint32_t pos = 0, h = 0xFFFFFFFFu;             // segment shorter than k: no usable locator sample
         if (want && nk) {
             pos = select_good(isB ? mB : mA, nchunk, sample_index(s, isB ? a.P : S, isB ? GB : GA));
-            h = hash_from_planes(lo, hi, pos, k);
+            h = hash_from_planes(pls, pos, k);
         }
         if (isB && want) {
             a.sidx[(size_t)seg * a.P + s] = (uint16_t)pos;
@@ -191,8 +254,9 @@ k_map_fused(const FusedArgs a) {
         }
         if (!isB && want) {
             const uint32_t hr = bm_revcomp_hash(h, k);
-            hsh[s] = h; hsh[S + s] = hr;
-            for (uint32_t i = 0; i < NQ; i++) {
+            hsh[s] = h; hsh[a.S4 + s] = hr;
+            if (fine && a.all_indexed) gathered += 2 * NQ;
+            else for (uint32_t i = 0; i < NQ; i++) {
                 const int32_t r0 = __ldg(a.k2i + ((h >> (2 * i)) & Q)), r1 = __ldg(a.k2i + ((hr >> (2 * i)) & Q));
                 if (!fine) { rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1; }
                 gathered += (r0 >= 0) + (r1 >= 0);
@@ -203,7 +267,7 @@ k_map_fused(const FusedArgs a) {
             uint32_t pos = 0, h = 0xFFFFFFFFu;
             if (nk) {
                 pos = select_good(mB, nchunk, sample_index(s, a.P, GB));
-                h = hash_from_planes(lo, hi, pos, k);
+                h = hash_from_planes(pls, pos, k);
             }
             a.sidx[(size_t)seg * a.P + s] = (uint16_t)pos;
             a.shash[(size_t)seg * a.P + s] = h;
@@ -214,10 +278,11 @@ k_map_fused(const FusedArgs a) {
         }
         for (uint32_t s = lane; s < S; s += 32) {
             const uint32_t pos = select_good(mA, nchunk, sample_index(s, S, GA));
-            const uint32_t h = hash_from_planes(lo, hi, pos, k);
+            const uint32_t h = hash_from_planes(pls, pos, k);
             const uint32_t hr = bm_revcomp_hash(h, k);
-            hsh[s] = h; hsh[S + s] = hr;
-            for (uint32_t i = 0; i < NQ; i++) {
+            hsh[s] = h; hsh[a.S4 + s] = hr;
+            if (fine && a.all_indexed) gathered += 2 * NQ;
+            else for (uint32_t i = 0; i < NQ; i++) {
                 const int32_t r0 = __ldg(a.k2i + ((h >> (2 * i)) & Q)), r1 = __ldg(a.k2i + ((hr >> (2 * i)) & Q));
                 if (!fine) { rid[s * NQ + i] = r0; rid[(S + s) * NQ + i] = r1; }
                 gathered += (r0 >= 0) + (r1 >= 0);
@@ -227,9 +292,20 @@ k_map_fused(const FusedArgs a) {
     __syncwarp();
 
     // ---- 3. + 4. per strand: coarse vote, exact recount of passing groups ----------------------------------------------------
+    // The reverse strand's coarse rows are requested into L2 now, one (sample, 128-B line) per lane, so that they arrive
+    // while the forward strand is voted on and recounted: one DRAM round trip less on the warp's critical path.
+    {
+        const uint32_t lines = (a.Wc * 4u + 127u) / 128u;
+        const uint32_t inv = 65535u / lines + 1u;      // t / lines == (t * inv) >> 16 for the small t of this loop
+        for (uint32_t t = lane; t < S * lines; t += 32) {
+            const uint32_t si = (lines * S < 4096u) ? ((t * inv) >> 16) : t / lines, ln = t - si * lines;
+            const uint2* pp = a.crows + (size_t)hsh[a.S4 + si] * a.Wcs2 + ln * 16u;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
+        }
+    }
     uint32_t nfine = 0;
     for (uint32_t strand = 0; strand < 2; strand++) {
-        const uint32_t* hs = hsh + strand * S;
+        const uint32_t* hs = hsh + strand * a.S4;
         const int32_t* rs = rid + (size_t)strand * S * NQ;
         const uint32_t list = 2 * seg + strand;
         uint32_t best = 0xFFFFFFFFu, count = 0, npass = 0;
@@ -238,26 +314,43 @@ k_map_fused(const FusedArgs a) {
         for (uint32_t w0 = 0; 2 * w0 < a.Wc; w0 += 32) {
             const uint32_t w = w0 + lane;              // this lane: coarse words 2w, 2w+1
             const bool act = 2 * w < a.Wc;
-            const uint2* colp = a.crows + (act ? w : 0);
+            const uint2* colp = a.crows + (act ? w : 0);   // idle lanes read column 0; their result is dropped below
             uint32_t px[NP], py[NP];
-#pragma unroll
-            for (int i = 0; i < NP; i++) { px[i] = 0u; py[i] = 0u; }
-            for (uint32_t s0 = 0; s0 < S; s0 += 16) {
+            if constexpr (NP == 4) {
+                // S <= 15: all rows in flight at once, hashes fetched four at a time, one exact 15-input counter
                 uint32_t mx[16], my[16];               // 1 = some bucket of the group holds the sample
+                const uint4* h4 = reinterpret_cast<const uint4*>(hs);
 #pragma unroll
-                for (int b = 0; b < 16; b++) {
-                    mx[b] = 0u; my[b] = 0u;            // no sample / no such word: no hit
-                    if (s0 + b < S && act) {
-                        const uint2 v = __ldg(colp + (size_t)hs[s0 + b] * a.Wcs2);
-                        mx[b] = v.x; my[b] = v.y;
+                for (int b4 = 0; b4 < 4; b4++) {
+                    const uint4 hv = h4[b4];           // entries past S name the all-zero row behind the table
+                    const uint32_t hh[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+                    for (int t = 0; t < 4; t++) {
+                        const uint2 v = __ldg(colp + (size_t)hh[t] * a.Wcs2);
+                        mx[4 * b4 + t] = v.x; my[4 * b4 + t] = v.y;
                     }
                 }
-                add16<NP>(px, mx);
-                add16<NP>(py, my);
+                count15(mx, px);
+                count15(my, py);
+            } else {
+#pragma unroll
+                for (int i = 0; i < NP; i++) { px[i] = 0u; py[i] = 0u; }
+                for (uint32_t s0 = 0; s0 < S; s0 += 16) {
+                    uint32_t mx[16], my[16];
+#pragma unroll
+                    for (int b = 0; b < 16; b++) {
+                        mx[b] = 0u; my[b] = 0u;        // no sample: no hit
+                        if (s0 + b < S) {
+                            const uint2 v = __ldg(colp + (size_t)hs[s0 + b] * a.Wcs2);
+                            mx[b] = v.x; my[b] = v.y;
+                        }
+                    }
+                    add16<NP>(px, mx);
+                    add16<NP>(py, my);
+                }
             }
             // px, py count HITS per group: fewer than F misses <=> at least S-F+1 hits
-            const uint32_t need = (S >= a.F) ? S - a.F + 1u : 0u;
-            const uint32_t passx = act ? ~below<NP>(px, need) : 0u, passy = act ? ~below<NP>(py, need) : 0u;
+            const uint32_t passx = act ? at_least<NP>(px, a.fm) : 0u, passy = act ? at_least<NP>(py, a.fm) : 0u;
             // On a repeat-rich reference a read made of repeat k-mers passes the coarse vote almost everywhere; recounting
             // group after group would then cost more than gathering the full-width rows once: such lists go to K2.
             npass += __reduce_add_sync(0xFFFFFFFFu, __popc(passx) + __popc(passy));
@@ -285,7 +378,7 @@ k_map_fused(const FusedArgs a) {
                             uint32_t word = 0u;
                             if (si < S) {
                                 word = vmask;          // q_gram_mapper.h:399-407
-                                if (fine) { word &= __ldg(a.frows32 + (size_t)hs[si] * a.Wp32 + gi); nfine++; }
+                                if (fine) { word &= ld_word(a.frows32 + (size_t)hs[si] * a.Wp32 + gi, a.ldmode); nfine++; }
                                 else for (uint32_t i = 0; i < NQ; i++) {
                                     const int32_t r = rs[si * NQ + i];
                                     if (r >= 0) { word &= __ldg(a.rows32 + (size_t)r * a.Wp32 + gi); nfine++; }
@@ -354,6 +447,7 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     a.k2i = c->d_k2i.as<int32_t>(); a.distok_p = c->d_distok_p.as<uint32_t>();
     a.k = p->k; a.q = p->q; a.NQ = NQ; a.S = S; a.min_good = min_good;
     a.crows = c->d_krows.as<uint2>(); a.Wcs2 = c->Wcs / 2; a.Wc = c->Wc; a.gshift = 5u - c->krows_logg;
+    a.zero_row = 1u << (2 * p->k);
     a.rows32 = c->d_rows.as<uint32_t>(); a.frows32 = c->use_ftable ? c->d_frows.as<uint32_t>() : nullptr; a.Wp32 = c->Wp / 4; a.NB = c->NB; a.F = p->mapper_fault; a.max_cand = p->max_candidates;
     a.cand_fixed = c->d_cand_fixed.as<uint32_t>(); a.cand_cnt = c->d_cand_cnt.as<uint32_t>(); a.segok = c->d_segok.as<uint8_t>();
     a.stats = c->d_stats.as<unsigned long long>();
@@ -362,7 +456,10 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     const uint32_t n_groups = c->Wc * 32;             // coarse bits per row
     a.max_pass = c->map_max_pass >= 0 ? (uint32_t)c->map_max_pass : (n_groups / 8 > 16 ? n_groups / 8 : 16);
     a.rowidx = c->d_rowidx.as<int32_t>(); a.over_list = c->d_map_over.as<uint32_t>(); a.n_over = a.over_list + c->map_over_cap;
-    const size_t smem = (size_t)kFW * (5 * a.NC + 2 * S + 2 * S * NQ) * 4;
+    a.S4 = (S + 3u) & ~3u;
+    if (a.S4 < 16 && S <= 15) a.S4 = 16;                  // the S <= 15 path reads four uint4 of hashes per strand
+    a.SW = (2 * a.S4 + 5 * a.NC + 2 * S * NQ + 3u) & ~3u;
+    const size_t smem = (size_t)kFW * a.SW * 4;
     const uint32_t blocks = (seg1 - seg0 + kFW - 1) / kFW;
     const int NP = (S <= 15) ? 4 : (S <= 63 ? 6 : 9);
     KScope ks(c, BM_K_MAP);
@@ -372,8 +469,20 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
             BM_CK(c, cudaFuncSetAttribute(k_map_fused<NPv, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         k_map_fused<NPv, MB><<<blocks, kFW * 32, smem, c->stream>>>(a);                                            \
     } while (0)
-    // min CTAs per SM: 9 x 4 warps at 56 registers; forcing 12 (40 registers) spills and was measured no faster
-    if (NP == 4) BM_FUSED(4, 9); else if (NP == 6) BM_FUSED(6, 8); else BM_FUSED(9, 6);
+    // min CTAs per SM (occupancy against registers per thread); $BM_K2F_MINB overrides the default for tuning runs
+    {
+        const uint32_t need = (S >= p->mapper_fault) ? S - p->mapper_fault + 1u : 0u;   // fewer than F misses <=> >= S-F+1 hits
+        for (int i = 0; i < 9; i++) a.fm[i] = ((need >> i) & 1u) ? 0xFFFFFFFFu : 0u;
+    }
+    a.all_indexed = (c->n_rows == (1u << (2 * c->q))) ? 1u : 0u;
+    const char* lde = getenv("BM_K2F_LD");
+    a.ldmode = lde ? (uint32_t)atoi(lde) : 3u;
+    const char* mbe = getenv("BM_K2F_MINB");
+    const int minb = mbe ? atoi(mbe) : 0;
+    if (NP == 4) {
+        if (minb == 8) BM_FUSED(4, 8); else if (minb == 10) BM_FUSED(4, 10); else if (minb == 9) BM_FUSED(4, 9);
+        else BM_FUSED(4, 12);                          // 48 warps per SM at 40 registers: measured fastest (2.36 vs 2.55 ms at 9)
+    } else if (NP == 6) BM_FUSED(6, 8); else BM_FUSED(9, 6);
 #undef BM_FUSED
     BM_CK(c, cudaGetLastError());
     return BM_OK;

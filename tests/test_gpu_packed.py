@@ -58,19 +58,18 @@ def test_packed_batch_equals_ascii_batch_and_oracle(oracle, bm, ctx, kw, pk, mix
         ctx.reads_upload(P, d.seq, qual, d.read_off)
         a = _device(ctx, P, False)
         planes, qk, pl_off, low = bm.pack_reads(ctx.lib, d.seq, qual, d.read_off, P.k, P.avg_base_quality)
-        assert (low > 0) == mixed or not mixed
         ctx.reads_upload_packed(P, planes, qk if low else None, pl_off, d.read_off)
         b = _device(ctx, P, False)
-        for x, y in zip(a, b):
-            assert np.array_equal(x, y)
+        for i, (x, y) in enumerate(zip(a, b)):
+            assert np.array_equal(x[:4], y[:4]) if i == 2 else np.array_equal(x, y)   # stats[4] (bytes loaded) differs
         assert np.array_equal(a[0], ocoff) and np.array_equal(a[1], ocand) and np.array_equal(a[2][:4], ostats)
         assert np.array_equal(a[3], oloff) and np.array_equal(a[4], olocs)
         # the quality plane always travels when given, even if all-pass
         if not low:
             ctx.reads_upload_packed(P, planes, qk, pl_off, d.read_off)
             c = _device(ctx, P, False)
-            for x, y in zip(a, c):
-                assert np.array_equal(x, y)
+            for i, (x, y) in enumerate(zip(a, c)):
+                assert np.array_equal(x[:4], y[:4]) if i == 2 else np.array_equal(x, y)
     finally:
         ctx.index_kmer_table(1)
         ctx.locator_index(1)
