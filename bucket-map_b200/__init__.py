@@ -13,9 +13,11 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libbucketmap_b200.so")
 
 (K_ROWPOP, K_INDEX, K_SAMPLE, K_MAP, K_LOCSAMPLE, K_LOCATE, K_MERGE, K_ALIGN, K_AUX, K_KTABLE, K_GIDX, K_LOCSCAN,
- K_MAPOVER, K_PACK, K_COUNT) = range(15)
+ K_MAPOVER, K_PACK, K_GATHER, K_COUNT) = range(16)
 KERNEL_NAMES = ["rowpop", "index_build", "map_sample", "map_vote", "loc_sample", "locate", "merge", "align", "aux",
-                "kmer_table", "locator_index", "locate_scan", "map_vote_handover", "pack_reads"]
+                "kmer_table", "locator_index", "locate_scan", "map_vote_handover", "pack_reads", "gather_pack"]
+COMM_ID_BYTES = 128
+PEER_HANDLE_BYTES = 128
 
 
 class Params(C.Structure):
@@ -80,6 +82,21 @@ SIGNATURES = {
     "bm_pipeline_lanes": (C.c_int, [_vp, C.c_uint32]),
     "bm_align_device": (C.c_int, [_vp, C.POINTER(Params)]),
     "bm_align_download": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "bm_comm_unique_id": (C.c_int, [_vp]),
+    "bm_comm_init": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "bm_comm_attach": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "bm_comm_destroy": (C.c_int, [_vp]),
+    "bm_bcast_index": (C.c_int, [_vp, C.c_int]),
+    "bm_bcast_ref": (C.c_int, [_vp, C.c_int]),
+    "bm_gather_open": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64, _vp]),
+    "bm_gather_connect": (C.c_int, [_vp, _vp]),
+    "bm_gather_results": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "bm_gather_sync": (C.c_int, [_vp]),
+    "bm_gather_join": (C.c_int, [_vp]),
+    "bm_gather_device_buffers": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_uint64),
+                                           C.POINTER(C.c_uint64)]),
+    "bm_gather_download": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "bm_gather_close": (C.c_int, [_vp]),
     "bm_timer_start": (C.c_int, [_vp]),
     "bm_timer_stop": (C.c_int, [_vp, C.POINTER(C.c_float)]),
     "bm_kernel_timing": (C.c_int, [_vp, C.c_int]),
@@ -351,10 +368,67 @@ class Context:
         n = len(read_off) - 1
         stats = np.zeros(8, np.uint64)
         self._ck(self.lib.bm_map_locate_packed(self.h, C.byref(P), _ptr(planes), _ptr(qk), _ptr(pl_off), _ptr(read_off), n,
-                                               int(filter_best), _ptr(out_off), _ptr(out_locs), len(out_locs),
-                                               _ptr(stats)), "bm_map_locate_packed")
+                                               int(filter_best), _ptr(out_off), _ptr(out_locs),
+                                               len(out_locs) if out_locs is not None else 0, _ptr(stats)),
+                 "bm_map_locate_packed")
         self.n_reads = n
-        return int(out_off[n]), stats
+        return (int(out_off[n]) if out_off is not None else -1), stats
+
+    # ---- several GPUs ----------------------------------------------------------------------------------------------
+    def comm_unique_id(self):
+        buf = (C.c_uint8 * COMM_ID_BYTES)()
+        rc = self.lib.bm_comm_unique_id(buf)
+        if rc:
+            raise BucketMapError(f"bm_comm_unique_id failed ({rc}): libnccl.so.2 not loadable?")
+        return bytes(buf)
+
+    def comm_init(self, uid, nranks, rank):
+        buf = (C.c_uint8 * COMM_ID_BYTES).from_buffer_copy(uid)
+        self._ck(self.lib.bm_comm_init(self.h, buf, nranks, rank), "bm_comm_init")
+
+    def bcast_index(self, root=0):
+        self._ck(self.lib.bm_bcast_index(self.h, root), "bm_bcast_index")
+
+    def bcast_ref(self, root=0):
+        self._ck(self.lib.bm_bcast_ref(self.h, root), "bm_bcast_ref")
+
+    def gather_open(self, rank, nranks, root, max_reads, max_locs):
+        buf = (C.c_uint8 * PEER_HANDLE_BYTES)()
+        self._ck(self.lib.bm_gather_open(self.h, rank, nranks, root, max_reads, max_locs, buf), "bm_gather_open")
+        return bytes(buf)
+
+    def gather_connect(self, handles):
+        blob = b"".join(handles)
+        buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+        self._ck(self.lib.bm_gather_connect(self.h, buf), "bm_gather_connect")
+
+    def gather_results(self, out_off=None, out_locs=None):
+        """every rank after locate_device; root with arrays: blocks and returns (n_reads_total, n_locs_total)"""
+        nr, nl = C.c_uint64(), C.c_uint64()
+        want = out_off is not None
+        self._ck(self.lib.bm_gather_results(self.h, _ptr(out_off), _ptr(out_locs), len(out_locs) if out_locs is not None else 0,
+                                            C.byref(nr) if want else None, C.byref(nl) if want else None),
+                 "bm_gather_results")
+        return nr.value, nl.value
+
+    def gather_sync(self):
+        self._ck(self.lib.bm_gather_sync(self.h), "bm_gather_sync")
+
+    def gather_join(self):
+        self._ck(self.lib.bm_gather_join(self.h), "bm_gather_join")
+
+    def gather_download(self):
+        """root: (loc_off, locs) of the last gathered batch, copied from the root's device buffers"""
+        nr, nl = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.bm_gather_download(self.h, None, None, 0, C.byref(nr), C.byref(nl)), "bm_gather_download")
+        off = np.empty(nr.value + 1, np.uint32)
+        locs = np.empty(nl.value, LOC_DTYPE)
+        self._ck(self.lib.bm_gather_download(self.h, _ptr(off), _ptr(locs), len(locs), C.byref(nr), C.byref(nl)),
+                 "bm_gather_download")
+        return off, locs
+
+    def gather_close(self):
+        self._ck(self.lib.bm_gather_close(self.h), "bm_gather_close")
 
     # ---- alignment -----------------------------------------------------------------------------------------------
     def align_device(self, P):

@@ -36,6 +36,8 @@ void bm_ctx_destroy(bm_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    bm_gather_close(c);
+    bm_comm_destroy(c);
     DevBuf* bufs[] = {&c->d_packed, &c->d_bstart, &c->d_blen, &c->d_rows, &c->d_k2i, &c->d_zeros, &c->d_distok,
                       &c->d_stage, &c->d_seq, &c->d_qual, &c->d_read_off, &c->d_seg_read, &c->d_seg_start,
                       &c->d_seg_len, &c->d_rowidx, &c->d_segok, &c->d_cand_fixed, &c->d_cand_cnt, &c->d_cand_off,

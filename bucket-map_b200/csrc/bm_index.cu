@@ -158,7 +158,10 @@ __global__ void k_distok_planes(const uint32_t* __restrict__ distok, uint32_t q,
     atomicOr(out + (idx >> 5), 1u << (idx & 31));
 }
 
-int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t NB) {
+}  // namespace
+
+// sizes the resident matrix for a kmer_to_index table (used by build, load, alloc and the index broadcast)
+int bm_internal_index_set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t NB) {
     if (q == 0 || q > 14) BM_FAIL(c, BM_E_LIMIT, "index seed length q must be in [1,14]");
     if (NB == 0) BM_FAIL(c, BM_E_ARG, "NB must be > 0");
     uint64_t n_codes = 1ull << (2 * q);
@@ -179,14 +182,18 @@ int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32
     return BM_OK;
 }
 
+namespace {
+inline int set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t NB) {
+    return bm_internal_index_set_table(c, k2i, q, n_rows, NB);
+}
 }  // namespace
 
 int bm_internal_index_prepare(bm_ctx* c, float d) {
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "no index resident (bm_index_build / bm_index_load first)");
     if (c->zeros_for_d == d) return BM_OK;
     const uint32_t thr = (unsigned int)(d * c->NB);          // q_gram_mapper.h:163 (float * unsigned, truncated)
-    BM_CK(c, c->d_stats.ensure(136 * 8));
-    uint32_t* d_valid = c->d_stats.as<uint32_t>() + 260;     // scratch word past the mapper's stats and counter slots
+    BM_CK(c, c->d_stats.ensure(208 * 8));
+    uint32_t* d_valid = c->d_stats.as<uint32_t>() + 400;     // scratch word past the mapper's stats and counter slots
     BM_CK(c, cudaMemsetAsync(d_valid, 0, 4, c->stream));
     if (c->n_rows) {
         KScope ks(c, BM_K_ROWPOP);

@@ -58,6 +58,8 @@ struct HostBuf {
 struct KStat { double ms = 0; uint64_t launches = 0; };
 struct PendingEv { int kid; cudaEvent_t a, b; };
 
+struct bm_gather;
+
 struct bm_ctx {
     int device = 0;
     int sm_count = 148;
@@ -157,6 +159,12 @@ struct bm_ctx {
     uint32_t lane_min_reads = 0xFFFFFFFFu;   // batches from this size on run on two lanes (bm_pipeline_lanes; default: never)
     HostBuf h_lane_off;
 
+    // multi-GPU (bm_comm.cu): NCCL communicator for the index broadcast; peer-memory gather of the location records
+    void* comm = nullptr;
+    bool comm_owned = false;
+    int comm_rank = 0, comm_nranks = 0;
+    bm_gather* gather = nullptr;
+
     // measurement
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     bool ktiming = false;
@@ -194,6 +202,7 @@ struct KScope {
     }
 };
 
+int bm_internal_gather_fence(bm_ctx* c);                       // bm_comm.cu: a gather copy still reads the result buffers
 int bm_internal_index_prepare(bm_ctx* ctx, float d);          // K0: zeros + distok bitmap for threshold d
 int bm_internal_kmer_table_prepare(bm_ctx* ctx, uint32_t k);  // K0b: k-mer row table for query seed length k (if it fits)
 int bm_internal_gidx_prepare(bm_ctx* ctx, uint32_t k);        // genome k-mer position index for seed length k (if it fits)

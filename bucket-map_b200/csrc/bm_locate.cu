@@ -497,6 +497,7 @@ int bm_locate_device(bm_ctx* c, const bm_params* p, int filter_best) {
     cudaSetDevice(c->device);
     c->have_locs = false; c->have_aln = false;
     { int rp = bm_internal_pack_check(c, p); if (rp) return rp; }
+    { int rg = bm_internal_gather_fence(c); if (rg) return rg; }
     const uint32_t n_seg = c->n_seg, n_reads = c->n_reads;
     const uint64_t n_cand = c->n_cand;
 

@@ -294,6 +294,8 @@ int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* 
     }
     BM_CK(c, cudaGetLastError());
     BM_CK(c, cudaMemcpyAsync(n_over, d_n_over, 4, cudaMemcpyDeviceToHost, c->stream));
+    if (c->d_stats.p)   // stats[7]: candidates whose vote map outgrew K3i's arrays (finished by the bucket-scan kernel)
+        BM_CK(c, cudaMemcpyAsync(c->d_stats.as<unsigned long long>() + 7, d_n_over, 4, cudaMemcpyDeviceToDevice, c->stream));
     BM_CK(c, cudaStreamSynchronize(c->stream));
     return BM_OK;
 }

@@ -272,12 +272,19 @@ k_map_vote_lists(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, con
     }
 }
 
-// K2f spreads its two counters over 60 slots (stats[8 + 2s], stats[9 + 2s]); fold them into stats[3], stats[4]
-__global__ void k_stats_fold(unsigned long long* __restrict__ stats) {
-    unsigned long long a = 0, b = 0;
-    if (threadIdx.x < 60) { a = stats[8 + 2 * threadIdx.x]; b = stats[9 + 2 * threadIdx.x]; stats[8 + 2 * threadIdx.x] = 0; stats[9 + 2 * threadIdx.x] = 0; }
-    for (int o = 16; o; o >>= 1) { a += __shfl_xor_sync(0xFFFFFFFFu, a, o); b += __shfl_xor_sync(0xFFFFFFFFu, b, o); }
-    if ((threadIdx.x & 31) == 0) { if (a) atomicAdd(stats + 3, a); if (b) atomicAdd(stats + 4, b); }
+// K2f spreads its three counters over 60 slots (stats[8 + 3s ..]); fold them into stats[3], stats[4], stats[6];
+// stats[5] = lists K2f handed to the full-width gather
+__global__ void k_stats_fold(unsigned long long* __restrict__ stats, const uint32_t* __restrict__ n_over) {
+    unsigned long long a = 0, b = 0, c = 0;
+    if (threadIdx.x < 60) {
+        a = stats[8 + 3 * threadIdx.x]; b = stats[9 + 3 * threadIdx.x]; c = stats[10 + 3 * threadIdx.x];
+        stats[8 + 3 * threadIdx.x] = 0; stats[9 + 3 * threadIdx.x] = 0; stats[10 + 3 * threadIdx.x] = 0;
+    }
+    for (int o = 16; o; o >>= 1) {
+        a += __shfl_xor_sync(0xFFFFFFFFu, a, o); b += __shfl_xor_sync(0xFFFFFFFFu, b, o); c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+    }
+    if ((threadIdx.x & 31) == 0) { if (a) atomicAdd(stats + 3, a); if (b) atomicAdd(stats + 4, b); if (c) atomicAdd(stats + 6, c); }
+    if (threadIdx.x == 0) stats[5] = *n_over;
 }
 
 // ---- compaction of the fixed-slot lists into cand_off / cand ---------------------------------------------------------------
@@ -408,8 +415,8 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
     BM_CK(c, c->d_cand_fixed.ensure(n_lists * p->max_candidates * 4 + 16));
     BM_CK(c, c->d_cand_cnt.ensure((n_lists + 1) * 4));
     BM_CK(c, c->d_cand_off.ensure((n_lists + 1) * 4));
-    BM_CK(c, c->d_stats.ensure(136 * 8));
-    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 128 * 8, c->stream));   // [0..7] the counters, [8..127] K2f's slots
+    BM_CK(c, c->d_stats.ensure(208 * 8));
+    BM_CK(c, cudaMemsetAsync(c->d_stats.p, 0, 192 * 8, c->stream));   // [0..7] the counters, [8..187] K2f's slots
     c->map_max_cand = p->max_candidates;
     c->n_cand = 0;
     if (c->use_ktable) {                                  // lists K2f hands over to K2 (+ their count)
@@ -499,7 +506,7 @@ int bm_internal_map_finish(bm_ctx* c, const bm_params* p) {
             }
         }
         BM_CK(c, e);
-        k_stats_fold<<<1, 64, 0, c->stream>>>(c->d_stats.as<unsigned long long>());
+        k_stats_fold<<<1, 64, 0, c->stream>>>(c->d_stats.as<unsigned long long>(), n_ids);
     }
     if (n_seg) {
         int r = bm_internal_exclusive_scan(c, c->d_cand_cnt.as<uint32_t>(), c->d_cand_off.as<uint32_t>(), n_lists + 1);

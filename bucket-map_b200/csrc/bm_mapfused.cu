@@ -34,7 +34,7 @@ struct FusedArgs {
     const uint32_t* rows32; const uint32_t* frows32; uint32_t Wp32, NB, F, max_cand;   // frows32: fine k-mer table or nullptr
     uint32_t* cand_fixed; uint32_t* cand_cnt; uint8_t* segok; unsigned long long* stats;
     uint32_t P; uint16_t* sidx; uint32_t* shash;
-    uint32_t ldmode;
+    uint32_t ldmode, pf_lines, pf_inv;
     uint32_t fm[9];                           // bit planes of the hits a group needs: S - F + 1
     uint32_t all_indexed;                     // every q-gram has a row (-f 1): no kmer_to_index look-ups needed for the counter
     uint32_t max_pass; int32_t* rowidx; uint32_t* over_list; uint32_t* n_over;   // hand-over to K2 (repeats)
@@ -295,15 +295,14 @@ k_map_fused(const FusedArgs a) {
     // The reverse strand's coarse rows are requested into L2 now, one (sample, 128-B line) per lane, so that they arrive
     // while the forward strand is voted on and recounted: one DRAM round trip less on the warp's critical path.
     {
-        const uint32_t lines = (a.Wc * 4u + 127u) / 128u;
-        const uint32_t inv = 65535u / lines + 1u;      // t / lines == (t * inv) >> 16 for the small t of this loop
+        const uint32_t lines = a.pf_lines;             // 128-B lines per coarse row; t / lines == (t * pf_inv) >> 16
         for (uint32_t t = lane; t < S * lines; t += 32) {
-            const uint32_t si = (lines * S < 4096u) ? ((t * inv) >> 16) : t / lines, ln = t - si * lines;
+            const uint32_t si = (t * a.pf_inv) >> 16, ln = t - si * lines;
             const uint2* pp = a.crows + (size_t)hsh[a.S4 + si] * a.Wcs2 + ln * 16u;
             asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
         }
     }
-    uint32_t nfine = 0;
+    uint32_t nfine = 0, npass_all = 0;
     for (uint32_t strand = 0; strand < 2; strand++) {
         const uint32_t* hs = hsh + strand * a.S4;
         const int32_t* rs = rid + (size_t)strand * S * NQ;
@@ -401,6 +400,7 @@ k_map_fused(const FusedArgs a) {
                 }
             }
         }
+        npass_all += npass;
         if (handover) {
             for (uint32_t t = lane; t < S * NQ; t += 32) {
                 int32_t r = 0;
@@ -418,9 +418,10 @@ k_map_fused(const FusedArgs a) {
     nfine = __reduce_add_sync(0xFFFFFFFFu, nfine);
     if (lane == 0) {
         // 60 counter slots picked by CTA (a million adds on one address would queue up in one L2 slice); folded into
-        // stats[3], stats[4] by bm_internal_map_finish
-        unsigned long long* slot = a.stats + 8 + 2 * (blockIdx.x % 60u);
+        // stats[3], stats[4], stats[6] by bm_internal_map_finish
+        unsigned long long* slot = a.stats + 8 + 3 * (blockIdx.x % 60u);
         if (gathered) atomicAdd(slot, (unsigned long long)gathered);
+        if (npass_all) atomicAdd(slot + 2, (unsigned long long)npass_all);      // coarse groups that needed an exact recount
         atomicAdd(slot + 1, 2ull * S * a.Wc * 4ull + (unsigned long long)nfine * 4ull + (a.rp.qk ? 12ull : 8ull) * nbch);   // bytes loaded
     }
 }
@@ -475,6 +476,9 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
         for (int i = 0; i < 9; i++) a.fm[i] = ((need >> i) & 1u) ? 0xFFFFFFFFu : 0u;
     }
     a.all_indexed = (c->n_rows == (1u << (2 * c->q))) ? 1u : 0u;
+    a.pf_lines = (a.Wc * 4u + 127u) / 128u;
+    a.pf_inv = 65535u / a.pf_lines + 1u;              // exact for t < 65536 / lines; S * lines <= 256 * 64 stays far below
+    if ((uint64_t)S * a.pf_lines * a.pf_lines >= 65536) { a.pf_lines = 0; a.pf_inv = 0; }   // (t * inv) >> 16 would be off: no prefetch
     const char* lde = getenv("BM_K2F_LD");
     a.ldmode = lde ? (uint32_t)atoi(lde) : 3u;
     const char* mbe = getenv("BM_K2F_MINB");

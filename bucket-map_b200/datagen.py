@@ -182,3 +182,17 @@ def write_fastq_fast(path, seq, qual, off):
                 f.write(names[i]); f.write(body[i].tobytes())
         return
     write_fastq(path, seq, qual, off)
+
+
+def add_repeats_packed(packed, n_bases, seg_len, n_copies, seed):
+    """add_repeats in the packed domain (4-base aligned source / destination / length), for Gbp genomes: copies
+    n_copies random segments of seg_len bases elsewhere (SURVEY 8d, C2': 5 % duplicated 10 kbp segments)"""
+    rng = np.random.default_rng(seed)
+    out = packed.copy()
+    nb = seg_len // 4
+    lim = (n_bases - seg_len) // 4
+    src = rng.integers(0, lim, n_copies)
+    dst = rng.integers(0, lim, n_copies)
+    for a, b in zip(src.tolist(), dst.tolist()):
+        out[b:b + nb] = out[a:a + nb]
+    return out

@@ -78,7 +78,7 @@ typedef struct bm_aln {
 
 /* kernel ids for bm_kernel_stats */
 enum { BM_K_ROWPOP = 0, BM_K_INDEX = 1, BM_K_SAMPLE = 2, BM_K_MAP = 3, BM_K_LOCSAMPLE = 4, BM_K_LOCATE = 5,
-       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_GIDX = 10, BM_K_LOCSCAN = 11, BM_K_MAPOVER = 12, BM_K_PACK = 13, BM_K_COUNT = 14 };
+       BM_K_MERGE = 6, BM_K_ALIGN = 7, BM_K_AUX = 8, BM_K_KTABLE = 9, BM_K_GIDX = 10, BM_K_LOCSCAN = 11, BM_K_MAPOVER = 12, BM_K_PACK = 13, BM_K_GATHER = 14, BM_K_COUNT = 15 };
 
 /* ---- context -------------------------------------------------------------------------------------------------- */
 int  bm_ctx_create(int device, bm_ctx** out);
@@ -171,7 +171,10 @@ int bm_map_device(bm_ctx* ctx, const bm_params* p);
 /* cand_off: 2*n_seg+1 entries; cand: capacity cand_cap entries (2*max_candidates*n_seg always suffices).
  * stats: 8 entries. [0]=segments with >=1 candidate, [1]=sum forward, [2]=sum reverse, [3]=rows the reference's
  * cascade ANDs for this batch (indexed q-grams of both strands: R of SURVEY 8d), [4]=bytes K2 actually gathered
- * (less than [3]*Wp: tiles whose buckets have all reached F misses are not gathered further), [5..7]=0. */
+ * (less than [3]*Wp: tiles whose buckets have all reached F misses are not gathered further; with the k-mer tables: the
+ * bytes the fused kernel's loads ask for), [5]=lists the fused kernel handed to the full-width gather (repeats),
+ * [6]=coarse groups that passed the coarse vote and were recounted exactly, [7]=candidates whose vote map outgrew the
+ * index locator's arrays and went to the bucket-scan kernel (valid after bm_locate_device). */
 int bm_map_download(bm_ctx* ctx, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats);
 /* host-buffer form: upload + device + download (what q_gram_mapper::map does per FASTQ batch) */
 int bm_map_reads(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off,
@@ -208,6 +211,42 @@ int bm_map_locate_packed(bm_ctx* ctx, const bm_params* p, const uint64_t* planes
  * other.  Same records in the same order; after such a call no batch is resident in ctx.  Not faster on a PCIe-bound
  * box (see bm_pipeline.cu), kept for hosts with a faster link. */
 int bm_pipeline_lanes(bm_ctx* ctx, uint32_t min_reads);
+
+/* ---- several GPUs (no reference counterpart: the reference is one single-threaded process; main.cpp:181-225 is the call
+ *      site a multi-GPU bucketmap shards).  Reads are sharded over the ranks, the index is replicated.  One
+ *      bm_ctx per GPU: one process per GPU (torchrun, MPI) or several contexts in one process (bucketmap --devices). -- */
+#define BM_COMM_ID_BYTES 128      /* ncclUniqueId */
+#define BM_PEER_HANDLE_BYTES 128
+/* NCCL (dlopen'ed libnccl.so.2): bm_comm_unique_id on one rank, its bytes to every rank by any means, bm_comm_init on all;
+ * or bm_comm_attach with a communicator (ncclComm_t) the caller already has. */
+int bm_comm_unique_id(uint8_t* id);
+int bm_comm_init(bm_ctx* ctx, const uint8_t* id, int nranks, int rank);
+int bm_comm_attach(bm_ctx* ctx, void* nccl_comm, int nranks, int rank);
+int bm_comm_destroy(bm_ctx* ctx);
+/* ncclBroadcast of the resident index (geometry, kmer_to_index, bit matrix) / of the reference (2-bit text + bucket table)
+ * from `root` into every rank's context; derived tables are rebuilt locally (cheaper than moving them).  Collective. */
+int bm_bcast_index(bm_ctx* ctx, int root);
+int bm_bcast_ref(bm_ctx* ctx, int root);
+/* Gather of the location records to `root`, in rank order = read order (contiguous shards).  Not an NCCL call: each rank's
+ * records are written into the root's memory over NVLink (peer mapping) behind its locator pass, flagged, and packed by
+ * the root -- no host synchronisation on any rank, two batches in flight.
+ *   bm_gather_open      on every rank: max_reads / max_locs = largest batch / record count of any rank; writes this rank's
+ *                       handle (BM_PEER_HANDLE_BYTES).  The caller passes the handles of all ranks, in rank order, to
+ *   bm_gather_connect   on every rank.
+ *   bm_gather_results   on every rank after bm_locate_device, the same number of times.  Root with host pointers: blocks
+ *                       until the packed records (loc_off: sum of n_reads + 1 entries) are in host memory; with NULLs (and
+ *                       on the other ranks) nothing waits.
+ *   bm_gather_sync      host waits for this rank's gather stream;  bm_gather_join: the library stream waits for it (so
+ *                       bm_timer_stop covers it);  bm_gather_device_buffers: the root's packed result on the device. */
+int bm_gather_open(bm_ctx* ctx, int rank, int nranks, int root, uint32_t max_reads, uint64_t max_locs, uint8_t* handle);
+int bm_gather_connect(bm_ctx* ctx, const uint8_t* handles);
+int bm_gather_results(bm_ctx* ctx, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* n_reads_total,
+                      uint64_t* n_locs_total);
+int bm_gather_sync(bm_ctx* ctx);
+int bm_gather_join(bm_ctx* ctx);
+int bm_gather_device_buffers(bm_ctx* ctx, void** loc_off, void** locs, uint64_t* n_reads, uint64_t* n_locs);
+int bm_gather_download(bm_ctx* ctx, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* n_reads, uint64_t* n_locs);
+int bm_gather_close(bm_ctx* ctx);
 
 /* ---- bucketmap_align verification (replaces seqan3::align_pairwise + cigar_from_alignment at
  *      bucket_locator.h:520-528,560-589) -------------------------------------------------------------------------- */
