@@ -60,6 +60,9 @@ SIGNATURES = {
     "bm_pack_layout": (C.c_int, [_vp, C.c_uint32, _vp]),
     "bm_pack_reads": (C.c_int, [_vp, _vp, _vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _vp, _vp,
                                 C.POINTER(C.c_uint32)]),
+    "bm_pack_reads_v": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _vp, _vp,
+                                  C.POINTER(C.c_uint32)]),
+    "bm_prepare": (C.c_int, [_vp, C.POINTER(Params)]),
     "bm_reads_upload_packed": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, _vp, C.c_uint32]),
     "bm_map_locate_packed": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, _vp, C.c_uint32, C.c_int, _vp, _vp,
                                        C.c_uint64, _vp]),
@@ -250,6 +253,10 @@ class Context:
     def locator_index(self, mode):
         """0: the locator scans each candidate bucket's text; 1 (default): genome k-mer position index when it fits."""
         self._ck(self.lib.bm_locator_index(self.h, mode), "bm_locator_index")
+
+    def prepare(self, P):
+        """build the derived tables now instead of at the first batch"""
+        self._ck(self.lib.bm_prepare(self.h, C.byref(P)), "bm_prepare")
 
     def index_free(self):
         self._ck(self.lib.bm_index_free(self.h), "bm_index_free")

@@ -1,7 +1,10 @@
 // bm_api.cu -- context, parameters, reference/read upload and measurement entry points of libbucketmap_b200.so.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
+#include <set>
 
 #include <cub/device/device_scan.cuh>
 
@@ -351,12 +354,29 @@ int bm_sync(bm_ctx* c) {
     BM_CK(c, cudaStreamSynchronize(c->stream));
     return BM_OK;
 }
+// Pinned memory for the caller's batches.  On a machine without a usable CUDA device (the host-side unit tests) plain
+// page-aligned memory is handed out instead; bm_host_free tells the two apart.
+static std::mutex g_plain_m;
+static std::set<void*> g_plain;
+
 void* bm_host_alloc(uint64_t bytes) {
     void* p = nullptr;
-    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) == cudaSuccess) return p;
+    cudaGetLastError();
+    if (posix_memalign(&p, 4096, bytes ? bytes : 1) != 0) return nullptr;
+    std::lock_guard<std::mutex> g(g_plain_m);
+    g_plain.insert(p);
     return p;
 }
-void bm_host_free(void* p) { if (p) cudaFreeHost(p); }
+void bm_host_free(void* p) {
+    if (!p) return;
+    {
+        std::lock_guard<std::mutex> g(g_plain_m);
+        auto it = g_plain.find(p);
+        if (it != g_plain.end()) { g_plain.erase(it); free(p); return; }
+    }
+    cudaFreeHost(p);
+}
 
 }  // extern "C"
 

@@ -366,6 +366,19 @@ int bm_map_device(bm_ctx* c, const bm_params* p) {
     return bm_internal_map_finish(c, p);
 }
 
+int bm_prepare(bm_ctx* c, const bm_params* p) {
+    if (!c) return BM_E_ARG;
+    if (!p) BM_FAIL(c, BM_E_ARG, "bm_prepare: null parameters");
+    if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_prepare: no index resident");
+    cudaSetDevice(c->device);
+    int r = bm_internal_index_prepare(c, p->distinguishability);
+    if (r) return r;
+    if (p->k >= p->q && p->k <= 16) { r = bm_internal_kmer_table_prepare(c, p->k); if (r) return r; }   // builds the locator index first
+    if (c->d_packed.p) { r = bm_internal_gidx_prepare(c, p->k); if (r) return r; }
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    return BM_OK;
+}
+
 int bm_map_download(bm_ctx* c, uint32_t* cand_off, uint32_t* cand, uint64_t cand_cap, uint64_t* stats) {
     if (!c) return BM_E_ARG;
     if (!c->have_map) BM_FAIL(c, BM_E_ARG, "bm_map_download: bm_map_device first");

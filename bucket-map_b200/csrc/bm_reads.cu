@@ -130,49 +130,76 @@ int bm_pack_layout(const uint64_t* read_off, uint32_t n_reads, uint32_t* pl_off)
     return BM_OK;
 }
 
-int bm_pack_reads(const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off, const uint32_t* pl_off, uint32_t r0,
-                  uint32_t r1, uint32_t k, uint32_t b, uint64_t* planes, uint32_t* qk, uint32_t* n_low) {
-    if (!seq || !read_off || !pl_off || !planes || k == 0 || k > 32) return BM_E_ARG;
+// one read: n bases at s, nq <= n quality characters at q (the rest count as '!', phred 0); returns 1 if a window fails
+static inline uint32_t pack_one(const uint8_t* lut, const uint8_t* s, const uint8_t* q, uint32_t n, uint32_t nq, uint32_t k,
+                                uint32_t b, uint64_t* out, uint32_t* qo) {
+    const uint32_t nch = (n + 31) / 32;
+    for (uint32_t c = 0; c < nch; c++) {
+        const uint32_t lim = n - 32 * c < 32 ? n - 32 * c : 32;
+        uint32_t lo = 0, hi = 0;
+        const uint8_t* t = s + 32 * c;
+        for (uint32_t i = 0; i < lim; i++) { const uint32_t v = lut[t[i]]; lo |= (v & 1u) << i; hi |= (v >> 1) << i; }
+        out[c] = (uint64_t)lo | ((uint64_t)hi << 32);
+    }
+    if (!q) return 0;
+    uint32_t mn = nq < n ? 0u : 0xFFFFFFFFu;
+    for (uint32_t i = 0; i < nq; i++) { const uint32_t v = (uint32_t)q[i] - 33u; mn = v < mn ? v : mn; }
+    const uint32_t nk = (n >= k) ? n - k + 1 : 0;
+    if (mn >= b || nk == 0) {                                     // every window passes
+        if (qo) for (uint32_t c = 0; c < nch; c++) {
+            const uint32_t first = 32 * c;
+            qo[c] = nk <= first ? 0u : (nk - first >= 32u ? 0xFFFFFFFFu : ((1u << (nk - first)) - 1u));
+        }
+        return 0;
+    }
+    const uint32_t minq = b * k;
+    bool any_fail = false;
+    if (qo) memset(qo, 0, (size_t)nch * 4);
+    auto ph = [&](uint32_t i) -> uint32_t { return i < nq ? (uint32_t)q[i] - 33u : 0u; };
+    uint32_t sum = 0;
+    for (uint32_t i = 0; i + 1 < k; i++) sum += ph(i);
+    for (uint32_t j = 0; j < nk; j++) {                           // quality_filter.h:531-534: window sum of phred ranks
+        sum += ph(j + k - 1);
+        if (sum >= minq) { if (qo) qo[j >> 5] |= 1u << (j & 31); } else any_fail = true;
+        sum -= ph(j);
+    }
+    return any_fail ? 1u : 0u;
+}
+
+static const uint8_t* pack_lut() {
     static uint8_t lut[256];
     static bool ready = false;
     if (!ready) { for (int c = 0; c < 256; c++) lut[c] = (uint8_t)rank_dna4_lut((uint32_t)c); ready = true; }
+    return lut;
+}
+
+int bm_pack_reads(const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off, const uint32_t* pl_off, uint32_t r0,
+                  uint32_t r1, uint32_t k, uint32_t b, uint64_t* planes, uint32_t* qk, uint32_t* n_low) {
+    if (!seq || !read_off || !pl_off || !planes || k == 0 || k > 32) return BM_E_ARG;
+    const uint8_t* lut = pack_lut();
     uint32_t low = 0;
-    const uint32_t minq = b * k;
     for (uint32_t r = r0; r < r1; r++) {
-        const uint8_t* s = seq + read_off[r];
         const uint32_t n = (uint32_t)(read_off[r + 1] - read_off[r]);
-        const uint32_t nch = (n + 31) / 32;
-        uint64_t* out = planes + pl_off[r];
-        for (uint32_t c = 0; c < nch; c++) {
-            const uint32_t lim = n - 32 * c < 32 ? n - 32 * c : 32;
-            uint32_t lo = 0, hi = 0;
-            const uint8_t* t = s + 32 * c;
-            for (uint32_t i = 0; i < lim; i++) { const uint32_t v = lut[t[i]]; lo |= (v & 1u) << i; hi |= (v >> 1) << i; }
-            out[c] = (uint64_t)lo | ((uint64_t)hi << 32);
-        }
-        if (!qual) continue;
-        const uint8_t* q = qual + read_off[r];
-        uint32_t mn = 0xFFFFFFFFu;
-        for (uint32_t i = 0; i < n; i++) { const uint32_t v = (uint32_t)q[i] - 33u; mn = v < mn ? v : mn; }
-        const uint32_t nk = (n >= k) ? n - k + 1 : 0;
-        uint32_t* qo = qk ? qk + pl_off[r] : nullptr;
-        if (mn >= b || nk == 0) {                                     // every window passes
-            if (qo) for (uint32_t c = 0; c < nch; c++) {
-                const uint32_t first = 32 * c;
-                qo[c] = nk <= first ? 0u : (nk - first >= 32u ? 0xFFFFFFFFu : ((1u << (nk - first)) - 1u));
-            }
-            continue;
-        }
-        bool any_fail = false;
-        if (qo) memset(qo, 0, (size_t)nch * 4);
-        uint32_t sum = 0;
-        for (uint32_t i = 0; i < k - 1; i++) sum += (uint32_t)q[i] - 33u;
-        for (uint32_t j = 0; j < nk; j++) {                           // quality_filter.h:531-534: window sum of phred ranks
-            sum += (uint32_t)q[j + k - 1] - 33u;
-            if (sum >= minq) { if (qo) qo[j >> 5] |= 1u << (j & 31); } else any_fail = true;
-            sum -= (uint32_t)q[j] - 33u;
-        }
-        low += any_fail ? 1u : 0u;
+        low += pack_one(lut, seq + read_off[r], qual ? qual + read_off[r] : nullptr, n, n, k, b, planes + pl_off[r],
+                        qk ? qk + pl_off[r] : nullptr);
+    }
+    if (n_low) *n_low = low;
+    return BM_OK;
+}
+
+// the same for reads that are not concatenated: read i has read_off[i+1] - read_off[i] bases at seq[i] and qual_len[i]
+// (NULL: as many as bases) quality characters at qual[i] -- views into a FASTQ buffer, nothing is copied first
+int bm_pack_reads_v(const uint8_t* const* seq, const uint8_t* const* qual, const uint32_t* qual_len, const uint64_t* read_off,
+                    const uint32_t* pl_off, uint32_t r0, uint32_t r1, uint32_t k, uint32_t b, uint64_t* planes, uint32_t* qk,
+                    uint32_t* n_low) {
+    if (!seq || !read_off || !pl_off || !planes || k == 0 || k > 32) return BM_E_ARG;
+    const uint8_t* lut = pack_lut();
+    uint32_t low = 0;
+    for (uint32_t r = r0; r < r1; r++) {
+        const uint32_t n = (uint32_t)(read_off[r + 1] - read_off[r]);
+        uint32_t nq = qual_len ? qual_len[r] : n;
+        if (nq > n) nq = n;
+        low += pack_one(lut, seq[r], qual ? qual[r] : nullptr, n, nq, k, b, planes + pl_off[r], qk ? qk + pl_off[r] : nullptr);
     }
     if (n_low) *n_low = low;
     return BM_OK;

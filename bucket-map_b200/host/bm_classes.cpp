@@ -185,18 +185,28 @@ void q_gram_mapper::load(fs::path const& index_directory, const std::string& ind
                 kmer_to_index.push_back((int)v);
             }
             std::cerr << "[INFO]\t\tSuccessfully loaded " << index_directory / (indicator + ".kmers_index") << ".\n";
+        } else {
+            // Legacy index without a .kmers_index file (written before FracMinHash existed): the reference reads no table,
+            // hence zero rows of the .qgram file (:331-357), and maps nothing -- a SAM with the header only.  Same here: no
+            // q-gram has a row.
+            kmer_to_index.assign(n_codes, -1);
         }
     }
-    // .qgram (:344-366)
+    // .qgram (:344-366): the file is memory-mapped and handed to the device as it is
     const uint32_t W = (NB_ + 7) >> 3;
-    FILE* f = fopen((index_directory / (indicator + ".qgram")).c_str(), "rb");
-    if (f && kmer_to_index.size() == n_codes) {
+    file_map fm;
+    if (fm.open(index_directory / (indicator + ".qgram")) && kmer_to_index.size() == n_codes) {
         const double t0 = now_s();
-        std::vector<uint8_t> rows((size_t)sampled_q_grams * W);
-        size_t got = fread(rows.data(), 1, rows.size(), f);
-        if (got < rows.size()) memset(rows.data() + got, 0, rows.size() - got);
+        const size_t need = (size_t)sampled_q_grams * W;
+        std::vector<uint8_t> padded;
+        const uint8_t* rows = (const uint8_t*)fm.data();
+        if (fm.size() < need) {                                   // short file: missing rows read as zero, like the stream would
+            padded.assign(need, 0);
+            if (fm.size()) memcpy(padded.data(), fm.data(), fm.size());
+            rows = padded.data();
+        }
         bm_ctx* c = ctx_->get();
-        int rc = bm_index_load(c, kmer_to_index.data(), q, rows.data(), sampled_q_grams, NB_);
+        int rc = bm_index_load(c, kmer_to_index.data(), q, rows, sampled_q_grams, NB_);
         uint32_t valid = 0;
         if (!rc) rc = bm_index_zeros(c, distinguishability_, nullptr, &valid);            // K0 (:171-187)
         if (rc) std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n";
@@ -209,7 +219,6 @@ void q_gram_mapper::load(fs::path const& index_directory, const std::string& ind
             std::cerr << "[INFO]\t\tSuccessfully loaded " << index_directory / (indicator + ".qgram") << ".\n";
         }
     }
-    if (f) fclose(f);
 }
 
 void q_gram_mapper::print_map_benchmark(float time) const {
@@ -238,14 +247,16 @@ std::pair<segments_t, segments_t> q_gram_mapper::map(fs::path const& sequence_fi
     read_batch b;
     std::vector<uint32_t> cand_off, cand, seg_read, seg_start, seg_len;
     const double t0 = now_s();
-    while (fin.next(b, 1u << 20, (uint64_t)1 << 30)) {
+    while (fin.next(b, 1u << 20, (uint64_t)1 << 30, p.k, p.avg_base_quality)) {
         const uint32_t n = b.size();
         const size_t nseg_max = (size_t)n * (num_segment_samples_ ? num_segment_samples_ : 1);
         cand_off.resize(2 * nseg_max + 1);
         cand.resize(2 * nseg_max * allowed_max_candidate_buckets + 1);
         uint64_t stats[8] = {0};
-        int rc = bm_map_reads(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n, cand_off.data(), cand.data(),
-                              cand.size(), stats);                                          // K2a + K2
+        int rc = bm_reads_upload_packed(c, &p, b.planes.as<uint64_t>(), b.all_pass ? nullptr : b.qk.as<uint32_t>(),
+                                        b.pl_off.as<uint32_t>(), b.read_off.as<uint64_t>(), n);
+        if (!rc) rc = bm_map_device(c, &p);                                                 // K2f (or K2a + K2)
+        if (!rc) rc = bm_map_download(c, cand_off.data(), cand.data(), cand.size(), stats);
         if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n"; break; }
         uint32_t n_seg = 0;
         bm_reads_segments(c, &n_seg, nullptr, nullptr, nullptr);

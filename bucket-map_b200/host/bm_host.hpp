@@ -16,7 +16,9 @@
 #include <cstring>
 #include <filesystem>
 #include <functional>
+#include <memory>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -37,7 +39,8 @@ public:
     context& operator=(context const&) = delete;
     bm_ctx* get() const { return c_; }
     int device() const { return device_; }
-    // process-wide default: device $BM_DEVICE (0 if unset); exits with an [ERROR] line if there is no CUDA device
+    // process-wide default: device $BM_DEVICE (0 if unset); exits with an [ERROR] line if there is no CUDA device.
+    // Thread-safe: main() brings it up on a side thread while the FASTA is parsed.
     static context& default_context();
 
 private:
@@ -46,10 +49,54 @@ private:
 };
 
 // ---- reference genome: FASTA -> 2-bit packed bases + bucket table (utils.h:60-102) -------------------------------------------
+// zero-initialised byte array from anonymous pages (first touched by whoever writes them: the FASTA packer's threads)
+class page_buffer {
+public:
+    page_buffer() = default;
+    page_buffer(page_buffer const&) = delete;
+    page_buffer& operator=(page_buffer const&) = delete;
+    ~page_buffer() { release(); }
+    bool allocate(size_t n);
+    void release();
+    uint8_t* data() { return p_; }
+    const uint8_t* data() const { return p_; }
+    size_t size() const { return n_; }
+
+private:
+    uint8_t* p_ = nullptr;
+    size_t n_ = 0;
+};
+
+// read-only memory map of a whole file
+class file_map {
+public:
+    file_map() = default;
+    file_map(file_map const&) = delete;
+    file_map& operator=(file_map const&) = delete;
+    ~file_map() { close(); }
+    bool open(std::filesystem::path const& p);
+    void close();
+    const char* data() const { return p_; }
+    size_t size() const { return n_; }
+    bool ok() const { return ok_; }
+
+private:
+    const char* p_ = nullptr;
+    size_t n_ = 0;
+    bool ok_ = false;
+};
+
+// worker threads of the host pipeline (FASTA packing, FASTQ packing, SAM rendering): --threads / $BM_THREADS, default
+// min(hardware threads, 16)
+unsigned host_threads();
+void set_host_threads(unsigned n);
+// fn(part, parts) on `parts` threads (the calling thread takes part 0)
+void parallel_parts(unsigned parts, std::function<void(unsigned, unsigned)> const& fn);
+
 struct genome {
     std::vector<std::string> ids;            // full FASTA header lines (after '>')
     std::vector<uint64_t> rec_len;
-    std::vector<uint8_t> packed;             // base i in byte i>>2 at bits 2*(i&3); A0 C1 G2 T3 (other letters as dna5->dna4)
+    page_buffer packed;                      // base i in byte i>>2 at bits 2*(i&3); A0 C1 G2 T3 (other letters as dna5->dna4)
     uint64_t n_bases = 0;
     // bucket table
     uint32_t NB = 0;                         // sum ceil(len/L): includes skipped ("phantom") buckets
@@ -60,9 +107,9 @@ struct genome {
     void bucketize(uint32_t bucket_len, uint32_t read_len);
 };
 
-// ---- reads: FASTQ -> batches of concatenated bases / qualities -------------------------------------------------------------------
-// growable byte array in pinned host memory (bm_host_alloc): the copy engine reads it directly, so the host->device copy
-// of a batch overlaps the mapper kernels inside bm_map_locate
+// ---- reads: FASTQ -> batches in the device's packed form -------------------------------------------------------------------------
+// growable array in pinned host memory (bm_host_alloc): the copy engine reads it directly, so the host->device copy
+// of a batch overlaps the mapper kernels inside bm_map_locate_packed
 class pinned_bytes {
 public:
     pinned_bytes() = default;
@@ -71,55 +118,48 @@ public:
     ~pinned_bytes() { if (p_) bm_host_free(p_); }
     uint8_t* data() { return p_; }
     const uint8_t* data() const { return p_; }
-    size_t size() const { return n_; }
-    void clear() { n_ = 0; }
-    void truncate(size_t n) { if (n < n_) n_ = n; }
-    uint8_t& operator[](size_t i) { return p_[i]; }
-    const uint8_t& operator[](size_t i) const { return p_[i]; }
-    void reserve(size_t cap) {
+    template <class T> T* as() { return reinterpret_cast<T*>(p_); }
+    size_t capacity() const { return cap_; }
+    void reserve(size_t cap) {                   // contents are NOT kept: every batch is written from scratch
         if (cap <= cap_) return;
         size_t want = cap_ ? cap_ : (size_t)1 << 20;
         while (want < cap) want *= 2;
         uint8_t* q = (uint8_t*)bm_host_alloc(want);
         if (!q) { fprintf(stderr, "[ERROR]\t\tOut of pinned host memory (%zu bytes).\n", want); std::exit(2); }
-        if (n_) memcpy(q, p_, n_);
         if (p_) bm_host_free(p_);
         p_ = q; cap_ = want;
     }
-    void append(const void* src, size_t len) { reserve(n_ + len); memcpy(p_ + n_, src, len); n_ += len; }
-    void append_fill(uint8_t v, size_t len) { reserve(n_ + len); memset(p_ + n_, v, len); n_ += len; }
 
 private:
     uint8_t* p_ = nullptr;
-    size_t n_ = 0, cap_ = 0;
+    size_t cap_ = 0;
 };
 
+// One batch of FASTQ records.  The text stays where it is (views into the memory-mapped file: SAM rendering copies
+// SEQ / QUAL from there); what travels to the device is written by the parser threads in the packed form of
+// include/bucketmap_b200.h (bm_pack_reads): 2-bit base planes + the k-mer quality plane when some window fails -b.
 struct read_batch {
-    pinned_bytes seq, qual;                  // ASCII, concatenated
-    std::vector<uint64_t> off{0};
-    std::vector<char> id_pool;               // id lines (after '@'), concatenated
-    std::vector<uint64_t> id_off{0};
+    std::vector<const char*> id, seq, qual;     // start of the id line (after '@'), of the bases, of the qualities
+    std::vector<uint32_t> id_len, qual_len;
+    std::vector<uint64_t> off{0};                // bases: read i = [off[i], off[i+1])
+    pinned_bytes planes, qk, pl_off, read_off;   // uint64 / uint32 / uint32 / uint64 arrays for bm_map_locate_packed
+    bool all_pass = true;                        // no k-mer window below -b: the quality plane need not travel
     uint32_t size() const { return (uint32_t)off.size() - 1; }
-    const char* id(uint32_t i) const { return id_pool.data() + id_off[i]; }
-    size_t id_len(uint32_t i) const { return (size_t)(id_off[i + 1] - id_off[i]); }
-    void clear() { seq.clear(); qual.clear(); off.assign(1, 0); id_pool.clear(); id_off.assign(1, 0); }
+    void clear() { id.clear(); seq.clear(); qual.clear(); id_len.clear(); qual_len.clear(); off.assign(1, 0); all_pass = true; }
 };
 
 class fastq_reader {
 public:
     explicit fastq_reader(std::filesystem::path const& p);
-    ~fastq_reader();
-    bool ok() const { return f_ != nullptr; }
-    // appends up to max_reads reads (or until max_bases bases) to `b` (cleared first); false when the file is exhausted
-    bool next(read_batch& b, uint32_t max_reads, uint64_t max_bases);
+    bool ok() const { return map_.ok(); }
+    // Next batch of up to max_reads reads (or max_bases bases): splits the records (one thread, memchr), then packs them
+    // for query seed length k and quality threshold b on the host threads.  false when the file is exhausted.
+    bool next(read_batch& b, uint32_t max_reads, uint64_t max_bases, uint32_t k, uint32_t bq);
 
 private:
-    // next line as a view into the file buffer (no copy); false at end of file
     bool line(const char*& s, size_t& len);
-    void* f_ = nullptr;
-    std::vector<char> buf_;
-    size_t pos_ = 0, end_ = 0;
-    bool eof_ = false;
+    file_map map_;
+    size_t pos_ = 0;
 };
 
 // FASTA parsed and bucketized once per (path, L, r); nullptr (after an [ERROR] line) if it cannot be read
@@ -226,6 +266,9 @@ public:
                 std::filesystem::path const& sam_file, unsigned int quality_threshold = 30) override;
     // reads per device batch (default 1 Mi) -- host memory / latency knob, no effect on results
     void set_batch_reads(uint32_t n) { batch_reads_ = n ? n : 1; }
+    // several GPUs (--devices): the batches of one FASTQ are spread over the devices, the index is replicated from the
+    // mapper's context by bm_bcast_ref / bm_bcast_index (NCCL), SAM records leave in read order
+    void set_devices(std::vector<int> const& devices) { devices_ = devices; }
 
 private:
     mapper* _m;
@@ -236,6 +279,7 @@ private:
     bool align_;
     std::filesystem::path genome_file_name;
     uint32_t batch_reads_ = 1u << 18;   // reads per device batch: small enough for the parse / device / SAM stages to overlap
+    std::vector<int> devices_;
 };
 
 }   // namespace bm

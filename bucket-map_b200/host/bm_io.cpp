@@ -5,6 +5,12 @@
 #include <cstdlib>
 #include <cstring>
 #include <ctime>
+#include <mutex>
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include "bm_host.hpp"
 
@@ -25,12 +31,63 @@ context::context(int device) : device_(device) {
 context::~context() { bm_ctx_destroy(c_); }
 
 context& context::default_context() {
+    static std::once_flag once;
     static context* c = nullptr;
-    if (!c) {
+    std::call_once(once, [] {
         const char* e = std::getenv("BM_DEVICE");
         c = new context(e ? std::atoi(e) : 0);
-    }
+    });
     return *c;
+}
+
+// ---- small utilities ------------------------------------------------------------------------------------------------------
+bool page_buffer::allocate(size_t n) {
+    release();
+    void* p = mmap(nullptr, n ? n : 1, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+    if (p == MAP_FAILED) return false;
+    p_ = (uint8_t*)p; n_ = n ? n : 1;
+    return true;
+}
+void page_buffer::release() { if (p_) munmap(p_, n_); p_ = nullptr; n_ = 0; }
+
+bool file_map::open(std::filesystem::path const& p) {
+    close();
+    int fd = ::open(p.c_str(), O_RDONLY);
+    if (fd < 0) return false;
+    struct stat st;
+    if (fstat(fd, &st) != 0) { ::close(fd); return false; }
+    n_ = (size_t)st.st_size;
+    ok_ = true;
+    if (n_) {
+        void* m = mmap(nullptr, n_, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (m == MAP_FAILED) { ::close(fd); n_ = 0; ok_ = false; return false; }
+        madvise(m, n_, MADV_SEQUENTIAL);
+        p_ = (const char*)m;
+    }
+    ::close(fd);
+    return true;
+}
+void file_map::close() { if (p_) munmap((void*)p_, n_); p_ = nullptr; n_ = 0; ok_ = false; }
+
+static unsigned g_host_threads = 0;
+unsigned host_threads() {
+    if (!g_host_threads) {
+        unsigned n = 0;
+        if (const char* e = std::getenv("BM_THREADS")) n = (unsigned)std::atoi(e);
+        if (!n) { n = std::thread::hardware_concurrency(); if (n > 16) n = 16; }
+        g_host_threads = n ? n : 1;
+    }
+    return g_host_threads;
+}
+void set_host_threads(unsigned n) { g_host_threads = n ? n : 1; }
+
+void parallel_parts(unsigned parts, std::function<void(unsigned, unsigned)> const& fn) {
+    if (parts <= 1) { fn(0, 1); return; }
+    std::vector<std::thread> ts;
+    ts.reserve(parts - 1);
+    for (unsigned i = 1; i < parts; i++) ts.emplace_back([&fn, i, parts] { fn(i, parts); });
+    fn(0, parts);
+    for (auto& t : ts) t.join();
 }
 
 // ---- FASTA ---------------------------------------------------------------------------------------------------------------
@@ -45,15 +102,14 @@ static inline uint8_t rank_fasta(unsigned char c) {
     }
 }
 
-// Line-oriented: memchr finds the end of the line, a sequence line is packed four bases per byte through a 256-entry
-// table (whitespace inside a line falls back to the per-character path).  ~1 GB/s instead of a per-byte state machine.
+// The file is memory-mapped and cut into one byte range per host thread (at line starts).  Pass 1 counts the bases of every
+// range and notes its header lines; a short serial step turns that into record lengths and the base offset of every
+// range; pass 2 packs each range, four bases per byte through a 256-entry table, straight into its place of the 2-bit
+// array (the two bytes a range shares with its neighbours are OR-ed in atomically).  Both passes are memory-bound.
 bool genome::read_fasta(std::filesystem::path const& p) {
-    FILE* f = fopen(p.c_str(), "rb");
-    if (!f) return false;
-    ids.clear(); rec_len.clear(); packed.clear(); n_bases = 0;
-    std::error_code ec;
-    auto fsz = std::filesystem::file_size(p, ec);
-    packed.assign((ec ? (size_t)1 << 20 : (size_t)fsz / 4) + 128, 0);
+    file_map fm;
+    if (!fm.open(p)) return false;
+    ids.clear(); rec_len.clear(); packed.release(); n_bases = 0;
     static uint8_t lut[256];
     static bool lut_ready = false;
     if (!lut_ready) {
@@ -61,56 +117,105 @@ bool genome::read_fasta(std::filesystem::path const& p) {
         lut[(unsigned char)'\r'] = lut[(unsigned char)' '] = lut[(unsigned char)'\t'] = 0xFF;   // skipped
         lut_ready = true;
     }
-    std::vector<char> buf(1 << 24);
-    bool in_header = false, line_start = true;
-    std::string header;
-    size_t n;
-    auto put = [&](uint8_t r) {
-        if ((n_bases >> 2) + 1 >= packed.size()) packed.resize(packed.size() * 2, 0);
-        packed[n_bases >> 2] |= (uint8_t)(r << ((n_bases & 3) << 1));
-        n_bases++;
+    const char* d = fm.data();
+    const size_t n = fm.size();
+    unsigned T = host_threads();
+    if (n < ((size_t)1 << 22)) T = 1;
+    std::vector<size_t> cut(T + 1, n);
+    cut[0] = 0;
+    for (unsigned t = 1; t < T; t++) {
+        size_t at = n / T * t;
+        const char* nl = at < n ? (const char*)memchr(d + at, '\n', n - at) : nullptr;
+        cut[t] = nl ? (size_t)(nl - d) + 1 : n;
+        if (cut[t] < cut[t - 1]) cut[t] = cut[t - 1];
+    }
+    struct header { size_t bases_before; std::string text; };          // bases of the range that precede the header
+    struct part { std::vector<header> hdr; uint64_t bases = 0; };
+    std::vector<part> parts(T);
+    auto count_line = [&](const char* s, size_t len) -> uint64_t {
+        if (len && s[len - 1] == '\r') len--;
+        if (!memchr(s, ' ', len) && !memchr(s, '\t', len) && !memchr(s, '\r', len)) return len;
+        uint64_t c = 0;
+        for (size_t i = 0; i < len; i++) c += lut[(unsigned char)s[i]] != 0xFF;
+        return c;
     };
-    while ((n = fread(buf.data(), 1, buf.size(), f)) > 0) {
-        size_t i = 0;
-        while (i < n) {
-            const char* nl = (const char*)memchr(buf.data() + i, '\n', n - i);
-            const size_t e = nl ? (size_t)(nl - buf.data()) : n;          // segment [i, e) lies inside one line
-            if (in_header) header.append(buf.data() + i, e - i);
-            else if (line_start && e > i && buf[i] == '>') { in_header = true; header.assign(buf.data() + i + 1, e - i - 1); }
-            else if (!ids.empty() && e > i) {
-                const unsigned char* s = (const unsigned char*)buf.data();
-                const uint64_t before = n_bases;
-                size_t t = i;
-                while (t < e) {
-                    if ((n_bases & 3) == 0 && t + 4 <= e) {
-                        if ((n_bases >> 2) + 2 >= packed.size()) packed.resize(packed.size() * 2, 0);
-                        const uint8_t v0 = lut[s[t]], v1 = lut[s[t + 1]], v2 = lut[s[t + 2]], v3 = lut[s[t + 3]];
+    parallel_parts(T, [&](unsigned t, unsigned) {
+        part& P = parts[t];
+        size_t i = cut[t];
+        const size_t e = cut[t + 1];
+        while (i < e) {
+            const char* nl = (const char*)memchr(d + i, '\n', e - i);
+            const size_t le = nl ? (size_t)(nl - d) : e;
+            if (le > i && d[i] == '>') {
+                size_t hl = le - i - 1;
+                if (hl && d[le - 1] == '\r') hl--;
+                P.hdr.push_back({(size_t)P.bases, std::string(d + i + 1, hl)});
+            } else if (le > i) {
+                P.bases += count_line(d + i, le - i);
+            }
+            i = le + 1;
+        }
+    });
+    // serial: record lengths, base offset of every range.  Bases before the first header of the file belong to no record.
+    std::vector<uint64_t> base0(T + 1, 0);
+    bool open_rec = false;
+    uint64_t total = 0;
+    std::vector<uint64_t> drop(T, 0);          // bases at the start of range t that precede the file's first header
+    for (unsigned t = 0; t < T; t++) {
+        base0[t] = total;
+        uint64_t prev = 0;
+        for (auto const& h : parts[t].hdr) {
+            const uint64_t seg = h.bases_before - prev;
+            if (open_rec) { rec_len.back() += seg; total += seg; } else drop[t] += seg;
+            prev = h.bases_before;
+            ids.push_back(h.text); rec_len.push_back(0); open_rec = true;
+        }
+        const uint64_t seg = parts[t].bases - prev;
+        if (open_rec) { rec_len.back() += seg; total += seg; } else drop[t] += seg;
+    }
+    base0[T] = total;
+    n_bases = total;
+    const size_t nbytes = ((size_t)n_bases + 3) / 4 + 64;
+    if (!packed.allocate(nbytes)) return false;
+    uint8_t* out = packed.data();
+    parallel_parts(T, [&](unsigned t, unsigned) {
+        uint64_t g = base0[t];
+        uint64_t skip = drop[t];
+        const uint64_t g_end = base0[t + 1];
+        auto put = [&](uint8_t r) {
+            if (skip) { skip--; return; }
+            const uint8_t v = (uint8_t)(r << ((g & 3) << 1));
+            const uint64_t byte = g >> 2;
+            // the first and last byte of a range may be shared with the neighbouring range
+            if (byte == (base0[t] >> 2) || byte == ((g_end - 1) >> 2)) __atomic_fetch_or(out + byte, v, __ATOMIC_RELAXED);
+            else out[byte] |= v;
+            g++;
+        };
+        size_t i = cut[t];
+        const size_t e = cut[t + 1];
+        const unsigned char* s = (const unsigned char*)d;
+        while (i < e) {
+            const char* nl = (const char*)memchr(d + i, '\n', e - i);
+            const size_t le = nl ? (size_t)(nl - d) : e;
+            if (le > i && d[i] != '>') {
+                size_t x = i;
+                while (x < le) {
+                    if (!skip && (g & 3) == 0 && x + 4 <= le && g + 4 <= g_end && (g >> 2) != ((g_end - 1) >> 2) &&
+                        (g >> 2) != (base0[t] >> 2)) {
+                        const uint8_t v0 = lut[s[x]], v1 = lut[s[x + 1]], v2 = lut[s[x + 2]], v3 = lut[s[x + 3]];
                         if (!((v0 | v1 | v2 | v3) & 0x80)) {
-                            packed[n_bases >> 2] = (uint8_t)(v0 | (v1 << 2) | (v2 << 4) | (v3 << 6));
-                            n_bases += 4; t += 4;
+                            out[g >> 2] = (uint8_t)(v0 | (v1 << 2) | (v2 << 4) | (v3 << 6));
+                            g += 4; x += 4;
                             continue;
                         }
                     }
-                    const uint8_t v = lut[s[t++]];
+                    const uint8_t v = lut[s[x++]];
                     if (v != 0xFF) put(v);
                 }
-                rec_len.back() += n_bases - before;
             }
-            if (e > i || nl) line_start = false;
-            if (nl) {
-                if (in_header) {
-                    if (!header.empty() && header.back() == '\r') header.pop_back();
-                    ids.push_back(header); rec_len.push_back(0); header.clear();
-                    in_header = false;
-                }
-                line_start = true;
-                i = e + 1;
-            } else i = e;
+            i = le + 1;
         }
-    }
-    if (in_header) { ids.push_back(header); rec_len.push_back(0); }
-    packed.resize(((size_t)n_bases + 3) / 4 + 64, 0);
-    fclose(f);
+    });
     return true;
 }
 
@@ -136,62 +241,63 @@ void genome::bucketize(uint32_t bucket_len, uint32_t read_len) {
 }
 
 // ---- FASTQ ---------------------------------------------------------------------------------------------------------------
-fastq_reader::fastq_reader(std::filesystem::path const& p) : buf_(1 << 24) { f_ = fopen(p.c_str(), "rb"); }
-fastq_reader::~fastq_reader() { if (f_) fclose((FILE*)f_); }
+fastq_reader::fastq_reader(std::filesystem::path const& p) { map_.open(p); }
 
-// Lines are handed out as views into the 16 MB file buffer; when a line is cut by the end of the buffer the unread tail
-// is moved to the front and the buffer refilled (grown if a single line is longer than the buffer).
+// next line as a view into the mapped file; false at end of file
 bool fastq_reader::line(const char*& s, size_t& len) {
-    while (true) {
-        const char* b = buf_.data() + pos_;
-        const char* nl = (end_ > pos_) ? (const char*)memchr(b, '\n', end_ - pos_) : nullptr;
-        if (nl) {
-            s = b; len = (size_t)(nl - b);
-            pos_ += len + 1;
-            if (len && s[len - 1] == '\r') len--;
-            return true;
-        }
-        if (eof_) {
-            if (end_ == pos_) return false;
-            s = b; len = end_ - pos_;                        // last line without a newline
-            pos_ = end_;
-            if (len && s[len - 1] == '\r') len--;
-            return true;
-        }
-        const size_t rest = end_ - pos_;
-        if (rest && pos_) memmove(buf_.data(), buf_.data() + pos_, rest);
-        pos_ = 0; end_ = rest;
-        if (end_ == buf_.size()) buf_.resize(buf_.size() * 2);
-        const size_t got = fread(buf_.data() + end_, 1, buf_.size() - end_, (FILE*)f_);
-        if (got == 0) eof_ = true;
-        end_ += got;
-    }
+    const size_t end = map_.size();
+    if (pos_ >= end) return false;
+    const char* b = map_.data() + pos_;
+    const char* nl = (const char*)memchr(b, '\n', end - pos_);
+    s = b;
+    len = nl ? (size_t)(nl - b) : end - pos_;
+    pos_ += len + (nl ? 1 : 0);
+    if (len && s[len - 1] == '\r') len--;
+    return true;
 }
 
-bool fastq_reader::next(read_batch& b, uint32_t max_reads, uint64_t max_bases) {
+bool fastq_reader::next(read_batch& b, uint32_t max_reads, uint64_t max_bases, uint32_t k, uint32_t bq) {
     b.clear();
-    if (!f_) return false;
+    if (!map_.ok()) return false;
+    // 1. split the records (one thread: four memchr per record); the text is not copied
     const char *id, *s, *plus, *q;
     size_t nid, ns, np, nq;
-    while (b.size() < max_reads && b.seq.size() < max_bases) {
-        do { if (!line(id, nid)) return b.size() > 0; } while (nid == 0);
-        // a view dies with the next refill: copy each line before asking for the next one
-        const size_t id_mark = b.id_pool.size(), seq_mark = b.seq.size();
-        b.id_pool.insert(b.id_pool.end(), id + 1, id + nid);     // full id line after '@' (seqan3 default)
-        bool ok = line(s, ns);
-        if (ok && b.size() == 0) {
-            // pinned allocations are slow (and growing means copying): size the batch from its first read
-            const uint64_t want = std::min<uint64_t>(max_bases + ns, (uint64_t)(ns + 8) * max_reads);
-            b.seq.reserve((size_t)want); b.qual.reserve((size_t)want);
-        }
-        if (ok) { b.seq.append(s, ns); ok = line(plus, np) && line(q, nq); }
-        if (!ok) { b.id_pool.resize(id_mark); b.seq.truncate(seq_mark); break; }   // truncated record: dropped
-        if (nq >= ns) b.qual.append(q, ns);
-        else { b.qual.append(q, nq); b.qual.append_fill('!', ns - nq); }
-        b.id_off.push_back(b.id_pool.size());
-        b.off.push_back(b.seq.size());
+    uint64_t bases = 0;
+    while (b.size() < max_reads && bases < max_bases) {
+        bool got = true;
+        do { if (!line(id, nid)) { got = false; break; } } while (nid == 0);
+        if (!got) break;
+        if (!line(s, ns) || !line(plus, np) || !line(q, nq)) break;     // truncated record: dropped
+        b.id.push_back(id + 1); b.id_len.push_back((uint32_t)(nid ? nid - 1 : 0));   // full id line after '@' (seqan3 default)
+        b.seq.push_back(s); b.qual.push_back(q); b.qual_len.push_back((uint32_t)(nq < ns ? nq : ns));
+        bases += ns;
+        b.off.push_back(bases);
     }
-    return b.size() > 0;
+    const uint32_t n = b.size();
+    if (!n) return false;
+    // 2. the device form, written by the host threads into pinned memory
+    b.read_off.reserve((size_t)(n + 1) * 8);
+    b.pl_off.reserve((size_t)(n + 1) * 4);
+    memcpy(b.read_off.data(), b.off.data(), (size_t)(n + 1) * 8);
+    uint32_t* plo = b.pl_off.as<uint32_t>();
+    if (bm_pack_layout(b.off.data(), n, plo) != BM_OK) {
+        fprintf(stderr, "[ERROR]\t\tA batch of %u reads is too large for the packed form; use a smaller --batch-reads.\n", n);
+        std::exit(2);
+    }
+    const size_t nch = plo[n];
+    b.planes.reserve((nch + 1) * 8);
+    b.qk.reserve((nch + 1) * 4);
+    unsigned T = host_threads();
+    if (n < 4096) T = 1;
+    std::vector<uint32_t> low(T, 0);
+    parallel_parts(T, [&](unsigned t, unsigned parts) {
+        const uint32_t r0 = (uint32_t)((uint64_t)n * t / parts), r1 = (uint32_t)((uint64_t)n * (t + 1) / parts);
+        bm_pack_reads_v((const uint8_t* const*)b.seq.data(), (const uint8_t* const*)b.qual.data(), b.qual_len.data(),
+                        b.off.data(), plo, r0, r1, k, bq, b.planes.as<uint64_t>(), b.qk.as<uint32_t>(), &low[t]);
+    });
+    b.all_pass = true;
+    for (uint32_t v : low) if (v) b.all_pass = false;
+    return true;
 }
 
 // ---- FracMinHash hash function (tools/hash_function_generator.h:25-117) ---------------------------------------------------------

@@ -9,11 +9,17 @@
 #include <cstdio>
 #include <cstring>
 #include <condition_variable>
+#include <atomic>
 #include <deque>
 #include <fstream>
 #include <iostream>
+#include <map>
+#include <memory>
 #include <mutex>
 #include <thread>
+
+#include <fcntl.h>
+#include <unistd.h>
 
 #include "bm_host.hpp"
 
@@ -61,18 +67,8 @@ namespace {
 template <class T>
 struct batch_queue {
     std::mutex m; std::condition_variable cv; std::deque<T> q;
-    void push(T v) { { std::lock_guard<std::mutex> g(m); q.push_back(v); } cv.notify_one(); }
+    void push(T v) { { std::lock_guard<std::mutex> g(m); q.push_back(v); } cv.notify_all(); }
     bool pop(T& v) { std::unique_lock<std::mutex> g(m); cv.wait(g, [&] { return !q.empty(); }); v = q.front(); q.pop_front(); return true; }
-};
-
-struct sam_writer {
-    FILE* f = nullptr;
-    std::string buf;
-    explicit sam_writer(fs::path const& p) { f = fopen(p.c_str(), "wb"); buf.reserve(1 << 24); }
-    ~sam_writer() { flush(); if (f) fclose(f); }
-    void flush() { if (f && !buf.empty()) fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
-    void maybe_flush() { if (buf.size() > (1 << 24) - (1 << 16)) flush(); }
-    void num(uint64_t v) { char t[24]; int n = snprintf(t, sizeof t, "%llu", (unsigned long long)v); buf.append(t, (size_t)n); }
 };
 
 inline char dna4_char(uint8_t c) {         // FASTQ read as dna4 and printed back (seqan3 dna4 conversion)
@@ -83,6 +79,25 @@ inline char dna4_char(uint8_t c) {         // FASTQ read as dna4 and printed bac
         default: return 'A';
     }
 }
+
+inline void put_num(std::string& out, uint64_t v) {
+    char t[24];
+    int n = 0;
+    do { t[n++] = (char)('0' + v % 10); v /= 10; } while (v);
+    while (n) out += t[--n];
+}
+
+// one batch on its way through the pipeline
+struct work {
+    read_batch b;
+    uint64_t seq_no = 0;
+    pinned_bytes loc_off, locs;            // uint32[n+1], bm_loc[cap]: the device writes them directly
+    size_t loc_cap = 0;
+    std::vector<bm_aln> aln;
+    std::vector<uint32_t> cigar;
+    std::vector<std::string> text;         // SAM text of the batch, one piece per render thread
+    bool failed = false;
+};
 
 }   // namespace
 
@@ -95,12 +110,12 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
         return;
     }
     if (!qm->loaded()) { std::cerr << "[ERROR]\t\tThe q-gram index is empty. Cannot accept query.\n"; return; }
-    bm_ctx* c = qm->ctx()->get();
+    bm_ctx* c0 = qm->ctx()->get();
     genome const* g = load_genome_cached(genome_file_name, bucket_length, read_length);
     if (!g) return;
     const uint32_t n_emit = (uint32_t)g->b_start.size();
-    int rc = bm_ref_upload(c, g->packed.data(), g->n_bases, g->b_start.data(), g->b_len.data(), n_emit, g->NB);
-    if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n"; return; }
+    int rc = bm_ref_upload(c0, g->packed.data(), g->n_bases, g->b_start.data(), g->b_len.data(), n_emit, g->NB);
+    if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c0) << "\n"; return; }
 
     bm_params p;
     qm->fill_params(p);
@@ -112,6 +127,67 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
     p.avg_base_quality = avg_base_quality_;
     p.num_segment_samples = num_segment_samples_;
     p.quality_threshold = quality_threshold;
+
+    fastq_reader fin(sequence_file);
+    if (!fin.ok()) { std::cerr << "[ERROR]\t\tCannot read " << sequence_file << ".\n"; return; }
+    int out_fd = ::open(sam_file.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (out_fd < 0) { std::cerr << "[ERROR]\t\tCannot write " << sam_file << ".\n"; return; }
+
+    // ---- the parser starts on the first batch now; the device side gets ready meanwhile ----------------------------------
+    struct dev { bm_ctx* c; std::unique_ptr<context> own; };
+    std::vector<dev> devs;
+    devs.push_back({c0, nullptr});
+    const size_t n_dev = devices_.size() > 1 ? devices_.size() : 1;
+    const size_t depth = n_dev + 3;
+    std::vector<work> pool(depth);
+    batch_queue<work*> free_q, parsed_q, done_q;
+    for (auto& w : pool) free_q.push(&w);
+    const uint32_t batch_reads = batch_reads_;
+    double parse_s = 0;
+    const double t_pipe = now_s();
+    std::thread reader([&] {
+        work* w;
+        uint64_t seq_no = 0;
+        while (free_q.pop(w) && w) {
+            const double t = now_s();
+            const bool more = fin.next(w->b, batch_reads, (uint64_t)1 << 31, p.k, p.avg_base_quality);
+            parse_s += now_s() - t;
+            if (!more) break;
+            w->seq_no = seq_no++;
+            parsed_q.push(w);
+        }
+        for (size_t i = 0; i < n_dev; i++) parsed_q.push(nullptr);
+    });
+
+    // several GPUs: one context per device; reference and index travel from the mapper's context over NCCL
+    bool setup_failed = false;
+    const double t_setup = now_s();
+    if (n_dev > 1) {
+        for (size_t i = 1; i < n_dev; i++) {
+            std::unique_ptr<context> cx(new context(devices_[i]));
+            bm_ctx* c = cx->get();
+            devs.push_back({c, std::move(cx)});
+        }
+        uint8_t id[BM_COMM_ID_BYTES];
+        if (bm_comm_unique_id(id) != BM_OK) { std::cerr << "[ERROR]\t\tNCCL (libnccl.so.2) is needed for --devices and cannot be loaded.\n"; setup_failed = true; }
+        std::vector<int> rcs(n_dev, 0);
+        if (!setup_failed) {
+            parallel_parts((unsigned)n_dev, [&](unsigned i, unsigned) {
+                bm_ctx* c = devs[i].c;
+                int r = bm_comm_init(c, id, (int)n_dev, (int)i);
+                if (!r) r = bm_bcast_ref(c, 0);
+                if (!r) r = bm_bcast_index(c, 0);
+                if (!r) r = bm_prepare(c, &p);
+                rcs[i] = r;
+            });
+            for (size_t i = 0; i < n_dev; i++)
+                if (rcs[i]) { std::cerr << "[ERROR]\t\t" << bm_last_error(devs[i].c) << "\n"; setup_failed = true; }
+        }
+    } else {
+        rc = bm_prepare(c0, &p);               // row zeros, k-mer tables, locator index: before the first batch arrives
+        if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c0) << "\n"; setup_failed = true; }
+    }
+    const double setup_s = now_s() - t_setup;
 
     // bucket names / offsets / @SQ lines (:473-503)
     std::vector<std::string> bucket_name, ref_ids;
@@ -135,159 +211,190 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
         }
         if (bucket_index != 0) { ref_ids.push_back(last_bucket_name); ref_lengths.push_back((size_t)bucket_index * bucket_length); }
     }
-    fastq_reader fin(sequence_file);
-    if (!fin.ok()) { std::cerr << "[ERROR]\t\tCannot read " << sequence_file << ".\n"; return; }
-    sam_writer out(sam_file);
-    if (!out.f) { std::cerr << "[ERROR]\t\tCannot write " << sam_file << ".\n"; return; }
-    out.buf += "@HD\tVN:1.6\n";
-    for (size_t i = 0; i < ref_ids.size(); i++) { out.buf += "@SQ\tSN:" + ref_ids[i] + "\tLN:"; out.num(ref_lengths[i]); out.buf += '\n'; }
-
-    bm_kernel_timing(c, 1);
-    bm_kernel_stats_reset(c);
-
-    // Three stages on three threads, batches handed on through two queues: FASTQ parsing into pinned buffers, the device
-    // pass (this thread: one context, one host thread at a time), SAM rendering.  Records leave in read order because
-    // every stage is a single thread working through the batches in order.
-    struct work {
-        read_batch b;
-        std::vector<uint32_t> loc_off, cigar;
-        std::vector<bm_loc> locs;
-        std::vector<bm_aln> aln;
-    };
-    constexpr int kDepth = 3;
-    work pool[kDepth];
-    batch_queue<work*> free_q, parsed_q, done_q;
-    for (auto& w : pool) free_q.push(&w);
-    const uint32_t batch_reads = batch_reads_;
-    double parse_s = 0;
-    const double t_pipe = now_s();
-    std::thread reader([&] {
-        work* w;
-        while (free_q.pop(w) && w) {
-            const double t = now_s();
-            const bool more = fin.next(w->b, batch_reads, (uint64_t)1 << 31);
-            parse_s += now_s() - t;
-            if (!more) break;
-            parsed_q.push(w);
-        }
-        parsed_q.push(nullptr);
-    });
-
-    std::string seq_text;
-    unsigned int read_id = 0, mapped_locations = 0;
-    double device_s = 0, output_s = 0;
-    const bool align = align_;
-    std::thread writer([&] {
-        static const char* kDecode = nullptr;
-        static char decode[256];
-        if (!kDecode) { for (int v = 0; v < 256; v++) decode[v] = dna4_char((uint8_t)v); kDecode = decode; }
-        work* w;
-        while (done_q.pop(w) && w) {
-            const double t1 = now_s();
-            const read_batch& b = w->b;
-            const uint32_t n = b.size();
-            // SAM records in read order (:535-604)
-            for (uint32_t i = 0; i < n; i++) {
-                if (w->loc_off[i] == w->loc_off[i + 1]) continue;
-                const uint8_t* s = &b.seq[b.off[i]];
-                const size_t len = (size_t)(b.off[i + 1] - b.off[i]);
-                seq_text.resize(len);
-                for (size_t t = 0; t < len; t++) seq_text[t] = kDecode[s[t]];
-                for (uint32_t j = w->loc_off[i]; j < w->loc_off[i + 1]; j++) {
-                    const bm_loc& l = w->locs[j];
-                    size_t map_qual, ref_offset;
-                    if (!align) {
-                        map_qual = std::min((unsigned int)60, 6 * l.votes);                  // :591
-                        ref_offset = (unsigned int)(bucket_offsets[l.bucket] + l.offset);    // :592
-                    } else {
-                        if (!w->aln[j].kept) continue;                                       // :571-573
-                        map_qual = (uint8_t)w->aln[j].map_qual;                              // mapq is a uint8_t field in SAM
-                        ref_offset = (unsigned int)(w->aln[j].begin + bucket_offsets[l.bucket] + l.offset);   // :576
-                    }
-                    out.buf.append(b.id(i), b.id_len(i)); out.buf += '\t';
-                    out.num(l.is_original ? 0 : 16); out.buf += '\t';
-                    out.buf += bucket_name[l.bucket]; out.buf += '\t';
-                    out.num(ref_offset + 1); out.buf += '\t';
-                    out.num(map_qual); out.buf += '\t';
-                    if (align && w->aln[j].cigar_len) {
-                        for (uint32_t t = 0; t < w->aln[j].cigar_len; t++) {
-                            const uint32_t op = w->cigar[w->aln[j].cigar_off + t];
-                            out.num(op >> 4); out.buf += "MID"[op & 15u];
-                        }
-                    } else out.buf += '*';
-                    out.buf += "\t*\t0\t0\t";
-                    out.buf += seq_text; out.buf += '\t';
-                    out.buf.append((const char*)&b.qual[b.off[i]], len);
-                    out.buf += '\n';
-                    mapped_locations++;
-                }
-                out.maybe_flush();
-            }
-            read_id += n;
-            output_s += now_s() - t1;
-            free_q.push(w);
-        }
-    });
-
-    bool failed = false;
+    uint64_t file_pos = 0;
     {
+        std::string hdr = "@HD\tVN:1.6\n";
+        for (size_t i = 0; i < ref_ids.size(); i++) { hdr += "@SQ\tSN:" + ref_ids[i] + "\tLN:"; put_num(hdr, ref_lengths[i]); hdr += '\n'; }
+        if (::pwrite(out_fd, hdr.data(), hdr.size(), 0) != (ssize_t)hdr.size()) setup_failed = true;
+        file_pos = hdr.size();
+    }
+    for (auto& d : devs) { bm_kernel_timing(d.c, 1); bm_kernel_stats_reset(d.c); }
+
+    // ---- stage 2: one thread per device -----------------------------------------------------------------------------------
+    std::mutex stat_m;
+    double device_s = 0;
+    std::atomic<bool> failed{setup_failed};
+    const bool align = align_;
+    auto device_loop = [&](size_t di) {
+        bm_ctx* c = devs[di].c;
         work* w;
         while (parsed_q.pop(w) && w) {
+            if (failed.load()) { w->failed = true; done_q.push(w); continue; }
             read_batch& b = w->b;
             const uint32_t n = b.size();
             const double t0 = now_s();
             uint64_t stats[8] = {0};
             uint64_t n_locs = 0;
-            w->loc_off.resize((size_t)n + 1);
-            rc = BM_OK;
+            const uint64_t* planes = b.planes.as<uint64_t>();
+            const uint32_t* qkp = b.all_pass ? nullptr : b.qk.as<uint32_t>();
+            const uint32_t* plo = b.pl_off.as<uint32_t>();
+            const uint64_t* roff = b.read_off.as<uint64_t>();
+            w->loc_off.reserve((size_t)(n + 1) * 4);
+            int r = BM_OK;
             bool done = false;
-            if (!align_) {
+            if (!align) {
                 // one call: H2D chunks overlapped with the mapper.  The merged lists are almost always one record per
                 // read; if this batch needs more room than 4 per read the staged calls below size the buffer exactly.
-                const size_t cap = (size_t)4 * n + 1024;
-                w->locs.resize(cap);
-                int r1 = bm_map_locate(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n, 1, w->loc_off.data(), w->locs.data(),
-                                       cap, stats);
-                if (r1 == BM_OK) { n_locs = w->loc_off[n]; done = true; }
+                w->loc_cap = (size_t)4 * n + 1024;
+                w->locs.reserve(w->loc_cap * sizeof(bm_loc));
+                int r1 = bm_map_locate_packed(c, &p, planes, qkp, plo, roff, n, 1, w->loc_off.as<uint32_t>(), w->locs.as<bm_loc>(),
+                                              w->loc_cap, stats);
+                if (r1 == BM_OK) { n_locs = w->loc_off.as<uint32_t>()[n]; done = true; }
             }
             if (!done) {
-                rc = bm_reads_upload(c, &p, b.seq.data(), b.qual.data(), b.off.data(), n);
-                if (!rc) rc = bm_map_device(c, &p);
-                if (!rc) rc = bm_locate_device(c, &p, align_ ? 0 : 1);
-                if (!rc) rc = bm_locate_count(c, &n_locs);
-                if (!rc) { w->locs.resize(n_locs + 1); rc = bm_locate_download(c, w->loc_off.data(), w->locs.data(), n_locs + 1); }
-                if (align_) {
-                    if (!rc) rc = bm_align_device(c, &p);                                   // K4 (:560-589)
+                r = bm_reads_upload_packed(c, &p, planes, qkp, plo, roff, n);
+                if (!r) r = bm_map_device(c, &p);
+                if (!r) r = bm_locate_device(c, &p, align ? 0 : 1);
+                if (!r) r = bm_locate_count(c, &n_locs);
+                if (!r) {
+                    w->loc_cap = n_locs + 1;
+                    w->locs.reserve(w->loc_cap * sizeof(bm_loc));
+                    r = bm_locate_download(c, w->loc_off.as<uint32_t>(), w->locs.as<bm_loc>(), w->loc_cap);
+                }
+                if (align) {
+                    if (!r) r = bm_align_device(c, &p);                                   // K4 (:560-589)
                     uint64_t used = 0;
                     w->aln.resize(n_locs + 1);
-                    if (!rc) rc = bm_align_download(c, w->aln.data(), nullptr, 0, &used);
+                    if (!r) r = bm_align_download(c, w->aln.data(), nullptr, 0, &used);
                     w->cigar.resize(used + 1);
-                    if (!rc && used) rc = bm_align_download(c, w->aln.data(), w->cigar.data(), used, &used);
+                    if (!r && used) r = bm_align_download(c, w->aln.data(), w->cigar.data(), used, &used);
                 }
-                if (!rc) rc = bm_map_download(c, nullptr, nullptr, 0, stats);
+                if (!r) r = bm_map_download(c, nullptr, nullptr, 0, stats);
             }
-            if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n"; failed = true; break; }
-            qm->mapped_reads += (unsigned)stats[0]; qm->num_buckets_orig += (unsigned)stats[1]; qm->num_buckets_rev_comp += (unsigned)stats[2];
-            qm->num_records += n;
-            device_s += now_s() - t0;
+            if (r) {
+                std::lock_guard<std::mutex> lk(stat_m);
+                std::cerr << "[ERROR]\t\t" << bm_last_error(c) << "\n";
+                failed.store(true); w->failed = true;
+            } else {
+                std::lock_guard<std::mutex> lk(stat_m);
+                qm->mapped_reads += (unsigned)stats[0]; qm->num_buckets_orig += (unsigned)stats[1]; qm->num_buckets_rev_comp += (unsigned)stats[2];
+                qm->num_records += n;
+                device_s += now_s() - t0;
+            }
             done_q.push(w);
         }
+        done_q.push(nullptr);
+    };
+    std::vector<std::thread> dev_threads;
+    for (size_t di = 0; di < n_dev; di++) dev_threads.emplace_back(device_loop, di);
+
+    // ---- stage 3: SAM rendering on the host threads, records in read order (:535-604) ---------------------------------------
+    unsigned int read_id = 0, mapped_locations = 0;
+    double output_s = 0;
+    {
+        static char decode[256];
+        for (int v = 0; v < 256; v++) decode[v] = dna4_char((uint8_t)v);
+        std::map<uint64_t, work*> waiting;
+        uint64_t next_seq = 0;
+        size_t ended = 0;
+        auto render = [&](work* w) {
+            const double t1 = now_s();
+            const read_batch& b = w->b;
+            const uint32_t n = b.size();
+            const uint32_t* loc_off = w->loc_off.as<uint32_t>();
+            const bm_loc* locs = w->locs.as<bm_loc>();
+            unsigned T = host_threads();
+            if (n < 2048) T = 1;
+            if (w->text.size() < T) w->text.resize(T);
+            std::vector<unsigned> cnt(T, 0);
+            parallel_parts(T, [&](unsigned t, unsigned parts) {
+                std::string& out = w->text[t];
+                out.clear();
+                const uint32_t r0 = (uint32_t)((uint64_t)n * t / parts), r1 = (uint32_t)((uint64_t)n * (t + 1) / parts);
+                std::string seq_text;
+                for (uint32_t i = r0; i < r1; i++) {
+                    if (loc_off[i] == loc_off[i + 1]) continue;
+                    const size_t len = (size_t)(b.off[i + 1] - b.off[i]);
+                    seq_text.resize(len);
+                    const uint8_t* s = (const uint8_t*)b.seq[i];
+                    for (size_t x = 0; x < len; x++) seq_text[x] = decode[s[x]];
+                    for (uint32_t j = loc_off[i]; j < loc_off[i + 1]; j++) {
+                        const bm_loc& l = locs[j];
+                        size_t map_qual, ref_offset;
+                        if (!align) {
+                            map_qual = std::min((unsigned int)60, 6 * l.votes);                  // :591
+                            ref_offset = (unsigned int)(bucket_offsets[l.bucket] + l.offset);    // :592
+                        } else {
+                            if (!w->aln[j].kept) continue;                                       // :571-573
+                            map_qual = (uint8_t)w->aln[j].map_qual;                              // mapq is a uint8_t field in SAM
+                            ref_offset = (unsigned int)(w->aln[j].begin + bucket_offsets[l.bucket] + l.offset);   // :576
+                        }
+                        out.append(b.id[i], b.id_len[i]); out += '\t';
+                        put_num(out, l.is_original ? 0 : 16); out += '\t';
+                        out += bucket_name[l.bucket]; out += '\t';
+                        put_num(out, ref_offset + 1); out += '\t';
+                        put_num(out, map_qual); out += '\t';
+                        if (align && w->aln[j].cigar_len) {
+                            for (uint32_t x = 0; x < w->aln[j].cigar_len; x++) {
+                                const uint32_t op = w->cigar[w->aln[j].cigar_off + x];
+                                put_num(out, op >> 4); out += "MID"[op & 15u];
+                            }
+                        } else out += '*';
+                        out += "\t*\t0\t0\t";
+                        out += seq_text; out += '\t';
+                        out.append(b.qual[i], b.qual_len[i]);
+                        if (b.qual_len[i] < len) out.append(len - b.qual_len[i], '!');
+                        out += '\n';
+                        cnt[t]++;
+                    }
+                }
+            });
+            std::vector<uint64_t> at(T + 1, file_pos);
+            for (unsigned t = 0; t < T; t++) { at[t + 1] = at[t] + w->text[t].size(); mapped_locations += cnt[t]; }
+            bool ok = true;
+            parallel_parts(T, [&](unsigned t, unsigned) {
+                const std::string& out = w->text[t];
+                size_t done = 0;
+                while (done < out.size()) {
+                    ssize_t k = ::pwrite(out_fd, out.data() + done, out.size() - done, (off_t)(at[t] + done));
+                    if (k <= 0) { ok = false; break; }
+                    done += (size_t)k;
+                }
+            });
+            if (!ok) { std::cerr << "[ERROR]\t\tWriting " << sam_file << " failed.\n"; failed.store(true); }
+            file_pos = at[T];
+            read_id += n;
+            output_s += now_s() - t1;
+        };
+        work* w;
+        while (ended < n_dev && done_q.pop(w)) {
+            if (!w) { ended++; continue; }
+            waiting[w->seq_no] = w;
+            while (!waiting.empty() && waiting.begin()->first == next_seq) {
+                work* x = waiting.begin()->second;
+                waiting.erase(waiting.begin());
+                if (!x->failed && !failed.load()) render(x);
+                next_seq++;
+                free_q.push(x);
+            }
+        }
     }
-    done_q.push(nullptr);
-    writer.join();
-    if (failed) { free_q.push(nullptr); work* w; while (parsed_q.pop(w) && w) free_q.push(w); }
-    else free_q.push(nullptr);
+    for (auto& t : dev_threads) t.join();
+    free_q.push(nullptr);
     reader.join();
-    if (failed) return;
-    out.flush();
+    ::close(out_fd);
+    if (failed.load()) return;
 
     // the reference's phase log (q_gram_mapper.h:548-555, bucket_locator.h:698-702,606-610), filled with device times
     double ms[BM_K_COUNT]; uint64_t launches[BM_K_COUNT];
-    for (int i = 0; i < BM_K_COUNT; i++) { ms[i] = 0; launches[i] = 0; bm_kernel_stats(c, i, &ms[i], &launches[i]); }
-    bm_kernel_timing(c, 0);
-    if (qm->num_records) qm->print_map_benchmark((float)((ms[BM_K_SAMPLE] + ms[BM_K_MAP]) * 1e-3));
+    for (int i = 0; i < BM_K_COUNT; i++) {
+        ms[i] = 0; launches[i] = 0;
+        for (auto& d : devs) { double m1 = 0; uint64_t l1 = 0; bm_kernel_stats(d.c, i, &m1, &l1); ms[i] += m1; launches[i] += l1; }
+    }
+    for (auto& d : devs) bm_kernel_timing(d.c, 0);
+    if (qm->num_records) qm->print_map_benchmark((float)((ms[BM_K_SAMPLE] + ms[BM_K_MAP] + ms[BM_K_MAPOVER]) * 1e-3));
     std::cerr << "[BENCHMARK]\tTotal time used for building k-mer index for each bucket: 0 s.\n";
-    const float time = (float)((ms[BM_K_LOCSAMPLE] + ms[BM_K_LOCATE] + ms[BM_K_MERGE]) * 1e-3);
+    const float time = (float)((ms[BM_K_LOCSAMPLE] + ms[BM_K_LOCATE] + ms[BM_K_LOCSCAN] + ms[BM_K_MERGE]) * 1e-3);
     std::cerr << "[BENCHMARK]\tTotal time used for finding exact location of the sequences: " << time << " s ("
               << time * 1000 * 1000 / (read_id ? read_id : 1) << " μs/seq).\n";
     std::cerr << "[BENCHMARK]\tTotal mapped locations: " << mapped_locations << " (" << (float)mapped_locations / read_id
@@ -295,8 +402,10 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
     const float es = (float)(ms[BM_K_ALIGN] * 1e-3 + output_s);
     std::cerr << "[BENCHMARK]\tTotal time used for alignment verification and output: " << es << " s ("
               << es / mapped_locations * 1000 * 1000 << " μs per pairwise alignment).\n";
-    std::cerr << "[BENCHMARK]\tHost pipeline: FASTQ parsing " << (float)parse_s << " s, device passes " << (float)device_s
-              << " s, SAM rendering " << (float)output_s << " s on three threads; wall " << (float)(now_s() - t_pipe) << " s.\n";
+    std::cerr << "[BENCHMARK]\tHost pipeline: FASTQ splitting + packing " << (float)parse_s << " s, device passes " << (float)device_s
+              << " s on " << n_dev << " GPU(s), SAM rendering + writing " << (float)output_s << " s; " << host_threads()
+              << " host threads; derived tables" << (n_dev > 1 ? " + NCCL replication" : "") << " " << (float)setup_s
+              << " s (under the first batch's parse); wall " << (float)(now_s() - t_pipe) << " s.\n";
     std::cerr << "[BENCHMARK]\tDevice pipeline (H2D + kernels + D2H): " << (float)device_s << " s for " << read_id
               << " reads (" << (float)(read_id / (device_s > 0 ? device_s : 1)) << " reads/s).\n";
     _m->reset();                                                                       // :627

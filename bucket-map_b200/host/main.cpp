@@ -6,14 +6,18 @@
 //     -g/--genome <fasta>       (BM_GENOME_PATH)      -L/--bucket-len <n>   (BM_BUCKET_LEN, default 65536)
 //     the bucket count          (BM_BUCKET_NUM)       computed from the FASTA
 // and the FracMinHash hash parameters, which the reference draws from rand() seeded with time(), can be pinned with
-// --seed-x / --seed-y so that index builds are reproducible.  --device selects the GPU; --batch-reads the reads per
-// device batch; --align switches the bucketmap_align behaviour on in either binary.
+// --seed-x / --seed-y so that index builds are reproducible.  --device selects the GPU, --devices several (0-7 or 0,2,5: the
+// batches of one FASTQ are spread over them, the index is replicated over NCCL, SAM records leave in read order);
+// --batch-reads the reads per device batch; --threads the host threads of the FASTA / FASTQ / SAM stages; --align switches
+// the bucketmap_align behaviour on in either binary.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
 #include <string>
+#include <thread>
+#include <vector>
 
 #include "bm_host.hpp"
 
@@ -40,7 +44,9 @@ struct cmd_arguments {                     // main.cpp:12-39
     unsigned int bucket_len = 65536;
     long seed_x = -1, seed_y = -1;
     int device = -1;
-    unsigned int batch_reads = 1u << 18;
+    std::vector<int> devices;            // --devices 0-3 / 0,2,5: the batches of the FASTQ are spread over these GPUs
+    unsigned int threads = 0;            // host threads of the FASTA / FASTQ / SAM stages (0: min(cores, 16))
+    unsigned int batch_reads = 1u << 20;
 #ifdef BM_ALIGN
     bool align = true;
 #else
@@ -115,6 +121,25 @@ static void parse(int argc, char** argv, cmd_arguments& a) {
         else if (name == "seed-x") a.seed_x = (long)to_uint(need(i, arg, val, has_inline), arg);
         else if (name == "seed-y") a.seed_y = (long)to_uint(need(i, arg, val, has_inline), arg);
         else if (name == "device") a.device = (int)to_uint(need(i, arg, val, has_inline), arg);
+        else if (name == "devices") {
+            std::string v = need(i, arg, val, has_inline);
+            a.devices.clear();
+            size_t pos = 0;
+            while (pos <= v.size()) {
+                size_t e = v.find(',', pos);
+                if (e == std::string::npos) e = v.size();
+                std::string tok = v.substr(pos, e - pos);
+                size_t dash = tok.find('-');
+                if (dash != std::string::npos) {
+                    unsigned long lo = to_uint(tok.substr(0, dash), arg), hi = to_uint(tok.substr(dash + 1), arg);
+                    if (hi < lo || hi - lo > 63) throw parser_error{"Value parse failed for " + arg + ": '" + v + "'"};
+                    for (unsigned long d = lo; d <= hi; d++) a.devices.push_back((int)d);
+                } else a.devices.push_back((int)to_uint(tok, arg));
+                pos = e + 1;
+            }
+            if (a.devices.empty()) throw parser_error{"Value parse failed for " + arg + ": '" + v + "'"};
+        }
+        else if (name == "threads") a.threads = (unsigned)to_uint(need(i, arg, val, has_inline), arg);
         else if (name == "batch-reads") a.batch_reads = (unsigned)to_uint(need(i, arg, val, has_inline), arg);
         else if (name == "align") a.align = true;
         else if (name == "version-check") (void)need(i, arg, val, has_inline);     // accepted and ignored (benchmark_map.sh:31)
@@ -145,9 +170,14 @@ int main(int argc, char** argv) {
         std::cerr << "[ERROR]\t\tThe reference genome is not set. Use '-g <fasta>' (or the BM_GENOME environment variable).\n";
         return -1;
     }
+    if (!args.devices.empty()) args.device = args.devices[0];
     if (args.device >= 0) setenv("BM_DEVICE", std::to_string(args.device).c_str(), 1);
+    if (args.threads) bm::set_host_threads(args.threads);
 
+    // the CUDA context comes up on a side thread while the host threads parse the FASTA
+    std::thread ctx_up([] { bm::context::default_context(); });
     bm::genome const* g = bm::load_genome_cached(args.genome_path, args.bucket_len, args.max_read_length);
+    ctx_up.join();
     if (!g) return -1;
     std::cerr << "[INFO]\t\tInitializing indexer and mapper with bucket length: " << args.bucket_len
               << ", and number of buckets: " << g->NB << ".\n";
@@ -178,6 +208,7 @@ int main(int argc, char** argv) {
                            args.allowed_seed_miss_rate, args.locator_allowed_indel_rate,
                            (unsigned int)args.locator_sample_size, args.average_base_quality, 5, args.align);
     loc.set_batch_reads(args.batch_reads);
+    if (args.devices.size() > 1) loc.set_devices(args.devices);
     loc.initialize(args.genome_path, fs::current_path(), args.index_indicator);
     loc.locate(args.fastq_path, fs::current_path() / (args.index_indicator + ".bucket_id"), args.output_sam_path,
                args.locator_quality_threshold);

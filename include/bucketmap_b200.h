@@ -160,6 +160,14 @@ int bm_reads_upload(bm_ctx* ctx, const bm_params* p, const uint8_t* seq, const u
 int bm_pack_layout(const uint64_t* read_off, uint32_t n_reads, uint32_t* pl_off);
 int bm_pack_reads(const uint8_t* seq, const uint8_t* qual, const uint64_t* read_off, const uint32_t* pl_off,
                   uint32_t r0, uint32_t r1, uint32_t k, uint32_t b, uint64_t* planes, uint32_t* qk, uint32_t* n_low);
+/* the same for reads that are not concatenated (views into a FASTQ buffer): read i has read_off[i+1] - read_off[i] bases at
+ * seq[i] and qual_len[i] (NULL: as many as bases; missing ones count as '!') quality characters at qual[i] */
+int bm_pack_reads_v(const uint8_t* const* seq, const uint8_t* const* qual, const uint32_t* qual_len,
+                    const uint64_t* read_off, const uint32_t* pl_off, uint32_t r0, uint32_t r1, uint32_t k, uint32_t b,
+                    uint64_t* planes, uint32_t* qk, uint32_t* n_low);
+/* Builds everything the first batch would otherwise build on arrival (row zeros for p->distinguishability, the k-mer
+ * tables and the locator index for p->k), so that a pipeline can do it while its parser fills the first batch. */
+int bm_prepare(bm_ctx* ctx, const bm_params* p);
 /* bm_reads_upload for a packed batch.  qk == NULL: every k-mer window passes the quality test for p->avg_base_quality. */
 int bm_reads_upload_packed(bm_ctx* ctx, const bm_params* p, const uint64_t* planes, const uint32_t* qk,
                            const uint32_t* pl_off, const uint64_t* read_off, uint32_t n_reads);

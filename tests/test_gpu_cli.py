@@ -96,6 +96,39 @@ def test_cli_small_batches_give_the_same_sam(tmp_path):
     _assert_sam_equal(open(tmp_path / "a.sam").read(), g.sam(False))
 
 
+def test_cli_host_threads_do_not_change_the_sam(tmp_path):
+    """--threads only changes how many host threads pack the FASTA / FASTQ and render the SAM"""
+    g = Golden("multirec")
+    d = str(tmp_path)
+    fa, fq, _ = _index(g, d)
+    for t in ("1", "3", "16"):
+        _run("bucketmap", ["-i", "idx", "-q", fq, "-o", f"t{t}.sam", "-g", fa, "-L", str(g.L), "--threads", t,
+                           "--batch-reads", "101"] + _flags(g), d)
+        _assert_sam_equal(open(tmp_path / f"t{t}.sam").read(), g.sam(False))
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 1
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs")
+@pytest.mark.parametrize("case,align", [("repeats", False), ("full300", True)])
+def test_cli_several_devices_give_the_same_sam(tmp_path, case, align):
+    """--devices spreads the batches of one FASTQ over the GPUs (index replicated over NCCL); records leave in read order"""
+    g = Golden(case)
+    d = str(tmp_path)
+    fa, fq, _ = _index(g, d)
+    n = min(_n_gpus(), 4)
+    _run("bucketmap_align" if align else "bucketmap",
+         ["-i", "idx", "-q", fq, "-o", "m.sam", "-g", fa, "-L", str(g.L), "--devices", "0-%d" % (n - 1), "--batch-reads", "23"]
+         + _flags(g), d)
+    _assert_sam_equal(open(tmp_path / "m.sam").read(), g.sam(align))
+
+
 def test_cli_builds_index_when_missing_then_maps(tmp_path):
     """`bucketmap -i -q -o` without a prior -x builds the index first (locator::initialize, locator.h:22-36)"""
     g = Golden("full300")
@@ -105,6 +138,21 @@ def test_cli_builds_index_when_missing_then_maps(tmp_path):
                        "--seed-y", str(g.y)] + _flags(g), d)
     assert sha256_file(tmp_path / "idx.qgram") == g.meta["qgram_sha256"]
     _assert_sam_equal(open(tmp_path / "out.sam").read(), g.sam(False))
+
+
+def test_cli_legacy_index_without_kmers_index_maps_nothing_like_the_reference(tmp_path):
+    """An index written before FracMinHash existed has no .kmers_index file.  The reference then reads no table and zero
+    rows (q_gram_mapper.h:331-357), maps nothing and writes a SAM with the header only, exit code 0.
+    tests/golden/full300.legacy_noindex.sam is what oracle/_ref/bucketmap_49_8192 wrote for the full300 inputs after
+    `rm idx.kmers_index` (observed in the build container)."""
+    g = Golden("full300")
+    d = str(tmp_path)
+    fa, fq, _ = _index(g, d)
+    os.remove(tmp_path / "idx.kmers_index")
+    log = _run("bucketmap", ["-i", "idx", "-q", fq, "-o", "out.sam", "-g", fa, "-L", str(g.L)] + _flags(g), d)
+    want = open(os.path.join(ROOT, "tests", "golden", "full300.legacy_noindex.sam")).read()
+    assert open(tmp_path / "out.sam").read() == want
+    assert "Total mapped locations: 0 " in log
 
 
 def test_cli_argument_errors(tmp_path):
