@@ -12,6 +12,13 @@
 // from (m, end) reading two records per step and prefers diagonal, then up (query base consumed: I), then left (text
 // base consumed: D) -- the conventions of the oracle (oracle/bm_oracle.cpp align_semi_global; seqan3's own tie-breaks
 // are not available in this environment).
+//
+// Two kernels.  k_align_band (the common case) keeps, per text column, only the two 64-row words of the delta vectors that
+// the optimal path can reach: with e edits the path stays on diagonals j - i in [-e, (n-m)+e], so for every e up to
+// E = (63 - (n-m))/2 (28 for a 300-base read and its 307-column window) the rows [j-(n-m)-E, j+E+1] of column j lie in words
+// w0(j), w0(j)+1 -- 40 bytes per column instead of 96, written plane by plane so that a warp's stores are contiguous, with the
+// pattern masks in shared memory instead of 40 registers per thread.  Alignments with more than E edits (false candidates)
+// go to k_align, which records whole columns.
 #include <algorithm>
 
 #include "bm_internal.cuh"
@@ -29,6 +36,8 @@ struct AlignArgs {
     unsigned long long* scratch; uint32_t chunk_n;
     bm_aln* aln; uint32_t* cig_tmp; uint32_t* cig_cnt;
     const uint32_t* cig_off; uint32_t* cigar; const uint32_t* over_list;
+    const uint32_t* id_list;          // MODE 0 over a list (alignments the band kernel passed on) or nullptr: first + t
+    uint32_t* band_over; uint32_t* n_band_over;
 };
 
 template <int NW> struct Rec { static constexpr int kWords = (2 * NW + (NW + 3) / 4 + 1) & ~1; };
@@ -67,7 +76,7 @@ __global__ void __launch_bounds__(kAlnThreads)
 k_align(AlignArgs a, uint32_t first, uint32_t count) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= count) return;
-    const uint32_t id = MODE ? a.over_list[first + t] : first + t;
+    const uint32_t id = MODE ? a.over_list[first + t] : (a.id_list ? a.id_list[first + t] : first + t);
     const bm_loc l = a.locs[id];
     const uint32_t r = read_of_loc(a.loc_off, a.n_reads, id);
     const uint2* qpl = a.rp.pl + a.rp.pl_off[r];            // bit planes of the whole read (32 bases per chunk)
@@ -195,6 +204,181 @@ k_align(AlignArgs a, uint32_t first, uint32_t count) {
     }
 }
 
+// ---- band-limited first pass ------------------------------------------------------------------------------------------------
+constexpr int kBandPlanes = 5;         // Pv[w0], Pv[w0+1], Mv[w0], Mv[w0+1], boundary score of word w0
+
+// first word kept for column j: the word of row max(1, j - nm - E), at most NW-2 (two words are kept)
+template <int NW>
+__device__ __forceinline__ uint32_t band_w0(int j, int nm, int E) {
+    if (NW == 1) return 0u;
+    int r = j - nm - E;
+    if (r < 1) r = 1;
+    uint32_t w = (uint32_t)(r - 1) >> 6;
+    return w > (uint32_t)(NW - 2) ? (uint32_t)(NW - 2) : w;
+}
+
+template <int NW>
+struct BandTracer {
+    const unsigned long long* scratch; size_t stride; uint32_t slot; int nm, E;
+    __device__ __forceinline__ unsigned long long plane(uint32_t col, uint32_t pl) const {
+        return scratch[((size_t)col * kBandPlanes + pl) * stride + slot];
+    }
+    // D[i][col]
+    __device__ __forceinline__ int cell(uint32_t col, uint32_t i) const {
+        if (i == 0) return 0;
+        const uint32_t w0 = band_w0<NW>((int)col, nm, E);
+        const uint32_t w = (i - 1) >> 6, nb = i - 64 * w;
+        const unsigned long long mask = nb == 64 ? ~0ull : ((1ull << nb) - 1ull);
+        int bs = (int)(long long)plane(col, 4);
+        if (w != w0) {                                            // second kept word: its boundary score follows from the first
+            bs += __popcll(plane(col, 0)) - __popcll(plane(col, 2));
+            return bs + __popcll(plane(col, 1) & mask) - __popcll(plane(col, 3) & mask);
+        }
+        return bs + __popcll(plane(col, 0) & mask) - __popcll(plane(col, 2) & mask);
+    }
+    // D[i][col] - D[i-1][col], i >= 1
+    __device__ __forceinline__ int vdelta(uint32_t col, uint32_t i) const {
+        const uint32_t w0 = band_w0<NW>((int)col, nm, E);
+        const uint32_t w = (i - 1) >> 6, b = (i - 1) & 63;
+        const uint32_t sel = (w != w0) ? 1u : 0u;
+        return (int)((plane(col, sel) >> b) & 1ull) - (int)((plane(col, 2 + sel) >> b) & 1ull);
+    }
+};
+
+template <int NW>
+__global__ void __launch_bounds__(kAlnThreads)
+k_align_band(AlignArgs a, uint32_t first, uint32_t count) {
+    extern __shared__ unsigned long long s_eq[];                  // [4][NW][kAlnThreads] pattern masks
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const uint32_t id = first + t;
+    const bm_loc l = a.locs[id];
+    const uint32_t r = read_of_loc(a.loc_off, a.n_reads, id);
+    const uint2* qpl = a.rp.pl + a.rp.pl_off[r];
+    const uint32_t qch = a.rp.pl_off[r + 1] - a.rp.pl_off[r];
+    const uint32_t m = (uint32_t)(a.read_off[r + 1] - a.read_off[r]);
+    const uint32_t blen = a.blen[l.bucket];
+    bm_aln out;
+    out.score = 0; out.begin = 0; out.map_qual = 0; out.kept = 0; out.cigar_off = 0; out.cigar_len = 0;
+    if (l.offset < 0 || (uint32_t)l.offset >= blen || m == 0 || m > 64u * NW) {
+        a.aln[id] = out; a.cig_cnt[id] = 0;
+        return;
+    }
+    const uint32_t extra = (uint32_t)(unsigned long long)__fmul_rn(a.indel_rate, (float)m);
+    const uint32_t n = min(m + 1u + extra, blen - (uint32_t)l.offset);          // :550
+    const uint64_t tbase = a.bstart[l.bucket] + (uint32_t)l.offset;
+    const bool rev = l.is_original == 0;
+    const int nm = (int)n - (int)m;
+    const int E = (63 - (nm > 0 ? nm : 0)) / 2;
+
+    unsigned long long* eq = s_eq + threadIdx.x;
+#define EQ(c, w) eq[((c) * NW + (w)) * kAlnThreads]
+#pragma unroll
+    for (int w = 0; w < NW; w++) {
+        const uint32_t lim = (m > 64u * w) ? min(64u, m - 64u * w) : 0u;
+        const unsigned long long mask = lim == 64u ? ~0ull : ((1ull << lim) - 1ull);
+        uint2 c0 = make_uint2(0u, 0u), c1 = make_uint2(0u, 0u);
+        if (2u * w < qch) c0 = __ldg(qpl + 2 * w);
+        if (2u * w + 1u < qch) c1 = __ldg(qpl + 2 * w + 1);
+        const unsigned long long lo = (unsigned long long)c0.x | ((unsigned long long)c1.x << 32);
+        const unsigned long long hi = (unsigned long long)c0.y | ((unsigned long long)c1.y << 32);
+        EQ(0, w) = ~lo & ~hi & mask; EQ(1, w) = lo & ~hi & mask; EQ(2, w) = ~lo & hi & mask; EQ(3, w) = lo & hi & mask;
+    }
+    unsigned long long Pv[NW], Mv[NW];
+    int bs[NW];
+#pragma unroll
+    for (int w = 0; w < NW; w++) { Pv[w] = ~0ull; Mv[w] = 0ull; bs[w] = 64 * w; }
+    const uint32_t lastw = (m - 1) >> 6, lastb = (m - 1) & 63;
+    const size_t stride = a.chunk_n;
+    unsigned long long* rec0 = a.scratch + t;
+    constexpr int W1 = NW > 1 ? 1 : 0;
+    // column 0
+    rec0[0 * stride] = Pv[0]; rec0[1 * stride] = Pv[W1]; rec0[2 * stride] = Mv[0]; rec0[3 * stride] = Mv[W1];
+    rec0[4 * stride] = (unsigned long long)(long long)bs[0];
+    int score = (int)m, best = (int)m;
+    uint32_t bj = 0;
+    uint32_t j = 1;
+    // the columns are walked in NW-1 phases: inside phase ww the kept words are ww, ww+1 (compile-time register indices)
+#pragma unroll
+    for (int ww = 0; ww < (NW > 1 ? NW - 1 : 1); ww++) {
+        uint32_t jend = n;
+        if (ww < NW - 2) { const int e2 = 64 * (ww + 1) + nm + E; jend = e2 < 0 ? 0u : ((uint32_t)e2 < n ? (uint32_t)e2 : n); }
+        for (; j <= jend; j++) {
+            const uint32_t tc = rev ? 3u - bm_gbase(a.packed, tbase + (n - j)) : bm_gbase(a.packed, tbase + (j - 1));   // :563-567
+            int hin = 0;
+#pragma unroll
+            for (int w = 0; w < NW; w++) {
+                unsigned long long Eq = EQ(tc, w);
+                const unsigned long long hneg = hin < 0 ? 1ull : 0ull, hpos = hin > 0 ? 1ull : 0ull;
+                const unsigned long long Xv = Eq | Mv[w];
+                Eq |= hneg;
+                const unsigned long long Xh = (((Eq & Pv[w]) + Pv[w]) ^ Pv[w]) | Eq;
+                unsigned long long Ph = Mv[w] | ~(Xh | Pv[w]);
+                unsigned long long Mh = Pv[w] & Xh;
+                if (w == (int)lastw) score += (int)((Ph >> lastb) & 1ull) - (int)((Mh >> lastb) & 1ull);
+                const int hout = (int)(Ph >> 63) - (int)(Mh >> 63);
+                Ph = (Ph << 1) | hpos;
+                Mh = (Mh << 1) | hneg;
+                Pv[w] = Mh | ~(Xv | Ph);
+                Mv[w] = Ph & Xv;
+                if (w + 1 < NW) bs[w + 1] += hout;
+                hin = hout;
+            }
+            unsigned long long* rc = rec0 + (size_t)j * kBandPlanes * stride;
+            rc[0 * stride] = Pv[ww]; rc[1 * stride] = Pv[ww + W1]; rc[2 * stride] = Mv[ww]; rc[3 * stride] = Mv[ww + W1];
+            rc[4 * stride] = (unsigned long long)(long long)bs[ww];
+            if (score <= best) { best = score; bj = j; }        // last column attaining the minimum
+        }
+    }
+#undef EQ
+    out.score = -best;
+    out.map_qual = 60u + (uint32_t)out.score;                                    // :570, 32-bit wrap
+    out.kept = ((unsigned long long)out.map_qual >= (unsigned long long)a.quality_threshold) ? 1u : 0u;
+    if (best > E) {                                              // the path may leave the kept words: full-column kernel
+        a.aln[id] = out; a.cig_cnt[id] = 0;
+        a.band_over[atomicAdd(a.n_band_over, 1u)] = id;
+        return;
+    }
+    // traceback from (m, bj): diagonal, then up (I), then left (D)
+    BandTracer<NW> tr{a.scratch, stride, t, nm, E};
+    uint32_t i = m, nops = 0, cur_op = 3, cur_len = 0;
+    j = bj;
+    int cur = best;
+    uint32_t* tmp = a.cig_tmp + (size_t)id * kCigTmp;
+    auto flush = [&]() {
+        if (cur_len) {
+            if (nops < kCigTmp) tmp[nops] = (cur_len << 4) | cur_op;
+            nops++;
+        }
+    };
+    while (i > 0) {
+        uint32_t op;
+        int nxt;
+        const int dg = (j > 0) ? tr.cell(j - 1, i - 1) : 0;
+        bool mism = true;
+        if (j > 0) {
+            const uint32_t tc = rev ? 3u - bm_gbase(a.packed, tbase + (n - j)) : bm_gbase(a.packed, tbase + (j - 1));
+            const uint2 qc = __ldg(qpl + ((i - 1) >> 5));
+            mism = ((((qc.y >> ((i - 1) & 31u)) & 1u) << 1) | ((qc.x >> ((i - 1) & 31u)) & 1u)) != tc;
+        }
+        if (j > 0 && cur == dg + (mism ? 1 : 0)) { op = 0; nxt = dg; }
+        else {
+            const int up = cur - tr.vdelta(j, i);
+            if (cur == up + 1) { op = 1; nxt = up; }
+            else { op = 2; nxt = tr.cell(j - 1, i); }
+        }
+        if (op != cur_op) { flush(); cur_op = op; cur_len = 0; }
+        cur_len++;
+        cur = nxt;
+        if (op == 0) { i--; j--; } else if (op == 1) { i--; } else { j--; }
+    }
+    flush();
+    out.begin = j;
+    out.cigar_len = nops;
+    a.aln[id] = out;
+    a.cig_cnt[id] = nops;
+}
+
 // final CIGAR arrays: reverse the first-pass ops into place; alignments with more ops than kCigTmp go to the overflow list
 __global__ void k_cigar_write(bm_aln* __restrict__ aln, const uint32_t* __restrict__ cig_off,
                               const uint32_t* __restrict__ cig_tmp, uint32_t n, uint32_t* __restrict__ cigar,
@@ -209,25 +393,58 @@ __global__ void k_cigar_write(bm_aln* __restrict__ aln, const uint32_t* __restri
 
 template <int NW>
 cudaError_t run_align(bm_ctx* c, AlignArgs& a, uint32_t n_aln, uint32_t max_cols) {
-    // first pass in chunks sized by the scratch budget
-    const size_t rec = (size_t)Rec<NW>::kWords * 8;
     size_t free_b = 0, total_b = 0;
     cudaError_t e = cudaMemGetInfo(&free_b, &total_b);
     if (e != cudaSuccess) return e;
     size_t budget = free_b / 2 + c->d_aln_scratch.cap;
     if (budget > ((size_t)16 << 30)) budget = (size_t)16 << 30;
-    size_t per = rec * max_cols;
-    uint32_t chunk = (uint32_t)std::min<size_t>(n_aln, std::max<size_t>(budget / per, kAlnThreads));
+    // ---- band kernel on everything, in chunks sized by the scratch budget ----
+    e = c->d_loc_over.ensure((size_t)(n_aln + 2) * 4 + 64);
+    if (e != cudaSuccess) return e;
+    a.band_over = c->d_loc_over.as<uint32_t>();
+    a.n_band_over = a.band_over + n_aln;
+    e = cudaMemsetAsync(a.n_band_over, 0, 4, c->stream);
+    if (e != cudaSuccess) return e;
+    {
+        const size_t per = (size_t)kBandPlanes * 8 * max_cols;
+        uint32_t chunk = (uint32_t)std::min<size_t>(n_aln, std::max<size_t>(budget / per, kAlnThreads));
+        chunk = (chunk + kAlnThreads - 1) / kAlnThreads * kAlnThreads;
+        e = c->d_aln_scratch.ensure((size_t)chunk * per);
+        if (e != cudaSuccess) return e;
+        a.scratch = c->d_aln_scratch.as<unsigned long long>();
+        a.chunk_n = chunk;
+        const size_t smem = (size_t)4 * NW * kAlnThreads * 8;
+        if (smem > 48 * 1024) {
+            e = cudaFuncSetAttribute(k_align_band<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+        }
+        for (uint32_t first = 0; first < n_aln; first += chunk) {
+            const uint32_t cnt = std::min(chunk, n_aln - first);
+            KScope ks(c, BM_K_ALIGN);
+            k_align_band<NW><<<(cnt + kAlnThreads - 1) / kAlnThreads, kAlnThreads, smem, c->stream>>>(a, first, cnt);
+        }
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    // ---- what left the band (more than E edits): whole-column records ----
+    uint32_t n_over = 0;
+    e = cudaMemcpyAsync(&n_over, a.n_band_over, 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return e;
+    const size_t per = (size_t)Rec<NW>::kWords * 8 * max_cols;
+    uint32_t chunk = (uint32_t)std::min<size_t>(n_over ? n_over : 1, std::max<size_t>(budget / per, kAlnThreads));
     chunk = (chunk + kAlnThreads - 1) / kAlnThreads * kAlnThreads;
-    e = c->d_aln_scratch.ensure((size_t)chunk * per);
+    e = c->d_aln_scratch.ensure((size_t)chunk * per);            // also what the CIGAR overflow pass (MODE 1) uses
     if (e != cudaSuccess) return e;
     a.scratch = c->d_aln_scratch.as<unsigned long long>();
     a.chunk_n = chunk;
-    for (uint32_t first = 0; first < n_aln; first += chunk) {
-        const uint32_t cnt = std::min(chunk, n_aln - first);
+    a.id_list = a.band_over;
+    for (uint32_t first = 0; first < n_over; first += chunk) {
+        const uint32_t cnt = std::min(chunk, n_over - first);
         KScope ks(c, BM_K_ALIGN);
         k_align<NW, 0><<<(cnt + kAlnThreads - 1) / kAlnThreads, kAlnThreads, 0, c->stream>>>(a, first, cnt);
     }
+    a.id_list = nullptr;
     return cudaGetLastError();
 }
 
@@ -275,6 +492,7 @@ int bm_align_device(bm_ctx* c, const bm_params* p) {
     a.scratch = nullptr; a.chunk_n = 0;
     a.aln = c->d_aln.as<bm_aln>(); a.cig_tmp = c->d_cigar_fixed.as<uint32_t>(); a.cig_cnt = c->d_cigar_cnt.as<uint32_t>();
     a.cig_off = c->d_cigar_off.as<uint32_t>(); a.cigar = nullptr; a.over_list = nullptr;
+    a.id_list = nullptr; a.band_over = nullptr; a.n_band_over = nullptr;
     const uint32_t nw = (max_len + 63) / 64;
     cudaError_t e;
     if (nw <= 1) e = run_align<1>(c, a, n_aln, max_cols);

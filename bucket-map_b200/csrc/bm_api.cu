@@ -5,6 +5,8 @@
 #include <mutex>
 #include <new>
 #include <set>
+#include <thread>
+#include <vector>
 
 #include <cub/device/device_scan.cuh>
 
@@ -100,7 +102,7 @@ int bm_ref_upload(bm_ctx* c, const uint8_t* packed, uint64_t n_bases, const uint
     c->d_gidx_pos.release(); c->d_gidx_off.release(); c->gidx_k = 0;          // the position index belongs to the old text
     BM_CK(c, c->d_packed.ensure(nbytes + 64));
     BM_CK(c, cudaMemsetAsync((uint8_t*)c->d_packed.p + nbytes, 0, 64, c->stream));   // kernels read whole words
-    BM_CK(c, cudaMemcpyAsync(c->d_packed.p, packed, nbytes, cudaMemcpyHostToDevice, c->stream));
+    { int rh = bm_internal_h2d(c, c->d_packed.p, packed, nbytes); if (rh) return rh; }
     BM_CK(c, c->d_bstart.ensure((size_t)(n_emit + 1) * 8));
     BM_CK(c, c->d_blen.ensure((size_t)(n_emit + 1) * 4));
     uint32_t mx = 0;
@@ -132,7 +134,7 @@ static void sample_det(uint32_t n, uint32_t ub, std::vector<uint32_t>& out) {
 
 // Sizes the host tables and the device buffers of a batch of n_reads reads (n_seg is bounded by
 // n_reads * num_segment_samples) and resets the per-batch state; the tables are filled by bm_internal_build_segments.
-int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads) {
+int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads, const uint32_t* pl_off) {
     if (p->read_len == 0 || p->num_segment_samples == 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad parameters");
     c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
     c->lsamp_k = c->lsamp_P = c->lsamp_b = 0;
@@ -140,14 +142,20 @@ int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_
     const uint64_t nbytes = read_off[n_reads] - read_off[0];
     // long reads (> 2r) are cut into num_segment_samples segments; without one the table has one entry per read
     // exact segment count: reads longer than 2r are cut into num_segment_samples segments (one cheap pass)
-    uint64_t n_long = 0;
+    uint64_t n_long = 0, n_chunks = 0, max_len = 0;
     const uint64_t two_r = 2ull * p->read_len;
-    for (uint32_t i = 0; i < n_reads; i++) n_long += (read_off[i + 1] - read_off[i]) > two_r;
+    for (uint32_t i = 0; i < n_reads; i++) {               // one pass: long reads, chunks of the packed form, longest read
+        const uint64_t len = read_off[i + 1] - read_off[i];
+        n_long += len > two_r;
+        n_chunks += (len + 31) / 32;
+        max_len = len > max_len ? len : max_len;
+        if (pl_off && (uint64_t)(pl_off[i + 1] - pl_off[i]) != (len + 31) / 32)
+            BM_FAIL(c, BM_E_ARG, "packed batch: pl_off is not the layout of bm_pack_layout");
+    }
+    if (max_len > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31 (or read_off not monotone)");
+    c->batch_max_len = (uint32_t)max_len;
     const uint64_t seg_cap = n_reads + n_long * (p->num_segment_samples - 1);
     if (seg_cap > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: too many segments in one batch");
-    // chunks of the packed form: ceil(len/32) per read
-    uint64_t n_chunks = 0;
-    for (uint32_t i = 0; i < n_reads; i++) n_chunks += (read_off[i + 1] - read_off[i] + 31) / 32;
     if (n_chunks > 0xFFFFFFF0ull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: more than 2^32 chunks of 32 bases in one batch");
     c->n_pl_chunks = n_chunks;
     BM_CK(c, c->h_pl_off.ensure((size_t)(n_reads + 1) * 4));
@@ -170,6 +178,33 @@ int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_
     BM_CK(c, c->d_seg_len.ensure((size_t)(seg_cap + 1) * 4));
     c->n_reads = n_reads; c->n_seg = 0; c->n_seg_total = (uint32_t)seg_cap; c->max_seg_len = 0; c->max_read_len = 0;
     c->n_read_bytes = nbytes;
+    c->h_seg_valid = true;
+    return BM_OK;
+}
+
+// Reads [r0, r1) of a batch WITHOUT long reads (one segment per read, segment index == read index): only the offset
+// tables are made on the host -- copied from the caller's arrays where those can be used as they are -- and the segment
+// tables are written on the device (k_unit_segments).  pl_off: the caller's chunk offsets (packed batches) or nullptr.
+int bm_internal_build_unit_range(bm_ctx* c, const bm_params* p, const uint64_t* read_off, const uint32_t* pl_off,
+                                 uint32_t r0, uint32_t r1) {
+    uint64_t* off_rel = c->h_off_rel.as<uint64_t>();
+    uint32_t* hpl = c->h_pl_off.as<uint32_t>();
+    const uint64_t base = read_off[0];
+    if (base == 0) memcpy(off_rel + r0, read_off + r0, (size_t)(r1 - r0 + 1) * 8);
+    else for (uint32_t i = r0; i <= r1; i++) off_rel[i] = read_off[i] - base;
+    if (pl_off) {
+        const uint32_t pb = pl_off[0];
+        if (pb == 0) memcpy(hpl + r0, pl_off + r0, (size_t)(r1 - r0 + 1) * 4);
+        else for (uint32_t i = r0; i <= r1; i++) hpl[i] = pl_off[i] - pb;
+    } else {
+        uint32_t plo = r0 ? hpl[r0] : 0u;
+        for (uint32_t i = r0; i < r1; i++) { hpl[i] = plo; plo += (uint32_t)((read_off[i + 1] - read_off[i] + 31) / 32); }
+        hpl[r1] = plo;
+    }
+    c->n_seg = r1;
+    c->max_read_len = c->batch_max_len;
+    c->max_seg_len = c->batch_max_len < p->read_len ? c->batch_max_len : p->read_len;
+    c->h_seg_valid = false;                      // the host copies of the segment tables were not made
     return BM_OK;
 }
 
@@ -236,7 +271,7 @@ int bm_reads_upload(bm_ctx* c, const bm_params* p, const uint8_t* seq, const uin
     cudaSetDevice(c->device);
     // read i = seq[read_off[i], read_off[i+1]); read_off[0] may be non-zero (a slice of a larger batch)
     c->want_ascii = true;
-    int r = bm_internal_reads_begin(c, p, read_off, n_reads);
+    int r = bm_internal_reads_begin(c, p, read_off, n_reads, nullptr);
     if (r) return r;
     r = bm_internal_build_segments(c, p, read_off, 0, n_reads);
     if (r) return r;
@@ -262,13 +297,10 @@ int bm_reads_upload_packed(bm_ctx* c, const bm_params* p, const uint64_t* planes
     if (!p || !read_off || !pl_off || (n_reads && !planes)) BM_FAIL(c, BM_E_ARG, "bm_reads_upload_packed: bad arguments");
     cudaSetDevice(c->device);
     c->want_ascii = false;
-    int r = bm_internal_reads_begin(c, p, read_off, n_reads);
+    int r = bm_internal_reads_begin(c, p, read_off, n_reads, pl_off);
     if (r) return r;
     r = bm_internal_build_segments(c, p, read_off, 0, n_reads);
     if (r) return r;
-    const uint32_t* hpl = c->h_pl_off.as<uint32_t>();
-    for (uint32_t i = 0; i <= n_reads; i++)
-        if (pl_off[i] - pl_off[0] != hpl[i]) BM_FAIL(c, BM_E_ARG, "bm_reads_upload_packed: pl_off is not the layout of bm_pack_layout");
     const uint64_t nch = c->n_pl_chunks;
     if (nch) {
         BM_CK(c, cudaMemcpyAsync(c->d_pl.p, planes + pl_off[0], nch * 8, cudaMemcpyHostToDevice, c->stream));
@@ -287,6 +319,14 @@ int bm_reads_segments(bm_ctx* c, uint32_t* n_seg, uint32_t* seg_read, uint32_t* 
     if (!c->have_reads) BM_FAIL(c, BM_E_ARG, "bm_reads_segments: no read batch resident");
     if (n_seg) *n_seg = c->n_seg;
     size_t b = (size_t)c->n_seg * 4;
+    if (!c->h_seg_valid && b && (seg_read || seg_start || seg_len)) {     // tables were written on the device: fetch them
+        cudaSetDevice(c->device);
+        BM_CK(c, cudaMemcpyAsync(c->h_seg_read.p, c->d_seg_read.p, b, cudaMemcpyDeviceToHost, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->h_seg_start.p, c->d_seg_start.p, b, cudaMemcpyDeviceToHost, c->stream));
+        BM_CK(c, cudaMemcpyAsync(c->h_seg_len.p, c->d_seg_len.p, b, cudaMemcpyDeviceToHost, c->stream));
+        BM_CK(c, cudaStreamSynchronize(c->stream));
+        c->h_seg_valid = true;
+    }
     if (seg_read && b) memcpy(seg_read, c->h_seg_read.p, b);
     if (seg_start && b) memcpy(seg_start, c->h_seg_start.p, b);
     if (seg_len && b) memcpy(seg_len, c->h_seg_len.p, b);
@@ -379,6 +419,56 @@ void bm_host_free(void* p) {
 }
 
 }  // extern "C"
+
+// Large host->device copy from memory that may be pageable (a memory-mapped index file, the FASTA packer's array).  The
+// driver stages such copies through its own pinned buffer on one thread (6-10 GB/s); here a few threads copy 16 MB
+// pieces into their own pinned slots and each hands its piece to the copy engine, which keeps the link busy.
+int bm_internal_h2d(bm_ctx* c, void* dst, const void* src, size_t bytes) {
+    constexpr size_t kPiece = (size_t)16 << 20;
+    cudaPointerAttributes at;
+    const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (pinned || bytes < 4 * kPiece) {
+        BM_CK(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
+        return BM_OK;
+    }
+    constexpr int kThreads = 4, kSlots = 2;
+    BM_CK(c, cudaStreamSynchronize(c->stream));               // whatever was ordered before the copy on the library stream
+    std::vector<cudaError_t> errs(kThreads, cudaSuccess);
+    std::vector<std::thread> ts;
+    const size_t n_pieces = (bytes + kPiece - 1) / kPiece;
+    const int device = c->device;
+    for (int t = 0; t < kThreads; t++) {
+        ts.emplace_back([=, &errs] {
+            cudaSetDevice(device);
+            void* slot[kSlots] = {nullptr, nullptr};
+            cudaEvent_t ev[kSlots] = {nullptr, nullptr};
+            cudaStream_t st = nullptr;
+            cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+            for (int i = 0; i < kSlots && e == cudaSuccess; i++) {
+                e = cudaMallocHost(&slot[i], kPiece);
+                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
+            }
+            size_t k = 0;
+            for (size_t p = (size_t)t; p < n_pieces && e == cudaSuccess; p += kThreads, k++) {
+                const int sl = (int)(k % kSlots);
+                if (k >= (size_t)kSlots) e = cudaEventSynchronize(ev[sl]);
+                if (e != cudaSuccess) break;
+                const size_t o = p * kPiece, n = bytes - o < kPiece ? bytes - o : kPiece;
+                memcpy(slot[sl], (const uint8_t*)src + o, n);
+                e = cudaMemcpyAsync((uint8_t*)dst + o, slot[sl], n, cudaMemcpyHostToDevice, st);
+                if (e == cudaSuccess) e = cudaEventRecord(ev[sl], st);
+            }
+            if (st) { cudaError_t e2 = cudaStreamSynchronize(st); if (e == cudaSuccess) e = e2; }
+            for (int i = 0; i < kSlots; i++) { if (ev[i]) cudaEventDestroy(ev[i]); if (slot[i]) cudaFreeHost(slot[i]); }
+            if (st) cudaStreamDestroy(st);
+            errs[t] = e;
+        });
+    }
+    for (auto& t : ts) t.join();
+    for (cudaError_t e : errs) BM_CK(c, e);
+    return BM_OK;
+}
 
 int bm_internal_exclusive_scan(bm_ctx* c, const uint32_t* d_in, uint32_t* d_out, uint32_t n) {
     size_t tmp = 0;

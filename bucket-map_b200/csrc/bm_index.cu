@@ -348,7 +348,7 @@ int bm_index_load(bm_ctx* c, const int32_t* k2i, uint32_t q, const uint8_t* rows
     uint64_t raw = (uint64_t)n_rows * c->W, padded = (uint64_t)n_rows * c->Wp;
     if (n_rows) {
         BM_CK(c, c->d_stage.ensure(raw));
-        BM_CK(c, cudaMemcpyAsync(c->d_stage.p, rows, raw, cudaMemcpyHostToDevice, c->stream));
+        { int rh = bm_internal_h2d(c, c->d_stage.p, rows, raw); if (rh) return rh; }
         KScope ks(c, BM_K_AUX);
         k_pad_rows<<<c->sm_count * 8, 256, 0, c->stream>>>(c->d_stage.as<uint8_t>(), c->d_rows.as<uint8_t>(), c->W, c->Wp, padded);
     }

@@ -156,7 +156,7 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const HostReads& src, const uint
     };
     int r = copy_text(0);
     if (r) return r;
-    r = bm_internal_reads_begin(c, p, read_off, n_reads);
+    r = bm_internal_reads_begin(c, p, read_off, n_reads, packed ? src.pl_off : nullptr);
     if (r) { cudaStreamSynchronize(c->copy_stream); return r; }
     c->ascii_resident = !packed; c->have_qk = !packed || src.qk != nullptr;
     c->pack_k = p->k; c->pack_b = p->avg_base_quality;
@@ -173,7 +173,8 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const HostReads& src, const uint
         const uint32_t s0 = c->n_seg;
         if (j == 1) t_first = since();
         if (j) { r = copy_text(j); if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; } }
-        r = bm_internal_build_segments(c, p, read_off, r0, r1);
+        r = unit_segments ? bm_internal_build_unit_range(c, p, read_off, packed ? src.pl_off : nullptr, r0, r1)
+                          : bm_internal_build_segments(c, p, read_off, r0, r1);
         if (r) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream); return r; }
         const uint32_t s1 = c->n_seg;
         cudaStream_t cs = c->copy_stream;
@@ -182,10 +183,6 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const HostReads& src, const uint
                                  cudaMemcpyHostToDevice, cs));
         BM_CK(c, cudaMemcpyAsync(c->d_pl_off.as<uint32_t>() + r0, c->h_pl_off.as<uint32_t>() + r0, (size_t)(r1 - r0 + 1) * 4,
                                  cudaMemcpyHostToDevice, cs));
-        if (packed && src.pl_off[r1] - src.pl_off[0] != c->h_pl_off.as<uint32_t>()[r1]) {
-            cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->stream);
-            BM_FAIL(c, BM_E_ARG, "bm_map_locate_packed: pl_off is not the layout of bm_pack_layout");
-        }
         if (!unit_segments)
             BM_CK(c, cudaMemcpyAsync(c->d_read_seg0.as<uint32_t>() + r0, c->h_read_seg0.as<uint32_t>() + r0, (size_t)(r1 - r0 + 1) * 4,
                                      cudaMemcpyHostToDevice, cs));

@@ -27,6 +27,7 @@ context::context(int device) : device_(device) {
     // device-memory options: both on by default, results identical either way
     if (const char* e = std::getenv("BM_KMER_TABLE")) bm_index_kmer_table(c_, std::atoi(e), 0);
     if (const char* e = std::getenv("BM_LOCATOR_INDEX")) bm_locator_index(c_, std::atoi(e) ? 1 : 0);
+    if (const char* e = std::getenv("BM_FINE_TABLE")) bm_index_fine_table(c_, std::atoi(e) ? 1 : 0);
 }
 context::~context() { bm_ctx_destroy(c_); }
 

@@ -130,6 +130,20 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
 
     fastq_reader fin(sequence_file);
     if (!fin.ok()) { std::cerr << "[ERROR]\t\tCannot read " << sequence_file << ".\n"; return; }
+    // The two big derived tables pay for themselves only on long runs: the locator's genome k-mer index (16 B per base of
+    // scratch, ~50 ms on 1.7 Gbp, saves ~5 ms per million reads) and the full-resolution k-mer table (tens of GB, saves
+    // ~1 ms per million reads).  A run of a few million reads is faster without building, allocating and freeing them;
+    // $BM_LOCATOR_INDEX / $BM_FINE_TABLE decide explicitly.  Results are identical either way.
+    int want_lidx = -1, want_fine = -1;            // -1: leave the context's setting alone
+    {
+        std::error_code ec;
+        const uint64_t fq_bytes = (uint64_t)fs::file_size(sequence_file, ec);
+        const uint64_t est_reads = ec ? 0 : fq_bytes / (2ull * read_length + 16);
+        if (!std::getenv("BM_LOCATOR_INDEX")) want_lidx = est_reads >= 8000000ull ? 1 : 0;
+        if (!std::getenv("BM_FINE_TABLE")) want_fine = est_reads >= 16000000ull ? 1 : 0;
+        if (want_lidx >= 0) bm_locator_index(c0, want_lidx);
+        if (want_fine >= 0) bm_index_fine_table(c0, want_fine);
+    }
     int out_fd = ::open(sam_file.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
     if (out_fd < 0) { std::cerr << "[ERROR]\t\tCannot write " << sam_file << ".\n"; return; }
 
@@ -162,10 +176,12 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
     // several GPUs: one context per device; reference and index travel from the mapper's context over NCCL
     bool setup_failed = false;
     const double t_setup = now_s();
-    if (n_dev > 1) {
+    if (n_dev > 1 && !setup_failed) {
         for (size_t i = 1; i < n_dev; i++) {
             std::unique_ptr<context> cx(new context(devices_[i]));
             bm_ctx* c = cx->get();
+            if (want_lidx >= 0) bm_locator_index(c, want_lidx);
+            if (want_fine >= 0) bm_index_fine_table(c, want_fine);
             devs.push_back({c, std::move(cx)});
         }
         uint8_t id[BM_COMM_ID_BYTES];
@@ -183,7 +199,7 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
             for (size_t i = 0; i < n_dev; i++)
                 if (rcs[i]) { std::cerr << "[ERROR]\t\t" << bm_last_error(devs[i].c) << "\n"; setup_failed = true; }
         }
-    } else {
+    } else if (!setup_failed) {
         rc = bm_prepare(c0, &p);               // row zeros, k-mer tables, locator index: before the first batch arrives
         if (rc) { std::cerr << "[ERROR]\t\t" << bm_last_error(c0) << "\n"; setup_failed = true; }
     }

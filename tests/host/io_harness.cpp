@@ -1,6 +1,7 @@
 // Test harness for the host I/O stage (no GPU needed): the multi-threaded FASTA packer and the FASTQ splitter / packer.
 //   io_harness fasta <file> <L> <r> <threads>      -> n_bases, NB, records, buckets, FNV-1a of the packed bytes
 //   io_harness fastq <file> <batch> <k> <b> <threads> -> per batch: reads, chunks, all_pass, FNV-1a of planes / qk / offsets / ids
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -43,6 +44,18 @@ int main(int argc, char** argv) {
                    (unsigned long long)fnv(b.read_off.data(), (size_t)(n + 1) * 8), (unsigned long long)fnv(plo, (size_t)(n + 1) * 4),
                    (unsigned long long)hid, (unsigned long long)hq);
         }
+        return 0;
+    }
+    if (!strcmp(argv[1], "fastq_time") && argc == 7) {            // wall time of the splitter + packer alone
+        bm::set_host_threads((unsigned)atoi(argv[6]));
+        bm::fastq_reader fin(argv[2]);
+        if (!fin.ok()) return 3;
+        bm::read_batch b;
+        uint64_t reads = 0;
+        const auto t0 = std::chrono::steady_clock::now();
+        while (fin.next(b, (uint32_t)atoi(argv[3]), (uint64_t)1 << 31, (uint32_t)atoi(argv[4]), (uint32_t)atoi(argv[5]))) reads += b.size();
+        const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        printf("reads %llu seconds %.4f reads_per_s %.0f\n", (unsigned long long)reads, dt, reads / dt);
         return 0;
     }
     return 2;
