@@ -33,7 +33,7 @@ struct AlignArgs {
     ReadPlanes rp; const uint64_t* read_off; uint32_t n_reads;
     const uint32_t* loc_off; const bm_loc* locs;
     float indel_rate; uint32_t quality_threshold;
-    unsigned long long* scratch; uint32_t chunk_n;
+    unsigned long long* scratch; uint32_t chunk_n, max_cols;
     bm_aln* aln; uint32_t* cig_tmp; uint32_t* cig_cnt;
     const uint32_t* cig_off; uint32_t* cigar; const uint32_t* over_list;
     const uint32_t* id_list;          // MODE 0 over a list (alignments the band kernel passed on) or nullptr: first + t
@@ -205,6 +205,16 @@ k_align(AlignArgs a, uint32_t first, uint32_t count) {
 }
 
 // ---- band-limited first pass ------------------------------------------------------------------------------------------------
+// 32 bases of the 2-bit genome from base `pos` on (base t at bits 2t): two aligned 8-byte loads and a funnel shift.  The
+// text of an alignment is read 32 columns at a time, one block ahead, instead of one dependent byte load per column.
+__device__ __forceinline__ unsigned long long load_bases32(const uint8_t* __restrict__ packed, uint64_t pos) {
+    const uint64_t byte = pos >> 2;
+    const uint32_t s = (uint32_t)(byte & 7u) * 8u + (uint32_t)(pos & 3u) * 2u;
+    const unsigned long long* p = reinterpret_cast<const unsigned long long*>(packed + (byte & ~(uint64_t)7));
+    const unsigned long long w0 = __ldg(p), w1 = __ldg(p + 1);
+    return s ? ((w0 >> s) | (w1 << (64u - s))) : w0;
+}
+
 constexpr int kBandPlanes = 5;         // Pv[w0], Pv[w0+1], Mv[w0], Mv[w0+1], boundary score of word w0
 
 // first word kept for column j: the word of row max(1, j - nm - E), at most NW-2 (two words are kept)
@@ -219,9 +229,15 @@ __device__ __forceinline__ uint32_t band_w0(int j, int nm, int E) {
 
 template <int NW>
 struct BandTracer {
-    const unsigned long long* scratch; size_t stride; uint32_t slot; int nm, E;
+    const unsigned long long* rec; int nm, E;                     // rec: this lane's word of column 0, plane 0
     __device__ __forceinline__ unsigned long long plane(uint32_t col, uint32_t pl) const {
-        return scratch[((size_t)col * kBandPlanes + pl) * stride + slot];
+        return rec[((size_t)col * kBandPlanes + pl) * 32];
+    }
+    // the next columns the walk will need, into L1 (a warp's five planes of one column are 1,280 contiguous bytes)
+    __device__ __forceinline__ void prefetch(uint32_t col) const {
+#pragma unroll
+        for (int pl = 0; pl < kBandPlanes; pl++)
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + ((size_t)col * kBandPlanes + pl) * 32));
     }
     // D[i][col]
     __device__ __forceinline__ int cell(uint32_t col, uint32_t i) const {
@@ -289,8 +305,11 @@ k_align_band(AlignArgs a, uint32_t first, uint32_t count) {
 #pragma unroll
     for (int w = 0; w < NW; w++) { Pv[w] = ~0ull; Mv[w] = 0ull; bs[w] = 64 * w; }
     const uint32_t lastw = (m - 1) >> 6, lastb = (m - 1) & 63;
-    const size_t stride = a.chunk_n;
-    unsigned long long* rec0 = a.scratch + t;
+    // Scratch layout [warp][column][plane][lane]: a warp writes 1,280 contiguous bytes per column and its columns follow
+    // each other, so the forward pass streams ~400 KB per warp front to back and the traceback walks the same region back
+    // (open DRAM pages, not one page per store as a [column][plane][alignment] layout would touch).
+    constexpr size_t stride = 32;
+    unsigned long long* rec0 = a.scratch + (size_t)(t >> 5) * a.max_cols * kBandPlanes * 32 + (t & 31u);
     constexpr int W1 = NW > 1 ? 1 : 0;
     // column 0
     rec0[0 * stride] = Pv[0]; rec0[1 * stride] = Pv[W1]; rec0[2 * stride] = Mv[0]; rec0[3 * stride] = Mv[W1];
@@ -298,13 +317,28 @@ k_align_band(AlignArgs a, uint32_t first, uint32_t count) {
     int score = (int)m, best = (int)m;
     uint32_t bj = 0;
     uint32_t j = 1;
+    // text of column j: base idx = j-1 of the window, or, reverse strand, the complement of base n-j (:563-567); the block
+    // of 32 bases in use and the one the walk enters next are kept in registers
+    const uint32_t idx0 = rev ? n - 1 : 0u;
+    uint32_t tblk = idx0 >> 5;
+    unsigned long long tw = load_bases32(a.packed, tbase + 32ull * tblk);
+    unsigned long long tw_next = (rev ? tblk > 0 : (uint64_t)32 * (tblk + 1) < n)
+                                     ? load_bases32(a.packed, tbase + 32ull * (rev ? tblk - 1 : tblk + 1)) : 0ull;
     // the columns are walked in NW-1 phases: inside phase ww the kept words are ww, ww+1 (compile-time register indices)
 #pragma unroll
     for (int ww = 0; ww < (NW > 1 ? NW - 1 : 1); ww++) {
         uint32_t jend = n;
         if (ww < NW - 2) { const int e2 = 64 * (ww + 1) + nm + E; jend = e2 < 0 ? 0u : ((uint32_t)e2 < n ? (uint32_t)e2 : n); }
         for (; j <= jend; j++) {
-            const uint32_t tc = rev ? 3u - bm_gbase(a.packed, tbase + (n - j)) : bm_gbase(a.packed, tbase + (j - 1));   // :563-567
+            const uint32_t idx = rev ? n - j : j - 1;
+            if ((idx >> 5) != tblk) {                            // entered the next block: it is there already; fetch the one after
+                tblk = idx >> 5;
+                tw = tw_next;
+                if (rev ? tblk > 0 : (uint64_t)32 * (tblk + 1) < n)
+                    tw_next = load_bases32(a.packed, tbase + 32ull * (rev ? tblk - 1 : tblk + 1));
+            }
+            const uint32_t tb = (uint32_t)(tw >> ((idx & 31u) * 2u)) & 3u;
+            const uint32_t tc = rev ? 3u - tb : tb;
             int hin = 0;
 #pragma unroll
             for (int w = 0; w < NW; w++) {
@@ -340,10 +374,14 @@ k_align_band(AlignArgs a, uint32_t first, uint32_t count) {
         return;
     }
     // traceback from (m, bj): diagonal, then up (I), then left (D)
-    BandTracer<NW> tr{a.scratch, stride, t, nm, E};
+    BandTracer<NW> tr{rec0, nm, E};
     uint32_t i = m, nops = 0, cur_op = 3, cur_len = 0;
     j = bj;
     int cur = best;
+    uint32_t tb_blk = 0xFFFFFFFFu, q_blk = 0xFFFFFFFFu;          // cached block of the text / chunk of the read
+    unsigned long long tb_w = 0ull;
+    uint2 q_w = make_uint2(0u, 0u);
+    for (uint32_t d = 1; d <= 3 && d <= j; d++) tr.prefetch(j - d);
     uint32_t* tmp = a.cig_tmp + (size_t)id * kCigTmp;
     auto flush = [&]() {
         if (cur_len) {
@@ -357,9 +395,12 @@ k_align_band(AlignArgs a, uint32_t first, uint32_t count) {
         const int dg = (j > 0) ? tr.cell(j - 1, i - 1) : 0;
         bool mism = true;
         if (j > 0) {
-            const uint32_t tc = rev ? 3u - bm_gbase(a.packed, tbase + (n - j)) : bm_gbase(a.packed, tbase + (j - 1));
-            const uint2 qc = __ldg(qpl + ((i - 1) >> 5));
-            mism = ((((qc.y >> ((i - 1) & 31u)) & 1u) << 1) | ((qc.x >> ((i - 1) & 31u)) & 1u)) != tc;
+            const uint32_t idx = rev ? n - j : j - 1;
+            if ((idx >> 5) != tb_blk) { tb_blk = idx >> 5; tb_w = load_bases32(a.packed, tbase + 32ull * tb_blk); }
+            const uint32_t tb = (uint32_t)(tb_w >> ((idx & 31u) * 2u)) & 3u;
+            const uint32_t tc = rev ? 3u - tb : tb;
+            if (((i - 1) >> 5) != q_blk) { q_blk = (i - 1) >> 5; q_w = __ldg(qpl + q_blk); }
+            mism = ((((q_w.y >> ((i - 1) & 31u)) & 1u) << 1) | ((q_w.x >> ((i - 1) & 31u)) & 1u)) != tc;
         }
         if (j > 0 && cur == dg + (mism ? 1 : 0)) { op = 0; nxt = dg; }
         else {
@@ -371,6 +412,7 @@ k_align_band(AlignArgs a, uint32_t first, uint32_t count) {
         cur_len++;
         cur = nxt;
         if (op == 0) { i--; j--; } else if (op == 1) { i--; } else { j--; }
+        if (op != 1 && j >= 4) tr.prefetch(j - 4);                // the column the walk reaches three steps from now
     }
     flush();
     out.begin = j;
@@ -412,7 +454,7 @@ cudaError_t run_align(bm_ctx* c, AlignArgs& a, uint32_t n_aln, uint32_t max_cols
         e = c->d_aln_scratch.ensure((size_t)chunk * per);
         if (e != cudaSuccess) return e;
         a.scratch = c->d_aln_scratch.as<unsigned long long>();
-        a.chunk_n = chunk;
+        a.chunk_n = chunk; a.max_cols = max_cols;
         const size_t smem = (size_t)4 * NW * kAlnThreads * 8;
         if (smem > 48 * 1024) {
             e = cudaFuncSetAttribute(k_align_band<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

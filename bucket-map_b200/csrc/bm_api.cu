@@ -420,53 +420,12 @@ void bm_host_free(void* p) {
 
 }  // extern "C"
 
-// Large host->device copy from memory that may be pageable (a memory-mapped index file, the FASTA packer's array).  The
-// driver stages such copies through its own pinned buffer on one thread (6-10 GB/s); here a few threads copy 16 MB
-// pieces into their own pinned slots and each hands its piece to the copy engine, which keeps the link busy.
+// Large host->device copy from memory that may be pageable (a memory-mapped index file, the FASTA packer's array).  One
+// cudaMemcpyAsync: the driver stages it through its own pinned buffers.  (Tried: four host threads copying 16 MB pieces into
+// their own pinned slots and handing each to the copy engine -- 0.24 s instead of 0.12 s for the 850 MB .qgram image of C2,
+// the slots' cudaMallocHost and the page faults of the mapping cost more than the staging saves; not kept.)
 int bm_internal_h2d(bm_ctx* c, void* dst, const void* src, size_t bytes) {
-    constexpr size_t kPiece = (size_t)16 << 20;
-    cudaPointerAttributes at;
-    const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost;
-    cudaGetLastError();
-    if (pinned || bytes < 4 * kPiece) {
-        BM_CK(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
-        return BM_OK;
-    }
-    constexpr int kThreads = 4, kSlots = 2;
-    BM_CK(c, cudaStreamSynchronize(c->stream));               // whatever was ordered before the copy on the library stream
-    std::vector<cudaError_t> errs(kThreads, cudaSuccess);
-    std::vector<std::thread> ts;
-    const size_t n_pieces = (bytes + kPiece - 1) / kPiece;
-    const int device = c->device;
-    for (int t = 0; t < kThreads; t++) {
-        ts.emplace_back([=, &errs] {
-            cudaSetDevice(device);
-            void* slot[kSlots] = {nullptr, nullptr};
-            cudaEvent_t ev[kSlots] = {nullptr, nullptr};
-            cudaStream_t st = nullptr;
-            cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
-            for (int i = 0; i < kSlots && e == cudaSuccess; i++) {
-                e = cudaMallocHost(&slot[i], kPiece);
-                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
-            }
-            size_t k = 0;
-            for (size_t p = (size_t)t; p < n_pieces && e == cudaSuccess; p += kThreads, k++) {
-                const int sl = (int)(k % kSlots);
-                if (k >= (size_t)kSlots) e = cudaEventSynchronize(ev[sl]);
-                if (e != cudaSuccess) break;
-                const size_t o = p * kPiece, n = bytes - o < kPiece ? bytes - o : kPiece;
-                memcpy(slot[sl], (const uint8_t*)src + o, n);
-                e = cudaMemcpyAsync((uint8_t*)dst + o, slot[sl], n, cudaMemcpyHostToDevice, st);
-                if (e == cudaSuccess) e = cudaEventRecord(ev[sl], st);
-            }
-            if (st) { cudaError_t e2 = cudaStreamSynchronize(st); if (e == cudaSuccess) e = e2; }
-            for (int i = 0; i < kSlots; i++) { if (ev[i]) cudaEventDestroy(ev[i]); if (slot[i]) cudaFreeHost(slot[i]); }
-            if (st) cudaStreamDestroy(st);
-            errs[t] = e;
-        });
-    }
-    for (auto& t : ts) t.join();
-    for (cudaError_t e : errs) BM_CK(c, e);
+    BM_CK(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
     return BM_OK;
 }
 

@@ -90,16 +90,20 @@ int pipeline_run(bm_ctx* c, const bm_params* p, const HostReads& src, const uint
     double t_pre = 0, t_first = 0, t_enq = 0, t_h2d = 0, t_fin = 0, t_loc = 0;
     if (!c->copy_stream) BM_CK(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
 
-    // Chunk schedule: large chunks first (every chunk costs five small table copies on top of its two large ones, and the
-    // link is the bottleneck), then halving towards the end so that only a small mapper launch is left when the last
-    // byte has landed: n/4, n/4, n/4, n/8, n/16, ... down to kChunkMin reads.
+    // Chunk schedule: a small first chunk so that the mapper starts as early as possible, growing chunks while the link
+    // and the mapper run side by side (every chunk costs a handful of small table copies and a launch), and a small last one
+    // so that little mapper work is left when the last byte has landed: 1/16, 1/8, 3/16, 1/4, 1/4, 1/8 of the batch.
     std::vector<uint32_t> bounds(1, 0u);
-    while (bounds.back() < n_reads) {
-        const uint32_t rem = n_reads - bounds.back();
-        uint32_t take = rem / 2 < n_reads / 4 ? rem / 2 : n_reads / 4;
-        if (take < kChunkMin) take = kChunkMin;
-        if (take > rem || rem - take < kChunkMin / 2) take = rem;
-        bounds.push_back(bounds.back() + take);
+    {
+        static const uint32_t kSixteenths[] = {1, 2, 3, 4, 4, 2};
+        uint32_t done16 = 0;
+        for (uint32_t f : kSixteenths) {
+            done16 += f;
+            uint32_t b = (uint32_t)((uint64_t)n_reads * done16 / 16);
+            if (done16 == 16) b = n_reads;
+            if (b - bounds.back() >= kChunkMin || b == n_reads) { if (b > bounds.back()) bounds.push_back(b); }
+        }
+        if (bounds.back() != n_reads) bounds.push_back(n_reads);
     }
     const uint32_t n_chunks = (uint32_t)bounds.size() - 1;
     while (c->chunk_ev.size() < n_chunks) {
