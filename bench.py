@@ -497,6 +497,7 @@ def main():
     lidx_ms = ctx.kernel_stats()["locator_index"][0]    # one-off, inside the first (untimed) locator call
     ktable_k, ktable_bytes = ctx.index_kmer_table_info()
     ftable_k, ftable_bytes = ctx.index_fine_table_info()
+    ktable_group, ktable_density = ctx.index_kmer_table_choice()
     ctx.kernel_stats_reset()
     barrier()
     clocks = ClockSampler(local)
@@ -663,11 +664,15 @@ def main():
         "config": {"workload": workload, "genome_bases": cfg["n_bases"], "bucket_len": L, "NB": NB,
                    "row_bytes": W, "matrix_bytes": int(n_rows) * W, "kmer_table_bytes": int(ktable_bytes),
                    "fine_table_bytes": int(ftable_bytes),
-                   "kmer_table": ("4^%d coarse k-mer rows (AND of each k-mer's q-gram rows, OR-reduced over groups of 16 buckets)%s, "
-                                  "derived on the device from the matrix in %.1f ms; the mapper gathers 1 coarse row per sample "
-                                  "and recounts passing groups exactly" % (
-                                      ktable_k, " + the same rows at full bucket resolution for the recount" if ftable_k else "", ktable_ms))
-                                 if ktable_k else "off: the mapper gathers the k-q+1 q-gram rows per sample",
+                   "kmer_table": ("4^%d coarse k-mer rows (AND of each k-mer's q-gram rows, OR-reduced over groups of %d buckets: "
+                                  "the cost model's choice at a measured row density of %.4f)%s, derived on the device from the "
+                                  "matrix in %.1f ms; the mapper gathers 1 coarse row per sample and recounts passing groups exactly" % (
+                                      ktable_k, ktable_group, ktable_density,
+                                      " + the same rows at full bucket resolution for the recount" if ftable_k else "", ktable_ms))
+                                 if ktable_k else ("none: the mapper gathers the k-q+1 q-gram rows per sample (k_map_sample + k_map_vote)"
+                                                   + (("; the cost model found the gather cheaper at a k-mer row density of %.3f" % ktable_density)
+                                                      if (a.ktable == 1 and ktable_density) else "")),
+                   "kmer_table_buckets_per_bit": int(ktable_group), "kmer_row_density": ktable_density,
                    "reads_per_gpu_per_step": n_reads, "read_len": cfg["read_len"],
                    "flags": "-k %d -l 12 -s 15 -e 0.4 -p 10 -f %g" % (q, a.frac),
                    "parallelism": f"reads sharded x{world}, index replicated",

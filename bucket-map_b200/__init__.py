@@ -54,6 +54,7 @@ SIGNATURES = {
     "bm_index_zeros": (C.c_int, [_vp, C.c_float, _vp, C.POINTER(C.c_uint32)]),
     "bm_index_kmer_table": (C.c_int, [_vp, C.c_int, C.c_uint64]),
     "bm_index_kmer_table_info": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
+    "bm_index_kmer_table_choice": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_double)]),
     "bm_map_handover": (C.c_int, [_vp, C.c_int]),
     "bm_index_fine_table": (C.c_int, [_vp, C.c_int]),
     "bm_index_fine_table_info": (C.c_int, [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]),
@@ -241,6 +242,12 @@ class Context:
         k, n = C.c_uint32(), C.c_uint64()
         self._ck(self.lib.bm_index_fine_table_info(self.h, C.byref(k), C.byref(n)), "bm_index_fine_table_info")
         return k.value, n.value
+
+    def index_kmer_table_choice(self):
+        """(buckets per coarse bit of the resident table or 0, measured k-mer row density)"""
+        g, d = C.c_uint32(), C.c_double()
+        self._ck(self.lib.bm_index_kmer_table_choice(self.h, C.byref(g), C.byref(d)), "bm_index_kmer_table_choice")
+        return g.value, d.value
 
     def map_handover(self, max_groups):
         """lists with more than max_groups passing coarse groups go to the full-width gather (-1: default)"""

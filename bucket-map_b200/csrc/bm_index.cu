@@ -3,6 +3,9 @@
 // Device layout: n_rows rows of Wp bytes, Wp = roundup((NB+7)>>3, 64); bucket j of a row at byte j>>3 bit j&7 exactly
 // like the .qgram file (indexer/bucket_indexer.h:64-73), padding bytes zero.  64-B padded rows make every row start
 // on a DRAM burst boundary and keep the mapper's 16-B vector loads aligned.
+#include <algorithm>
+#include <cmath>
+
 #include "bm_internal.cuh"
 
 namespace {
@@ -144,6 +147,33 @@ k_kmer_coarse(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const 
     }
 }
 
+// Density of the k-mer rows: set bits of the AND row of `n_samples` pseudo-random k-mer codes (one CTA each).  Feeds the
+// choice of the coarse group size.
+__global__ void __launch_bounds__(128)
+k_kmer_density(const uint4* __restrict__ rows, uint32_t Wp16, uint32_t NB, const int32_t* __restrict__ k2i, uint32_t NQ,
+               uint32_t Q, uint32_t kmask, unsigned long long* __restrict__ total) {
+    const uint32_t x = (blockIdx.x * 0x9E3779B1u) & kmask;
+    int32_t r[8];
+    for (uint32_t i = 0; i < NQ; i++) r[i] = __ldg(k2i + ((x >> (2 * i)) & Q));
+    uint32_t ones = 0;
+    for (uint32_t c = threadIdx.x; c < Wp16; c += blockDim.x) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t b = c * 128u + 32u * i;
+            w[i] = (b >= NB) ? 0u : (NB - b >= 32u ? 0xFFFFFFFFu : ((1u << (NB - b)) - 1u));
+        }
+        for (uint32_t i = 0; i < NQ; i++)
+            if (r[i] >= 0) {
+                const uint4 t = __ldg(rows + (size_t)r[i] * Wp16 + c);
+                w[0] &= t.x; w[1] &= t.y; w[2] &= t.z; w[3] &= t.w;
+            }
+        ones += __popc(w[0]) + __popc(w[1]) + __popc(w[2]) + __popc(w[3]);
+    }
+    ones = __reduce_add_sync(0xFFFFFFFFu, ones);
+    if ((threadIdx.x & 31) == 0 && ones) atomicAdd(total, (unsigned long long)ones);
+}
+
 // the same bits indexed by the two q-bit planes of a q-gram as the fused mapper kernel reads them out of its ballot
 // words: index = (hi << q) | lo, bit t of lo / hi = low / high bit of the rank of base t (first base = bit 0)
 __global__ void k_distok_planes(const uint32_t* __restrict__ distok, uint32_t q, uint32_t n_codes, uint32_t* __restrict__ out) {
@@ -170,7 +200,7 @@ int bm_internal_index_set_table(bm_ctx* c, const int32_t* k2i, uint32_t q, uint3
         if (k2i[i] >= 0) { if ((uint32_t)k2i[i] >= n_rows) BM_FAIL(c, BM_E_ARG, "kmer_to_index entry >= n_rows"); cnt++; }
     }
     (void)cnt;
-    c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0; c->frows_k = 0; c->fine_tried_k = 0;
+    c->have_index = false; c->zeros_for_d = -1.f; c->krows_k = 0; c->frows_k = 0; c->fine_tried_k = 0; c->auto_k = 0;
     c->q = q; c->n_rows = n_rows; c->NB = NB;
     c->W = (NB + 7) >> 3; c->Wp = (c->W + 63u) & ~63u;
     BM_CK(c, c->d_k2i.ensure(n_codes * 4));
@@ -217,25 +247,96 @@ int bm_internal_index_prepare(bm_ctx* c, float d) {
     return BM_OK;
 }
 
-// Builds (or re-uses) the coarse k-mer table for query seed length k; sets c->use_ktable.  Not built when switched off
-// or when 4^k rows do not fit the memory budget: the mapper then gathers the k-q+1 q-gram rows per sample over the full
-// row width.  Both ways are CUDA paths with identical results.
-int bm_internal_kmer_table_prepare(bm_ctx* c, uint32_t k) {
+// Which coarse table, if any, pays off for this index and these parameters.  Bytes per read at the DRAM pins (128-B lines):
+//   coarse vote   2 S rows of ceil(NB / G / 8) bytes, whole lines
+//   recount       every group that passes the coarse vote costs S table words (S * (k-q+1) .qgram words without the fine
+//                 table), one line each; a group passes by chance when >= S-F+1 of the S samples hit one of its G buckets:
+//                 binomial tail with p = 1 - (1 - d)^G, d = measured density of the k-mer rows
+//   full gather   (no table, or a list with too many passing groups) the k-q+1 q-gram rows of every sample, about half of
+//                 them with the dead-tile exit when every q-gram is indexed
+// On the 1.7 Gbp / L=65536 / -f 1 reference d = 1.6 % and G = 16 wins (7.7 + 3 kB against 17 kB for G = 8, 86 kB for G = 32,
+// 166 kB for the gather); with L = 262144 / -k 10 d = 3.8 % and G = 8 wins; with -f 0.25 a third of all k-mers has no indexed
+// q-gram (d = 43 %): every coarse bit is set, every list would be handed over, and the gather alone is cheaper.
+static int kmer_table_choose(bm_ctx* c, const bm_params* p, uint32_t* logg_out) {
+    const uint32_t k = p->k, S = p->mapper_samples, F = p->mapper_fault, NQ = k - c->q + 1;
+    if (c->auto_k == k && c->auto_S == S && c->auto_F == F) { *logg_out = c->auto_logg; return BM_OK; }
+    BM_CK(c, c->d_stats.ensure(208 * 8));
+    unsigned long long* d_tot = c->d_stats.as<unsigned long long>() + 204;
+    BM_CK(c, cudaMemsetAsync(d_tot, 0, 8, c->stream));
+    const uint32_t n_samples = 4096;
+    {
+        KScope ks(c, BM_K_AUX);
+        k_kmer_density<<<n_samples, 128, 0, c->stream>>>(c->d_rows.as<uint4>(), c->Wp / 16, c->NB, c->d_k2i.as<int32_t>(), NQ,
+                                                         (1u << (2 * c->q)) - 1u, (k >= 16) ? 0xFFFFFFFFu : ((1u << (2 * k)) - 1u),
+                                                         d_tot);
+    }
+    BM_CK(c, cudaGetLastError());
+    unsigned long long tot = 0;
+    BM_CK(c, cudaMemcpyAsync(&tot, d_tot, 8, cudaMemcpyDeviceToHost, c->stream));
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    const double d = (double)tot / ((double)n_samples * (double)c->NB);
+    const double f_idx = (double)c->n_rows / (double)(1ull << (2 * c->q));
+    const double gather = 2.0 * S * NQ * f_idx * c->Wp * (f_idx > 0.9 ? 0.45 : 0.8);
+    const uint32_t need = (S >= F) ? S - F + 1 : 0;
+    auto tail = [&](double pr) {                      // P(Bin(S, pr) >= need)
+        double t = 0.0;
+        for (uint32_t h = need; h <= S; h++) {
+            double cmb = 1.0;
+            for (uint32_t i = 0; i < h; i++) cmb = cmb * (double)(S - i) / (double)(i + 1);
+            t += cmb * std::pow(pr, (double)h) * std::pow(1.0 - pr, (double)(S - h));
+        }
+        return t > 1.0 ? 1.0 : t;
+    };
+    const bool fine = c->ftable_mode != 0;
+    double best = gather;
+    uint32_t best_logg = 0xFF;
+    for (uint32_t logg = 3; logg <= 5 && need > 0; logg++) {
+        const double G = (double)(1u << logg);
+        const double groups = std::ceil((double)c->NB / G);
+        const double lines = std::ceil(std::ceil(groups / 8.0) / 128.0);
+        const double coarse = 2.0 * S * lines * 128.0;
+        const double pc = 1.0 - std::pow(1.0 - d, G);
+        const double passes = 2.0 * groups * tail(pc) + 1.0;
+        const double max_pass = std::max(16.0, groups / 8.0);
+        const double recount = passes * S * (fine ? 1.0 : NQ * f_idx) * 128.0;
+        const double cost = coarse + (passes > max_pass ? gather : std::min(recount, gather));
+        if (cost < best) { best = cost; best_logg = logg; }
+    }
+    c->auto_k = k; c->auto_S = S; c->auto_F = F; c->auto_logg = best_logg; c->auto_density = d;
+    *logg_out = best_logg;
+    return BM_OK;
+}
+
+// Builds (or re-uses) the k-mer tables for query seed length p->k; sets c->use_ktable / c->use_ftable.  Not built when
+// switched off, when 4^k rows do not fit the memory budget, or (mode 1) when the cost model above says that the full-width
+// gather is cheaper for this index: the mapper then gathers the k-q+1 q-gram rows per sample.  Both ways are CUDA paths
+// with identical results.
+int bm_internal_kmer_table_prepare(bm_ctx* c, const bm_params* p) {
+    const uint32_t k = p->k;
     c->use_ktable = false; c->use_ftable = false;
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "no index resident (bm_index_build / bm_index_load first)");
-    if (c->ktable_mode == 0 || k < c->q || k < 3 || k > 15 || c->n_rows == 0) {
+    if (c->ktable_mode == 0 || k < c->q || k < 3 || k > 15 || k - c->q + 1 > 8 || c->n_rows == 0) {
         if (c->ktable_mode == 0 && c->d_krows.p) { c->d_krows.release(); c->krows_k = 0; c->d_frows.release(); c->frows_k = 0; }
         return BM_OK;
     }
+    uint32_t want_logg = c->ktable_logg;
+    if (c->ktable_auto) {
+        int rc = kmer_table_choose(c, p, &want_logg);
+        if (rc) return rc;
+        if (want_logg == 0xFF) {                  // the gather is cheaper: no tables
+            if (c->d_krows.p) { c->d_krows.release(); c->krows_k = 0; c->d_frows.release(); c->frows_k = 0; }
+            return BM_OK;
+        }
+    }
     if (c->ftable_mode == 0 && c->d_frows.p) { c->d_frows.release(); c->frows_k = 0; }
     const bool fine_ok = c->ftable_mode == 0 || (c->frows_k == k && c->d_frows.p) || c->fine_tried_k == k;
-    if (c->krows_k == k && c->krows_logg == c->ktable_logg && c->d_krows.p && fine_ok) {
+    if (c->krows_k == k && c->krows_logg == want_logg && c->d_krows.p && fine_ok) {
         c->use_ktable = true; c->use_ftable = c->ftable_mode != 0 && c->frows_k == k && c->d_frows.p;
         return BM_OK;
     }
     const uint64_t n_kmers = 1ull << (2 * k);
     const uint32_t Wp32 = c->Wp / 4;
-    const uint32_t logg = c->ktable_logg;                          // buckets per coarse bit = 1 << logg
+    const uint32_t logg = want_logg;                               // buckets per coarse bit = 1 << logg
     c->Wc = ((Wp32 << (5 - logg)) + 31) / 32;
     c->Wcs = (c->Wc + 15u) & ~15u;
     const uint64_t bytes = (n_kmers + 1) * c->Wcs * 4;             // + one all-zero row (the fused mapper's padding samples)
@@ -285,6 +386,7 @@ int bm_index_kmer_table(bm_ctx* c, int mode, uint64_t max_bytes) {
     if (mode != 0 && mode != 1 && mode != 8 && mode != 16 && mode != 32)
         BM_FAIL(c, BM_E_ARG, "bm_index_kmer_table: mode must be 0 (off), 1 (when it fits) or a group size 8/16/32");
     c->ktable_logg = (mode == 8) ? 3 : (mode == 32) ? 5 : 4;
+    c->ktable_auto = mode == 1; c->auto_k = 0;
     c->ktable_mode = mode ? 1 : 0; c->ktable_max_bytes = max_bytes;
     if (mode == 0 || (max_bytes && c->d_krows.cap > max_bytes)) {
         cudaSetDevice(c->device);
@@ -297,7 +399,7 @@ int bm_index_kmer_table(bm_ctx* c, int mode, uint64_t max_bytes) {
 int bm_index_fine_table(bm_ctx* c, int mode) {
     if (!c) return BM_E_ARG;
     if (mode != 0 && mode != 1) BM_FAIL(c, BM_E_ARG, "bm_index_fine_table: mode must be 0 (off) or 1 (when it fits)");
-    c->ftable_mode = mode; c->fine_tried_k = 0;
+    c->ftable_mode = mode; c->fine_tried_k = 0; c->auto_k = 0;
     if (!mode) { cudaSetDevice(c->device); c->d_frows.release(); c->frows_k = 0; }
     return BM_OK;
 }
@@ -310,10 +412,18 @@ int bm_index_fine_table_info(bm_ctx* c, uint32_t* k, uint64_t* bytes) {
     return BM_OK;
 }
 
+int bm_index_kmer_table_choice(bm_ctx* c, uint32_t* buckets_per_bit, double* density) {
+    if (!c) return BM_E_ARG;
+    const bool on = c->d_krows.p && c->krows_k;
+    if (buckets_per_bit) *buckets_per_bit = on ? (1u << c->krows_logg) : 0u;
+    if (density) *density = c->auto_k ? c->auto_density : 0.0;
+    return BM_OK;
+}
+
 int bm_index_kmer_table_info(bm_ctx* c, uint32_t* k, uint64_t* bytes) {
     if (!c) return BM_E_ARG;
     if (k) *k = (c->d_krows.p ? c->krows_k : 0);
-    if (bytes) *bytes = (c->d_krows.p && c->krows_k) ? ((1ull << (2 * c->krows_k)) * c->Wcs * 4) : 0;
+    if (bytes) *bytes = (c->d_krows.p && c->krows_k) ? (((1ull << (2 * c->krows_k)) + 1) * c->Wcs * 4) : 0;
     return BM_OK;
 }
 
@@ -407,7 +517,7 @@ int bm_index_alloc(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, u
 int bm_index_device(bm_ctx* c, void** dptr, uint64_t* bytes) {
     if (!c) return BM_E_ARG;
     if (!c->have_index) BM_FAIL(c, BM_E_ARG, "bm_index_device: no index resident");
-    c->zeros_for_d = -1.f; c->krows_k = 0; c->frows_k = 0; c->fine_tried_k = 0;   // the caller may overwrite the rows: recompute on next use
+    c->zeros_for_d = -1.f; c->krows_k = 0; c->frows_k = 0; c->fine_tried_k = 0; c->auto_k = 0;   // the caller may overwrite the rows: recompute on next use
     if (dptr) *dptr = c->d_rows.p;
     if (bytes) *bytes = (uint64_t)c->n_rows * c->Wp;
     return BM_OK;

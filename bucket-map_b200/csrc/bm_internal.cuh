@@ -88,6 +88,11 @@ struct bm_ctx {
     uint32_t krows_k = 0, Wc = 0, Wcs = 0;   // coarse words in use per row / row stride in words (64-B multiple)
     uint32_t ktable_logg = 4, krows_logg = 0;   // log2 of the buckets per coarse bit: wanted / of the resident table
     int ktable_mode = 1;          // 0 never, 1 when it fits (bm_index_kmer_table)
+    // mode 1 chooses the buckets per coarse bit (8 / 16 / 32) -- or no table at all -- from a cost model fed with the measured
+    // density of the k-mer rows (bm_index.cu: kmer_table_choose); modes 8 / 16 / 32 force a group size
+    bool ktable_auto = true;
+    uint32_t auto_k = 0, auto_S = 0, auto_F = 0, auto_logg = 4;   // the decision and what it was made for (auto_logg 0xFF: no table)
+    double auto_density = 0.0;
     uint64_t ktable_max_bytes = 0;   // 0: half of the free device memory at build time
     bool use_ktable = false;      // decided by bm_internal_kmer_table_prepare for the current mapper call
     // locator samples written by the fused mapper kernel for the resident batch (0: none; else the (k, P, b) they
@@ -205,7 +210,7 @@ struct KScope {
 
 int bm_internal_gather_fence(bm_ctx* c);                       // bm_comm.cu: a gather copy still reads the result buffers
 int bm_internal_index_prepare(bm_ctx* ctx, float d);          // K0: zeros + distok bitmap for threshold d
-int bm_internal_kmer_table_prepare(bm_ctx* ctx, uint32_t k);  // K0b: k-mer row table for query seed length k (if it fits)
+int bm_internal_kmer_table_prepare(bm_ctx* ctx, const bm_params* p);  // K0b: k-mer tables for p->k (if they fit and pay off)
 int bm_internal_gidx_prepare(bm_ctx* ctx, uint32_t k);        // genome k-mer position index for seed length k (if it fits)
 int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* over_list, uint32_t* d_n_over, uint32_t* n_over);
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);

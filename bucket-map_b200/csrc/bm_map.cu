@@ -373,7 +373,7 @@ int bm_prepare(bm_ctx* c, const bm_params* p) {
     cudaSetDevice(c->device);
     int r = bm_internal_index_prepare(c, p->distinguishability);
     if (r) return r;
-    if (p->k >= p->q && p->k <= 16) { r = bm_internal_kmer_table_prepare(c, p->k); if (r) return r; }   // builds the locator index first
+    if (p->k >= p->q && p->k <= 16) { r = bm_internal_kmer_table_prepare(c, p); if (r) return r; }   // builds the locator index first
     if (c->d_packed.p) { r = bm_internal_gidx_prepare(c, p->k); if (r) return r; }
     BM_CK(c, cudaStreamSynchronize(c->stream));
     return BM_OK;
@@ -420,7 +420,7 @@ int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uin
     c->have_map = false; c->have_locs = false; c->have_aln = false;
     int r = bm_internal_index_prepare(c, p->distinguishability);
     if (r) return r;
-    r = bm_internal_kmer_table_prepare(c, p->k);          // decides c->use_ktable for this call
+    r = bm_internal_kmer_table_prepare(c, p);             // decides c->use_ktable for this call
     if (r) return r;
     const size_t n_lists = 2 * (size_t)n_seg_cap;
     BM_CK(c, c->d_rowidx.ensure(n_lists * S * NQ * 4 + 16));

@@ -56,7 +56,7 @@ void lane_share_index(bm_ctx* l, bm_ctx* c) {
     l->q = c->q; l->n_rows = c->n_rows; l->W = c->W; l->Wp = c->Wp; l->have_index = c->have_index;
     l->zeros_for_d = c->zeros_for_d; l->dist_threshold = c->dist_threshold; l->dist_valid = c->dist_valid;
     l->d_krows.view_of(c->d_krows); l->krows_k = c->krows_k; l->Wc = c->Wc; l->Wcs = c->Wcs;
-    l->ktable_logg = c->ktable_logg; l->krows_logg = c->krows_logg;
+    l->ktable_logg = c->krows_logg; l->krows_logg = c->krows_logg; l->ktable_auto = false;   // the lane takes the parent's table as it is
     l->d_frows.view_of(c->d_frows); l->frows_k = c->frows_k; l->fine_tried_k = c->fine_tried_k;
     l->ftable_mode = (c->d_frows.p && c->frows_k) ? 1 : 0;
     l->ktable_mode = c->d_krows.p ? 1 : 0;          // never build in the lane: use the parent's table or none
@@ -304,7 +304,7 @@ extern "C" int bm_map_locate(bm_ctx* c, const bm_params* p, const uint8_t* seq, 
     // derived tables are built once, by the parent, before the lanes start (the child only ever views them)
     int r = bm_internal_index_prepare(c, p->distinguishability);
     if (r) return r;
-    if (p->k >= p->q && p->k <= 16) { r = bm_internal_kmer_table_prepare(c, p->k); if (r) return r; }
+    if (p->k >= p->q && p->k <= 16) { r = bm_internal_kmer_table_prepare(c, p); if (r) return r; }
     r = bm_internal_gidx_prepare(c, p->k);
     if (r) return r;
     BM_CK(c, cudaStreamSynchronize(c->stream));

@@ -114,7 +114,7 @@ int bm_index_zeros(bm_ctx* ctx, float distinguishability, uint32_t* zeros_out /*
  * bucket with < F misses lies in a group with < F coarse misses) and recounts the few passing groups exactly from the
  * .qgram matrix.  The table is derived from the resident matrix at the first mapper call for a given k; index files are
  * unchanged and results are identical.  mode 1 (default): build it when it fits in max_bytes (0 = half of the free
- * device memory), G=16; mode 8/16/32: the same with that G; mode 0: never (the mapper gathers the k-q+1 q-gram rows of
+ * device memory) and pays off, G chosen by a cost model from the measured row density; mode 8/16/32: that G, always; mode 0: never (the mapper gathers the k-q+1 q-gram rows of
  * every sample over the full row width). */
 int bm_index_kmer_table(bm_ctx* ctx, int mode, uint64_t max_bytes);
 /* With the coarse table the mapper recounts exactly every group of buckets that passes the coarse vote.  A read made of
@@ -124,6 +124,11 @@ int bm_index_kmer_table(bm_ctx* ctx, int mode, uint64_t max_bytes);
 int bm_map_handover(bm_ctx* ctx, int max_groups);
 /* k the resident table was built for (0: none) and its size */
 int bm_index_kmer_table_info(bm_ctx* ctx, uint32_t* k, uint64_t* bytes);
+/* What mode 1 decided at the last mapper call: *buckets_per_bit = 8 / 16 / 32 of the resident coarse table, or 0 when no
+ * table is in use (switched off, does not fit, or the cost model found the full-width gather cheaper for this index: e.g. a
+ * FracMinHash-sparse index, where a third of all k-mers has no indexed q-gram and every coarse bit would be set);
+ * *density = measured share of set bits in the k-mer rows that fed the decision (0 if none was made). */
+int bm_index_kmer_table_choice(bm_ctx* ctx, uint32_t* buckets_per_bit, double* density);
 /* full-resolution k-mer table (no reference counterpart): the same precomputed AND, one bit per BUCKET, 4^k rows of
  * roundup(W,64) bytes (54.8 GB on the 1.7 Gbp reference).  With it the exact recount of a passing group reads ONE 32-bit
  * word per sample instead of the k-q+1 scattered .qgram words (each of which costs a 128-B DRAM line).  Built together

@@ -51,7 +51,7 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     d = dataset(**kw)
     handover = {-1: 0, -2: 1}.get(ktable, -1)
     fine = 0 if ktable == -3 else 1
-    ktable = 1 if ktable < 0 else ktable
+    ktable = 16 if ktable < 0 else ktable     # the hand-over / fine-table variants run on a forced table (1 = the cost model's choice)
     ctx.index_fine_table(fine)
     ctx.index_kmer_table(ktable)
     ctx.map_handover(handover)
@@ -72,11 +72,18 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     assert stats[0] > 0.9 * len(segs[0]) or kw.get("read_len") == 800
     tk, tbytes = ctx.index_kmer_table_info()
     fk, fbytes = ctx.index_fine_table_info()
-    assert (fk, fbytes) == ((P.k, 4 ** P.k * ((((d.NB + 7) >> 3) + 63) & ~63)) if (ktable and fine) else (0, 0))
+    chosen, density = ctx.index_kmer_table_choice()
+    if ktable == 1:                               # mode 1: 8 / 16 / 32 buckets per coarse bit, or no table when the gather is cheaper
+        assert chosen in (0, 8, 16, 32) and 0.0 < density <= 1.0
+        if kw.get("frac", 1.0) < 0.5:
+            assert chosen == 0                    # FracMinHash-sparse index: every coarse bit would be set
+    else:
+        assert chosen == ktable
+    have = chosen != 0
+    assert (fk, fbytes) == ((P.k, 4 ** P.k * ((((d.NB + 7) >> 3) + 63) & ~63)) if (have and fine) else (0, 0))
     ctx.index_fine_table(1)
     ctx.index_kmer_table(1)   # session-wide context: back to the default for the tests that follow
     ctx.map_handover(-1)
     wp = (((d.NB + 7) >> 3) + 63) & ~63                       # padded row bytes
-    group = 16 if ktable == 1 else ktable                      # buckets per coarse bit (default 16)
-    wcs = ((wp * 8 // max(group, 1) + 31) // 32 + 15) & ~15    # coarse row stride in 32-bit words
-    assert (tk, tbytes) == ((P.k, 4 ** P.k * wcs * 4) if ktable else (0, 0))
+    wcs = ((wp * 8 // max(chosen, 1) + 31) // 32 + 15) & ~15   # coarse row stride in 32-bit words
+    assert (tk, tbytes) == ((P.k, (4 ** P.k + 1) * wcs * 4) if have else (0, 0))   # + the all-zero padding row
