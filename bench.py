@@ -547,6 +547,8 @@ def main():
             ctx.gather_results()
             return 0
 
+        if world > 1 and rank == 0:
+            ctx.gather_host_async(True)          # the gathered records reach rank 0's host under the next step
         for _ in range(max(1, min(a.warmup, 3))):
             step_e2e()
         barrier()

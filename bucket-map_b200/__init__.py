@@ -96,6 +96,7 @@ SIGNATURES = {
     "bm_gather_connect": (C.c_int, [_vp, _vp]),
     "bm_gather_results": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "bm_gather_sync": (C.c_int, [_vp]),
+    "bm_gather_host_async": (C.c_int, [_vp, C.c_int]),
     "bm_gather_join": (C.c_int, [_vp]),
     "bm_gather_device_buffers": (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(C.c_uint64),
                                            C.POINTER(C.c_uint64)]),
@@ -427,6 +428,9 @@ class Context:
 
     def gather_sync(self):
         self._ck(self.lib.bm_gather_sync(self.h), "bm_gather_sync")
+
+    def gather_host_async(self, on):
+        self._ck(self.lib.bm_gather_host_async(self.h, int(on)), "bm_gather_host_async")
 
     def gather_join(self):
         self._ck(self.lib.bm_gather_join(self.h), "bm_gather_join")

@@ -116,6 +116,7 @@ struct bm_gather {
     cudaStream_t gstream = nullptr;                 // root: waits + pack; every rank: the copies into the root's slots
     cudaEvent_t ev_ready = nullptr, ev_copied = nullptr;
     bool copy_pending = false;
+    bool host_async = false;                        // root: host copies of the packed records are not waited for in the call
     // local block: root = [kSlotSets][nranks] slots + flags; every rank = ack word (first 256 bytes of its block)
     DevBuf block;
     uint8_t* root_base = nullptr;                   // root's block as seen from this rank (peer mapping or own pointer)
@@ -497,7 +498,17 @@ int bm_gather_results(bm_ctx* c, uint32_t* loc_off, bm_loc* locs, uint64_t loc_c
         if (tot[1] > loc_cap) BM_FAIL(c, BM_E_ARG, "bm_gather_results: location buffer too small");
         BM_CK(c, cudaMemcpyAsync(locs, g->r_locs.p, (size_t)tot[1] * sizeof(bm_loc), cudaMemcpyDeviceToHost, g->gstream));
     }
-    BM_CK(c, cudaStreamSynchronize(g->gstream));
+    if (!g->host_async) BM_CK(c, cudaStreamSynchronize(g->gstream));   // else: complete after bm_gather_sync / the next call
+    return BM_OK;
+}
+
+// Root: with on != 0 a bm_gather_results call with host pointers returns as soon as the totals are known and leaves the
+// copy of the packed records to the gather stream (it then runs under the next batch's host->device copy and mapper); the
+// host arrays are complete after bm_gather_sync or the next bm_gather_results.  Default 0: the call returns with the data.
+int bm_gather_host_async(bm_ctx* c, int on) {
+    if (!c) return BM_E_ARG;
+    if (!c->gather) BM_FAIL(c, BM_E_ARG, "bm_gather_host_async: bm_gather_open first");
+    c->gather->host_async = on != 0;
     return BM_OK;
 }
 

@@ -256,6 +256,9 @@ int bm_gather_connect(bm_ctx* ctx, const uint8_t* handles);
 int bm_gather_results(bm_ctx* ctx, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* n_reads_total,
                       uint64_t* n_locs_total);
 int bm_gather_sync(bm_ctx* ctx);
+/* root: on != 0 -- a bm_gather_results call with host pointers returns once the totals are known; the arrays are complete
+ * after bm_gather_sync or the next bm_gather_results (the copy runs under the next batch).  Default 0. */
+int bm_gather_host_async(bm_ctx* ctx, int on);
 int bm_gather_join(bm_ctx* ctx);
 int bm_gather_device_buffers(bm_ctx* ctx, void** loc_off, void** locs, uint64_t* n_reads, uint64_t* n_locs);
 int bm_gather_download(bm_ctx* ctx, uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* n_reads, uint64_t* n_locs);
