@@ -50,6 +50,10 @@ CONFIGS = {
     "c2r": dict(n_bases=1_700_000_000, gseed=3, L=65536, q=9, read_len=300, rseed=4, sub=0.002, indel=0.00025, reads=1_000_000,
                 repeats=(10_000, 8_500),
                 desc="C2': the 1.7 Gbp reference with 5% of it overwritten by 8,500 duplicated 10 kbp segments, 300bp reads"),
+    "c2x": dict(n_bases=1_700_000_000, gseed=3, L=65536, q=9, read_len=300, rseed=4, sub=0.002, indel=0.00025, reads=1_000_000,
+                family=(1_000, 34_000, 0.03),
+                desc="repeat-family stress: the 1.7 Gbp reference with 2% of it = 34,000 copies of one 1 kbp element (3% "
+                     "divergence, a copy in almost every bucket), 300bp reads"),
     "c3": dict(n_bases=3_100_000_000, gseed=5, L=65536, q=9, read_len=150, rseed=6, sub=0.002, indel=0.00025, reads=10_000_000,
                strong=True, desc="3.1 Gbp synthetic reference, L=65536, 10M x 150bp reads sharded over the GPUs"),
     "c4-16384": dict(n_bases=1_700_000_000, gseed=3, L=16384, q=9, read_len=300, rseed=4, sub=0.002, indel=0.00025,
@@ -145,6 +149,9 @@ def make_workload(cfg):
     if cfg.get("repeats"):
         seg, copies = cfg["repeats"]
         packed = datagen.add_repeats_packed(packed, cfg["n_bases"], seg, copies, cfg["gseed"] + 100)
+    if cfg.get("family"):
+        unit, copies, div = cfg["family"]
+        packed = datagen.add_family_packed(packed, cfg["n_bases"], unit, copies, div, cfg["gseed"] + 200)
     NB, b_start, b_len, _ = datagen.bucketize(np.array([cfg["n_bases"]], np.uint64), cfg["L"], 300)
     return packed, NB, b_start, b_len
 
@@ -602,7 +609,7 @@ def main():
     peak, peak_src = measured_peak()
     vote_ms, vote_n = kst["map_vote"]
     alt = None
-    if ktable_k and rank == 0 and world == 1 and not align and a.config in ("c2", "c2r"):
+    if ktable_k and rank == 0 and world == 1 and not align and a.config in ("c2", "c2r", "c2x"):
         # the full-width q-gram gather (k_map_vote) on the same batch, outside the timed region: the mapper when the
         # tables are off / do not fit, and the kernel the HBM roofline target of BASELINE.json was written for
         ctx.index_kmer_table(0)

@@ -196,3 +196,26 @@ def add_repeats_packed(packed, n_bases, seg_len, n_copies, seed):
     for a, b in zip(src.tolist(), dst.tolist()):
         out[b:b + nb] = out[a:a + nb]
     return out
+
+
+def add_family_packed(packed, n_bases, unit_len, n_copies, divergence, seed):
+    """a high-copy repeat family (Alu-like): n_copies copies of ONE random element of unit_len bases, each with its own
+    substitutions (rate `divergence`), written at random 4-base-aligned positions.  Reads that fall inside a copy share
+    their k-mers with copies in almost every bucket: the mapper's worst case (coarse vote passes everywhere, the list goes
+    to the full-width gather and comes back longer than 30 buckets, i.e. empty, in the reference as here)."""
+    rng = np.random.default_rng(seed)
+    out = packed.copy()
+    unit_len -= unit_len % 4
+    unit = rng.integers(0, 4, unit_len).astype(np.uint8)
+    pos = rng.integers(0, (n_bases - unit_len) // 4, n_copies)
+    chunk = 4096
+    for c0 in range(0, n_copies, chunk):
+        c1 = min(c0 + chunk, n_copies)
+        copies = np.broadcast_to(unit, (c1 - c0, unit_len)).copy()
+        mut = rng.random(copies.shape) < divergence
+        copies[mut] = (copies[mut] + rng.integers(1, 4, int(mut.sum())).astype(np.uint8)) & 3
+        r = copies.reshape(c1 - c0, unit_len // 4, 4)
+        by = (r[:, :, 0] | (r[:, :, 1] << 2) | (r[:, :, 2] << 4) | (r[:, :, 3] << 6)).astype(np.uint8)
+        for i, p in enumerate(pos[c0:c1].tolist()):
+            out[p:p + unit_len // 4] = by[i]
+    return out

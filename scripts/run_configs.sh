@@ -19,6 +19,7 @@ for c in $cfgs; do
   case $c in
     c2f025) run c2_f025 --config c2 --frac 0.25 --steps 10 --warmup 3 ;;
     c2r) run c2r --config c2r --steps 10 --warmup 3 --no-cpu ;;
+    c2x) run c2x --config c2x --steps 10 --warmup 3 --no-cpu ;;
     c5) run c5 --config c5 --steps 5 --warmup 2 ;;
     c1) run c1 --config c1 --frac 0.25 --steps 20 --warmup 3 ;;
     c3) run c3 --config c3 --steps 3 --warmup 2 --no-cpu ;;
