@@ -1,6 +1,6 @@
 # Builds the product library (CUDA, sm_100a), the host tools and the test-only CPU oracle.
 #   make lib      -> bucket-map_b200/libbucketmap_b200.so   (C-ABI of include/bucketmap_b200.h)
-#   make tools    -> bucket-map_b200/bin/bucketmap, bucketmap_align   (C++ host over the C-ABI)
+#   make tools    -> bucket-map_b200/bin/bucketmap, bucketmap_align   (C++ host over the C-ABI), bucketmap_analyze
 #   make oracle   -> oracle/libbm_oracle.so                 (test infrastructure only)
 #   make ref      -> oracle/_ref/...                        (reference headers built against oracle/shim; needs /root/reference)
 NVCC      ?= nvcc
@@ -34,7 +34,12 @@ oracle/libbm_oracle.so: oracle/bm_oracle.cpp oracle/bm_oracle.h
 HOST_SRCS := $(wildcard $(PKG)/host/*.cpp)
 HOST_HDRS := $(wildcard $(PKG)/host/*.hpp) include/bucketmap_b200.h
 
-tools: $(PKG)/bin/bucketmap $(PKG)/bin/bucketmap_align
+tools: $(PKG)/bin/bucketmap $(PKG)/bin/bucketmap_align $(PKG)/bin/bucketmap_analyze
+
+# accuracy metrics of a SAM file against a ground truth (host-only evaluation tool)
+$(PKG)/bin/bucketmap_analyze: $(PKG)/tools/sam_analyze.cpp
+	@mkdir -p $(PKG)/bin
+	$(CXX) -O2 -std=c++17 -Wall -o $@ $<
 
 $(PKG)/bin/bucketmap: $(HOST_SRCS) $(HOST_HDRS) $(LIB)
 	@mkdir -p $(PKG)/bin

@@ -162,6 +162,26 @@ def simulate(cfg, packed, n_reads, seed, n_span=None):
                                   cfg["indel"], cfg["indel"], seed)[:3]
 
 
+def accuracy(loff, locs, L, start, rev, tolerance=10):
+    """the analyzer's metrics (benchmark/sam_file_analyzer.cpp:250-358, tolerance 10 as its main() sets) of one batch's
+    location records against the simulator's ground truth; one reference sequence, so position = bucket * L + offset"""
+    cnt = np.diff(loff.astype(np.int64))
+    read_of = np.repeat(np.arange(len(cnt)), cnt)
+    pos = locs["bucket"].astype(np.int64) * L + locs["offset"]
+    good = (np.abs(pos - start[read_of]) <= tolerance) & ((locs["is_original"] == 0) == rev[read_of])
+    correct = np.zeros(len(cnt), bool)
+    correct[read_of[good]] = True
+    single = cnt <= 1                     # the analyzer's per-read counts leave out reads with several records
+    n = len(cnt)
+    return {"reads": int(n), "mapped_pct": 100.0 * int(((cnt > 0) & single).sum()) / n,
+            "correct_pct": 100.0 * int((correct & single).sum()) / n,
+            "reads_with_several_locations": int((~single).sum()),
+            "correct_incl_several_pct": 100.0 * int(correct.sum()) / n,
+            "locations": int(len(locs)), "precision_pct": 100.0 * int(good.sum()) / max(1, len(locs)),
+            "tolerance": tolerance, "definition": "benchmark/sam_file_analyzer.cpp:250-358 on the records of one step "
+                                                  "against the read simulator's origin and strand"}
+
+
 def bind_to_gpu_numa_node(device):
     """run this rank (and first-touch its pinned buffers) on the CPUs next to its GPU: on a two-socket box a rank that
     lands on the far socket pushes every host<->device byte across the socket link"""
@@ -448,7 +468,9 @@ def main():
     W = (NB + 7) >> 3
 
     # ---- reads of this rank (its contiguous shard of the job's reads), in both host forms
-    seq, qual, off = simulate(cfg, packed, n_reads_cfg, cfg["rseed"] + rank)
+    from bucketmap_b200 import datagen
+    seq, qual, off, truth_start, truth_rev = datagen.simulate_reads(packed, cfg["n_bases"], n_reads_cfg, cfg["read_len"], cfg["sub"],
+                                                                    cfg["indel"], cfg["indel"], cfg["rseed"] + rank)
     n_reads = len(off) - 1
     planes, qk, pl_off, n_low = bm.pack_reads(ctx.lib, seq, qual, off, P.k, P.avg_base_quality)
     setup_s = time.perf_counter() - t0
@@ -519,9 +541,9 @@ def main():
     clk = clocks.stop()
     kst = ctx.kernel_stats()
     _, _, mstats = ctx.map_download()
-    n_aln = 0
-    if align:
-        n_aln = len(ctx.locate_download()[1])
+    res_off, res_locs = ctx.locate_download()
+    n_aln = len(res_locs) if align else 0
+    acc = accuracy(res_off, res_locs, L, truth_start, truth_rev) if rank == 0 else None
     tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -705,6 +727,7 @@ def main():
                    "lists_handed_to_full_width_gather": int(mstats[5]), "coarse_groups_recounted_per_read": int(mstats[6]) / max(1, n_reads),
                    "locator_candidates_to_bucket_scan": int(mstats[7])},
     }
+    out["accuracy"] = acc
     if world > 1:
         out["gather_verified"] = gather_verified
         out["gather"] = "bm_gather_results: peer-memory stores over NVLink into rank 0's slots + cuStreamWaitValue32 + pack kernel"

@@ -219,3 +219,20 @@ def add_family_packed(packed, n_bases, unit_len, n_copies, divergence, seed):
         for i, p in enumerate(pos[c0:c1].tolist()):
             out[p:p + unit_len // 4] = by[i]
     return out
+
+
+def write_ground_truth(path, starts, rev, rec_len=None):
+    """the simulator's `.position_ground_truth` (tools/short_read_simulator.h:237-240): one line per read,
+    `<record index> <1-based position inside the record> <reverse complement 0|1> <cigar>`; this generator keeps no
+    CIGAR of its edits, the column (never read by the analyzer, sam_file_analyzer.cpp:141) is written as `*`."""
+    starts = np.asarray(starts, np.int64)
+    if rec_len is None:
+        rec = np.zeros(len(starts), np.int64)
+        pos = starts
+    else:
+        bounds = np.concatenate([[0], np.cumsum(np.asarray(rec_len, np.int64))])
+        rec = np.searchsorted(bounds, starts, side="right") - 1
+        pos = starts - bounds[rec]
+    with open(path, "w") as f:
+        f.write("".join("%d %d %d *\n" % (r, p + 1, v) for r, p, v in zip(rec.tolist(), pos.tolist(),
+                                                                         np.asarray(rev, bool).astype(int).tolist())))
