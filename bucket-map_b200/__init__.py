@@ -297,7 +297,9 @@ class Context:
         self.n_seg = n.value
 
     def segments(self):
-        n = self.n_seg
+        nq = C.c_uint32()
+        self._ck(self.lib.bm_reads_segments(self.h, C.byref(nq), None, None, None), "bm_reads_segments")
+        n = self.n_seg = nq.value               # the host-buffer entry points (bm_map_locate*) leave a batch resident too
         a, b, c = (np.empty(n, np.uint32) for _ in range(3))
         nn = C.c_uint32()
         self._ck(self.lib.bm_reads_segments(self.h, C.byref(nn), _ptr(a), _ptr(b), _ptr(c)), "bm_reads_segments")

@@ -134,7 +134,10 @@ static void sample_det(uint32_t n, uint32_t ub, std::vector<uint32_t>& out) {
 
 // Sizes the host tables and the device buffers of a batch of n_reads reads (n_seg is bounded by
 // n_reads * num_segment_samples) and resets the per-batch state; the tables are filled by bm_internal_build_segments.
-int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads, const uint32_t* pl_off) {
+// lazy (packed batches only): the pass over the reads is left to bm_internal_build_unit_range(scan = true), chunk by chunk,
+// under the assumption that no read is longer than 2r; the caller starts over without `lazy` when a chunk says otherwise.
+int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads, const uint32_t* pl_off,
+                            bool lazy) {
     if (p->read_len == 0 || p->num_segment_samples == 0) BM_FAIL(c, BM_E_ARG, "bm_reads_upload: bad parameters");
     c->have_reads = false; c->have_map = false; c->have_locs = false; c->have_aln = false;
     c->lsamp_k = c->lsamp_P = c->lsamp_b = 0;
@@ -144,7 +147,8 @@ int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_
     // exact segment count: reads longer than 2r are cut into num_segment_samples segments (one cheap pass)
     uint64_t n_long = 0, n_chunks = 0, max_len = 0;
     const uint64_t two_r = 2ull * p->read_len;
-    for (uint32_t i = 0; i < n_reads; i++) {               // one pass: long reads, chunks of the packed form, longest read
+    if (lazy && pl_off) n_chunks = (uint64_t)pl_off[n_reads] - pl_off[0];
+    else for (uint32_t i = 0; i < n_reads; i++) {          // one pass: long reads, chunks of the packed form, longest read
         const uint64_t len = read_off[i + 1] - read_off[i];
         n_long += len > two_r;
         n_chunks += (len + 31) / 32;
@@ -185,8 +189,24 @@ int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_
 // Reads [r0, r1) of a batch WITHOUT long reads (one segment per read, segment index == read index): only the offset
 // tables are made on the host -- copied from the caller's arrays where those can be used as they are -- and the segment
 // tables are written on the device (k_unit_segments).  pl_off: the caller's chunk offsets (packed batches) or nullptr.
+// scan: the checks bm_internal_reads_begin(lazy) left out, for these reads; returns 1 when one of them is longer than 2r.
 int bm_internal_build_unit_range(bm_ctx* c, const bm_params* p, const uint64_t* read_off, const uint32_t* pl_off,
-                                 uint32_t r0, uint32_t r1) {
+                                 uint32_t r0, uint32_t r1, bool scan) {
+    if (scan) {
+        const uint64_t two_r = 2ull * p->read_len;
+        uint64_t max_len = c->batch_max_len, bad = 0;
+        for (uint32_t i = r0; i < r1; i++) {
+            const uint64_t len = read_off[i + 1] - read_off[i];          // a decreasing offset wraps to a huge length
+            max_len = len > max_len ? len : max_len;
+            bad |= (uint64_t)(pl_off[i + 1] - pl_off[i]) ^ ((len + 31) / 32);
+        }
+        if (max_len > two_r) {
+            if (max_len > 0x7FFFFFFFull) BM_FAIL(c, BM_E_LIMIT, "bm_reads_upload: read longer than 2^31 (or read_off not monotone)");
+            return 1;
+        }
+        if (bad) BM_FAIL(c, BM_E_ARG, "packed batch: pl_off is not the layout of bm_pack_layout");
+        c->batch_max_len = (uint32_t)max_len;
+    }
     uint64_t* off_rel = c->h_off_rel.as<uint64_t>();
     uint32_t* hpl = c->h_pl_off.as<uint32_t>();
     const uint64_t base = read_off[0];

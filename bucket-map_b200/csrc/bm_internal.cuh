@@ -216,13 +216,15 @@ int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* 
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
 int bm_internal_h2d(bm_ctx* c, void* dst, const void* src, size_t bytes);   // large copy from possibly pageable memory
 // reads: size the batch buffers (host tables + device), then append the segment table of reads [r0, r1)
-int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads, const uint32_t* pl_off);
+int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads, const uint32_t* pl_off,
+                            bool lazy = false);
 // k_pack_reads over reads [r0, r1) of the resident ASCII batch (d_seq, d_qual, d_read_off, d_pl_off) on c->stream
 int bm_internal_pack_range(bm_ctx* c, const bm_params* p, uint32_t r0, uint32_t r1);
 // makes sure the quality plane of the resident batch matches (k, b) of this call (re-packs an ASCII batch if not)
 int bm_internal_pack_check(bm_ctx* c, const bm_params* p);
 int bm_internal_build_segments(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t r0, uint32_t r1);
-int bm_internal_build_unit_range(bm_ctx* c, const bm_params* p, const uint64_t* read_off, const uint32_t* pl_off, uint32_t r0, uint32_t r1);
+int bm_internal_build_unit_range(bm_ctx* c, const bm_params* p, const uint64_t* read_off, const uint32_t* pl_off, uint32_t r0, uint32_t r1,
+                                 bool scan = false);
 // mapper in three steps so that K2a/K2 can run on a segment range as soon as its bytes are resident
 int bm_internal_map_begin(bm_ctx* c, const bm_params* p, uint32_t n_seg_cap, uint32_t max_seg_len);
 int bm_internal_map_range(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t seg1, uint32_t max_seg_len);

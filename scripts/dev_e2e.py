@@ -1,11 +1,12 @@
-"""dev: phases of bm_map_locate_packed on C2 ($BM_PIPE_TRACE=1 prints them per call).  usage: python scripts/dev_e2e.py"""
+"""dev: phases of bm_map_locate_packed on C2 ($BM_PIPE_TRACE=1 prints them per call).  usage: python scripts/dev_e2e.py [--plain]"""
 import os
 import sys
 import time
 
 import numpy as np
 
-os.environ["BM_PIPE_TRACE"] = "1"
+if "--plain" not in sys.argv:
+    os.environ["BM_PIPE_TRACE"] = "1"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bucketmap_b200 as bm
@@ -27,7 +28,7 @@ hplo = ctx.pinned(len(pl_off), np.uint32); hplo[:] = pl_off
 hoff = ctx.pinned(len(off), np.uint64); hoff[:] = off
 ooff = ctx.pinned(n_reads + 1, np.uint32)
 olocs = ctx.pinned(4 * n_reads, bm.LOC_DTYPE)
-for i in range(6):
+for i in range(10 if "--plain" in sys.argv else 6):
     t = time.perf_counter()
     ctx.map_locate_packed_into(P, hpl, None, hplo, hoff, ooff, olocs, True)
     print("call %d: %.2f ms" % (i, (time.perf_counter() - t) * 1e3), flush=True)

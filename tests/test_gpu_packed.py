@@ -125,3 +125,41 @@ def test_quality_plane_follows_the_parameters(oracle, bm, ctx):
     P3 = bm.default_params(ctx.lib, d.L, b=40)
     with pytest.raises(bm.BucketMapError):
         ctx.map_device(P3)
+
+
+def test_pipelined_packed_call_with_a_long_read_in_a_late_chunk(oracle, bm, ctx):
+    """bm_map_locate_packed scans the read offsets chunk by chunk assuming one segment per read; a read longer than 2r found
+    in a later chunk makes the call start over with the general segment tables.  Same records as the ASCII call."""
+    d = dataset(read_len=150, n_reads=70_000, n_bases=3_000_000)
+    _setup(oracle, ctx, d)
+    P = bm.default_params(ctx.lib, d.L)
+    # reads 60000..60004 become one 750-base read (> 2r = 600): five segments
+    read_off = np.delete(d.read_off, [60001, 60002, 60003, 60004])
+    n = len(read_off) - 1
+    assert int(read_off[60001] - read_off[60000]) == 750
+    off_a, locs_a, st_a = ctx.map_locate(P, d.seq, d.qual, read_off, True)
+    planes, qk, pl_off, low = bm.pack_reads(ctx.lib, d.seq, d.qual, read_off, P.k, P.avg_base_quality)
+    off_b = np.empty(n + 1, np.uint32)
+    locs_b = np.empty(len(locs_a) + 16, bm.LOC_DTYPE)
+    nl, st_b = ctx.map_locate_packed_into(P, planes, qk if low else None, pl_off, read_off, off_b, locs_b, True)
+    assert nl == len(locs_a)
+    assert np.array_equal(off_a, off_b) and np.array_equal(locs_a, locs_b[:nl])
+    assert np.array_equal(st_a[:4], st_b[:4])
+    assert len(ctx.segments()[0]) == n + 4
+
+
+def test_pipelined_packed_call_rejects_a_bad_layout_in_a_late_chunk(oracle, bm, ctx):
+    d = dataset(read_len=150, n_reads=70_000, n_bases=3_000_000)
+    _setup(oracle, ctx, d)
+    P = bm.default_params(ctx.lib, d.L)
+    planes, qk, pl_off, low = bm.pack_reads(ctx.lib, d.seq, d.qual, d.read_off, P.k, P.avg_base_quality)
+    n = len(d.read_off) - 1
+    bad = pl_off.copy()
+    bad[65_000] += 1
+    off_b = np.empty(n + 1, np.uint32)
+    locs_b = np.empty(4 * n, bm.LOC_DTYPE)
+    with pytest.raises(bm.BucketMapError, match="pl_off"):
+        ctx.map_locate_packed_into(P, planes, None, bad, d.read_off, off_b, locs_b, True)
+    # the context is usable afterwards
+    nl, _ = ctx.map_locate_packed_into(P, planes, None, pl_off, d.read_off, off_b, locs_b, True)
+    assert nl > 0.9 * n
