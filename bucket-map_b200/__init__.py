@@ -84,6 +84,7 @@ SIGNATURES = {
     "bm_map_locate": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, C.c_uint32, C.c_int, _vp, _vp, C.c_uint64,
                                 _vp]),
     "bm_pipeline_lanes": (C.c_int, [_vp, C.c_uint32]),
+    "bm_ctx_create_lane": (C.c_int, [_vp, C.POINTER(Params), C.POINTER(_vp)]),
     "bm_align_device": (C.c_int, [_vp, C.POINTER(Params)]),
     "bm_align_download": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64)]),
     "bm_comm_unique_id": (C.c_int, [_vp]),
@@ -173,6 +174,15 @@ class Context:
                                  "(this library has no CPU fallback)")
         self.h = h
         self._keep = []
+
+    def create_lane(self, P):
+        """a second context on this GPU viewing this one's reference, index and tables (bm_ctx_create_lane): drive it from
+        another host thread to keep two batches in flight.  Close it before this context."""
+        h = _vp()
+        self._ck(self.lib.bm_ctx_create_lane(self.h, C.byref(P), C.byref(h)), "bm_ctx_create_lane")
+        lane = Context.__new__(Context)
+        lane.lib, lane.h, lane._keep = self.lib, h, []
+        return lane
 
     def close(self):
         if getattr(self, "h", None):

@@ -274,6 +274,26 @@ extern "C" int bm_pipeline_lanes(bm_ctx* c, uint32_t min_reads) {
     return BM_OK;
 }
 
+// A second context on the parent's GPU that VIEWS its reference, index and derived tables and owns only its streams and batch
+// buffers: batches submitted from two host threads -- one per context -- overlap the host<->device copies of one with the
+// kernels of the other (every call of the path waits for its own results, so one context alone cannot).
+extern "C" int bm_ctx_create_lane(bm_ctx* c, const bm_params* p, bm_ctx** lane) {
+    if (!c) return BM_E_ARG;
+    if (!lane || !p) BM_FAIL(c, BM_E_ARG, "bm_ctx_create_lane: null argument");
+    *lane = nullptr;
+    if (c->lanes_off) BM_FAIL(c, BM_E_ARG, "bm_ctx_create_lane: the parent is a lane itself");
+    int r = bm_prepare(c, p);                        // a lane never builds: everything it views exists from here on
+    if (r) return r;
+    bm_ctx* l = nullptr;
+    r = bm_ctx_create(c->device, &l);
+    if (r) BM_FAIL(c, r, "bm_ctx_create_lane: cannot create a context on the parent's device");
+    l->lanes_off = true;
+    lane_share_index(l, c);
+    l->ktiming = false;
+    *lane = l;
+    return BM_OK;
+}
+
 extern "C" int bm_map_locate_packed(bm_ctx* c, const bm_params* p, const uint64_t* planes, const uint32_t* qk,
                                     const uint32_t* pl_off, const uint64_t* read_off, uint32_t n_reads, int filter_best,
                                     uint32_t* loc_off, bm_loc* locs, uint64_t loc_cap, uint64_t* stats) {

@@ -224,6 +224,13 @@ int bm_map_locate_packed(bm_ctx* ctx, const bm_params* p, const uint64_t* planes
  * other.  Same records in the same order; after such a call no batch is resident in ctx.  Not faster on a PCIe-bound
  * box (see bm_pipeline.cu), kept for hosts with a faster link. */
 int bm_pipeline_lanes(bm_ctx* ctx, uint32_t min_reads);
+/* A lane: a second context on ctx's GPU that views ctx's reference, index and derived tables (bm_prepare(ctx, p) is run
+ * first) and owns only streams and batch buffers.  Every call of the path returns with its results, so one context keeps
+ * one batch in flight; a pipeline that drives ctx and a lane from two host threads (what locator/bucket_locator.h:505-604
+ * would be with two batches in flight) hides one batch's host<->device copies under the other's kernels.  The lane is
+ * valid until the parent's index, reference or table settings change; destroy it (bm_ctx_destroy) before the parent.
+ * Index-changing calls on a lane are undefined. */
+int bm_ctx_create_lane(bm_ctx* ctx, const bm_params* p, bm_ctx** lane);
 
 /* ---- several GPUs (no reference counterpart: the reference is one single-threaded process; main.cpp:181-225 is the call
  *      site a multi-GPU bucketmap shards).  Reads are sharded over the ranks, the index is replicated.  One

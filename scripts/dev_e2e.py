@@ -32,4 +32,28 @@ for i in range(10 if "--plain" in sys.argv else 6):
     t = time.perf_counter()
     ctx.map_locate_packed_into(P, hpl, None, hplo, hoff, ooff, olocs, True)
     print("call %d: %.2f ms" % (i, (time.perf_counter() - t) * 1e3), flush=True)
+if "--plain" in sys.argv:
+    # two batches in flight: this context and a lane, one host thread each
+    import threading
+    lane = ctx.create_lane(P)
+    ooff2 = ctx.pinned(n_reads + 1, np.uint32)
+    olocs2 = ctx.pinned(4 * n_reads, bm.LOC_DTYPE)
+    steps = 10
+
+    def drive(c, oo, ol):
+        for _ in range(steps):
+            c.map_locate_packed_into(P, hpl, None, hplo, hoff, oo, ol, True)
+
+    for rep in range(3):
+        th = [threading.Thread(target=drive, args=a) for a in ((ctx, ooff, olocs), (lane, ooff2, olocs2))]
+        t = time.perf_counter()
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        dt = time.perf_counter() - t
+        print("two lanes: %.2f ms per batch  (%.1f M reads/s)  same=%s" % (
+            dt / (2 * steps) * 1e3, 2 * steps * n_reads / dt / 1e6,
+            np.array_equal(ooff, ooff2) and np.array_equal(olocs[:int(ooff[-1])], olocs2[:int(ooff2[-1])])), flush=True)
+    lane.close()
 ctx.close()

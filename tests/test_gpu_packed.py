@@ -163,3 +163,43 @@ def test_pipelined_packed_call_rejects_a_bad_layout_in_a_late_chunk(oracle, bm, 
     # the context is usable afterwards
     nl, _ = ctx.map_locate_packed_into(P, planes, None, pl_off, d.read_off, off_b, locs_b, True)
     assert nl > 0.9 * n
+
+
+def test_lane_context_gives_the_same_records_from_a_second_thread(oracle, bm, ctx):
+    """bm_ctx_create_lane: a context viewing the parent's index; two host threads keep two batches in flight"""
+    import threading
+    d = dataset(read_len=150, n_reads=70_000, n_bases=3_000_000)
+    _setup(oracle, ctx, d)
+    P = bm.default_params(ctx.lib, d.L)
+    planes, qk, pl_off, low = bm.pack_reads(ctx.lib, d.seq, d.qual, d.read_off, P.k, P.avg_base_quality)
+    n = len(d.read_off) - 1
+    off_a = np.empty(n + 1, np.uint32)
+    locs_a = np.empty(4 * n, bm.LOC_DTYPE)
+    na, _ = ctx.map_locate_packed_into(P, planes, None, pl_off, d.read_off, off_a, locs_a, True)
+    want_off, want = off_a.copy(), locs_a[:na].copy()
+    lane = ctx.create_lane(P)
+    try:
+        off_b = np.empty(n + 1, np.uint32)
+        locs_b = np.empty(4 * n, bm.LOC_DTYPE)
+        errs = []
+
+        def drive(c, oo, ol, lo, hi):
+            try:
+                for _ in range(4):
+                    m, _ = c.map_locate_packed_into(P, planes, None, pl_off[lo:hi + 1], d.read_off[lo:hi + 1], oo, ol, True)
+                    assert np.array_equal(np.diff(oo[:hi - lo + 1]), np.diff(want_off[lo:hi + 1]))
+                    assert np.array_equal(ol[:m], want[want_off[lo]:want_off[hi]])
+            except Exception as e:                       # noqa: BLE001 -- reported by the main thread
+                errs.append(e)
+
+        th = [threading.Thread(target=drive, args=(ctx, off_a, locs_a, 0, n)),
+              threading.Thread(target=drive, args=(lane, off_b, locs_b, 5_000, 65_000))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        assert not errs, errs
+        with pytest.raises(bm.BucketMapError, match="lane"):
+            lane.create_lane(P)
+    finally:
+        lane.close()
