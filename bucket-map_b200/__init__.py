@@ -84,6 +84,8 @@ SIGNATURES = {
     "bm_map_locate": (C.c_int, [_vp, C.POINTER(Params), _vp, _vp, _vp, C.c_uint32, C.c_int, _vp, _vp, C.c_uint64,
                                 _vp]),
     "bm_pipeline_lanes": (C.c_int, [_vp, C.c_uint32]),
+    "bm_align_noalloc": (C.c_int, [_vp, C.POINTER(Params)] + [C.c_void_p] * 6 + [C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                                                   C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "bm_ctx_create_lane": (C.c_int, [_vp, C.POINTER(Params), C.POINTER(_vp)]),
     "bm_align_device": (C.c_int, [_vp, C.POINTER(Params)]),
     "bm_align_download": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64)]),
@@ -174,6 +176,13 @@ class Context:
                                  "(this library has no CPU fallback)")
         self.h = h
         self._keep = []
+
+    def align_noalloc(self, P, d_packed, d_bstart, d_blen, d_planes, d_pl_off, d_read_off, n_reads, max_read_len,
+                      d_loc_off, d_locs, n_aln, d_aln, d_cigar, d_cigar_cnt):
+        """bm_align_noalloc: every d_* is a DEVICE address (int); enqueues on the context's stream, allocates nothing"""
+        self._ck(self.lib.bm_align_noalloc(self.h, C.byref(P), d_packed, d_bstart, d_blen, d_planes, d_pl_off, d_read_off,
+                                           n_reads, max_read_len, d_loc_off, d_locs, n_aln, d_aln, d_cigar, d_cigar_cnt),
+                 "bm_align_noalloc")
 
     def create_lane(self, P):
         """a second context on this GPU viewing this one's reference, index and tables (bm_ctx_create_lane): drive it from

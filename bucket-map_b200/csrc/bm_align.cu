@@ -20,6 +20,7 @@
 // pattern masks in shared memory instead of 40 registers per thread.  Alignments with more than E edits (false candidates)
 // go to k_align, which records whole columns.
 #include <algorithm>
+#include <mutex>
 
 #include "bm_internal.cuh"
 
@@ -596,3 +597,109 @@ int bm_align_download(bm_ctx* c, bm_aln* aln, uint32_t* cigar, uint64_t cigar_ca
 }
 
 }  // extern "C"
+
+// ---- bm_align_noalloc: K4 without a single allocation -------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  It is k_align<NW, 0> -- the whole-column verifier
+// above, unchanged -- with its traceback records in a file-scope device array instead of ctx's grown-on-demand buffer; inputs
+// and outputs are the caller's device pointers.  Every GPU that loads the library holds the array until the process exits.
+//
+// All calls share the array: two calls that overlap on the GPU (different contexts, lanes or streams) race.  Nothing in it has
+// to start at zero -- a thread's traceback reads only records (columns 0..n of its own slot) that the same thread stored
+// earlier in the same launch -- so the previous call's contents are simply overwritten.
+namespace {
+
+constexpr size_t kNoAllocWords = (size_t)BM_NOALLOC_SCRATCH_BYTES / 8;
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocWords];
+
+// The array's name is a host-side stand-in in host code, not a device address: the address the kernels get is asked for once
+// per device, with that device current.
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned long long* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+
+cudaError_t noalloc_scratch(int device, unsigned long long** out) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        g_noalloc_ptr[device] = static_cast<unsigned long long*>(p);
+    }
+    *out = g_noalloc_ptr[device];
+    return cudaSuccess;
+}
+
+// ops of alignment id, first op first, at cigar[id * BM_NOALLOC_CIGAR_OPS ..]; k_align leaves them last op first
+__global__ void k_noalloc_finish(bm_aln* __restrict__ aln, uint32_t* __restrict__ cigar, uint32_t n) {
+    const uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n) return;
+    const uint32_t len = aln[id].cigar_len;
+    aln[id].cigar_off = id * kCigTmp;
+    if (len > kCigTmp) return;                 // more runs than a slot holds: the count is reported, the ops are not
+    uint32_t* s = cigar + (size_t)id * kCigTmp;
+    for (uint32_t a = 0, b = len; a + 1 < b; a++) { --b; const uint32_t t = s[a]; s[a] = s[b]; s[b] = t; }
+}
+
+template <int NW>
+cudaError_t noalloc_launch(cudaStream_t st, AlignArgs& a, uint32_t n_aln, uint32_t max_cols, size_t* need, uint32_t* most) {
+    const uint32_t padded = (n_aln + kAlnThreads - 1) / kAlnThreads * kAlnThreads;
+    const size_t per = (size_t)Rec<NW>::kWords * 8 * max_cols;
+    *need = (size_t)padded * per;
+    *most = (uint32_t)((size_t)BM_NOALLOC_SCRATCH_BYTES / per / kAlnThreads * kAlnThreads);
+    if (*need > (size_t)BM_NOALLOC_SCRATCH_BYTES) return cudaErrorInvalidValue;
+    a.chunk_n = padded; a.max_cols = max_cols;
+    k_align<NW, 0><<<padded / kAlnThreads, kAlnThreads, 0, st>>>(a, 0u, n_aln);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" int bm_align_noalloc(bm_ctx* c, const bm_params* p, const uint8_t* d_packed, const uint64_t* d_bstart,
+                                const uint32_t* d_blen, const uint64_t* d_planes, const uint32_t* d_pl_off,
+                                const uint64_t* d_read_off, uint32_t n_reads, uint32_t max_read_len,
+                                const uint32_t* d_loc_off, const bm_loc* d_locs, uint32_t n_aln,
+                                bm_aln* d_aln, uint32_t* d_cigar, uint32_t* d_cigar_cnt) {
+    if (!c) return BM_E_ARG;
+    if (!p || !d_packed || !d_bstart || !d_blen || !d_planes || !d_pl_off || !d_read_off || !d_loc_off || !d_locs ||
+        !d_aln || !d_cigar || !d_cigar_cnt)
+        BM_FAIL(c, BM_E_ARG, "bm_align_noalloc: null argument");
+    if (n_aln == 0) return BM_OK;
+    if (n_reads == 0 || max_read_len == 0) BM_FAIL(c, BM_E_ARG, "bm_align_noalloc: locations without reads");
+    if (max_read_len > 1024) BM_FAIL(c, BM_E_LIMIT, "bm_align_noalloc: reads longer than 1024 bases are not supported by the verifier");
+    BM_CK(c, cudaSetDevice(c->device));
+    AlignArgs a;
+    BM_CK(c, noalloc_scratch(c->device, &a.scratch));
+    a.packed = d_packed; a.bstart = d_bstart; a.blen = d_blen;
+    a.rp = ReadPlanes{reinterpret_cast<const uint2*>(d_planes), nullptr, d_pl_off};
+    a.read_off = d_read_off; a.n_reads = n_reads;
+    a.loc_off = d_loc_off; a.locs = d_locs;
+    a.indel_rate = p->indel_rate; a.quality_threshold = p->quality_threshold;
+    a.aln = d_aln; a.cig_tmp = d_cigar; a.cig_cnt = d_cigar_cnt;
+    a.cig_off = nullptr; a.cigar = nullptr; a.over_list = nullptr; a.id_list = nullptr;
+    a.band_over = nullptr; a.n_band_over = nullptr;
+    const uint32_t max_cols = max_read_len + 2 + (uint32_t)(p->indel_rate * (float)max_read_len) + 1;
+    const uint32_t nw = (max_read_len + 63) / 64;
+    size_t need = 0;
+    uint32_t most = 0;
+    cudaError_t e;
+    if (nw <= 1) e = noalloc_launch<1>(c->stream, a, n_aln, max_cols, &need, &most);
+    else if (nw <= 2) e = noalloc_launch<2>(c->stream, a, n_aln, max_cols, &need, &most);
+    else if (nw <= 3) e = noalloc_launch<3>(c->stream, a, n_aln, max_cols, &need, &most);
+    else if (nw <= 4) e = noalloc_launch<4>(c->stream, a, n_aln, max_cols, &need, &most);
+    else if (nw <= 5) e = noalloc_launch<5>(c->stream, a, n_aln, max_cols, &need, &most);
+    else if (nw <= 8) e = noalloc_launch<8>(c->stream, a, n_aln, max_cols, &need, &most);
+    else e = noalloc_launch<16>(c->stream, a, n_aln, max_cols, &need, &most);
+    if (need > (size_t)BM_NOALLOC_SCRATCH_BYTES) {
+        char msg[256];
+        snprintf(msg, sizeof msg, "bm_align_noalloc: %u alignments of reads up to %u bases need %zu bytes of traceback records, "
+                 "the static array holds %u: at most %u alignments per call at this read length", n_aln, max_read_len, need,
+                 (unsigned)BM_NOALLOC_SCRATCH_BYTES, most);
+        BM_FAIL(c, BM_E_LIMIT, msg);
+    }
+    BM_CK(c, e);
+    k_noalloc_finish<<<(n_aln + 255) / 256, 256, 0, c->stream>>>(d_aln, d_cigar, n_aln);
+    BM_CK(c, cudaGetLastError());
+    return BM_OK;
+}

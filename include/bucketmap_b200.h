@@ -278,6 +278,30 @@ int bm_align_device(bm_ctx* ctx, const bm_params* p);
 /* aln: one per location; cigar: capacity cigar_cap ops; *cigar_used = ops needed */
 int bm_align_download(bm_ctx* ctx, bm_aln* aln, uint32_t* cigar, uint64_t cigar_cap, uint64_t* cigar_used);
 
+/* K4 for callers that cannot allocate.  No counterpart in the reference: added (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The call allocates nothing -- no
+ * cudaMalloc / cudaFree, no allocating library routine: the traceback records of the verifier live in a static device array
+ * of BM_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until the process exits.
+ *   Inputs, all DEVICE pointers in the layouts of the calls above: the 2-bit text + bucket tables (bm_ref_upload), the reads'
+ * base planes + chunk offsets (bm_pack_layout / bm_pack_reads) and base offsets, loc_off[n_reads + 1] + locs (what
+ * bm_locate_download delivers); max_read_len = the longest read (<= 1024).  n_aln = loc_off[n_reads] alignments are made.
+ *   Outputs, DEVICE pointers: aln[n_aln] (same fields as bm_align_device; cigar_off = i * BM_NOALLOC_CIGAR_OPS), cigar[n_aln *
+ * BM_NOALLOC_CIGAR_OPS] (the ops of alignment i, first op first, in its slot; an alignment with more than
+ * BM_NOALLOC_CIGAR_OPS runs reports its cigar_len but no ops: use bm_align_device for those), cigar_cnt[n_aln].
+ *   Limit: ceil(n_aln / 128) * 128 * max_cols * 8 * words bytes of records must fit the array, max_cols = max_read_len + 3 +
+ * (uint32_t)(p->indel_rate * max_read_len), words = 4 / 6 / 8 / 10 / 12 / 18 / 36 for reads of up to 64 / 128 / 192 / 256 /
+ * 320 / 512 / 1024 bases: 1,024 alignments of 300-base reads, 3,328 of 150-base reads.  More is refused with BM_E_LIMIT and
+ * a message that names the bound; split the batch.
+ *   The kernels are enqueued on ctx's stream and the call returns without waiting (bm_sync).  All calls share the array: calls
+ * that overlap on the GPU race; nothing in it must be cleared between calls. */
+#define BM_NOALLOC_SCRATCH_BYTES (32u << 20)
+#define BM_NOALLOC_CIGAR_OPS 16
+int bm_align_noalloc(bm_ctx* ctx, const bm_params* p, const uint8_t* d_packed, const uint64_t* d_bstart,
+                     const uint32_t* d_blen, const uint64_t* d_planes, const uint32_t* d_pl_off,
+                     const uint64_t* d_read_off, uint32_t n_reads, uint32_t max_read_len,
+                     const uint32_t* d_loc_off, const bm_loc* d_locs, uint32_t n_aln,
+                     bm_aln* d_aln, uint32_t* d_cigar, uint32_t* d_cigar_cnt);
+
 /* ---- measurement ----------------------------------------------------------------------------------------------- */
 /* CUDA events on the library's stream around whatever is enqueued between start and stop. */
 int bm_timer_start(bm_ctx* ctx);
