@@ -2,6 +2,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <new>
 #include <set>
@@ -9,6 +10,8 @@
 #include <vector>
 
 #include <cub/device/device_scan.cuh>
+
+#include <sys/mman.h>
 
 #include "bm_internal.cuh"
 
@@ -414,26 +417,51 @@ int bm_sync(bm_ctx* c) {
     BM_CK(c, cudaStreamSynchronize(c->stream));
     return BM_OK;
 }
-// Pinned memory for the caller's batches.  On a machine without a usable CUDA device (the host-side unit tests) plain
-// page-aligned memory is handed out instead; bm_host_free tells the two apart.
+// Pinned memory for the caller's batches.  Large blocks are 2 MB-aligned anonymous memory with MADV_HUGEPAGE, touched by the
+// caller's thread and then registered with the driver: on the measured host cudaMallocHost costs 0.4 ms per MB, all of it
+// under the driver's lock (a parser thread getting its next batch buffer stalls the device thread's copies for that long),
+// huge-page faults 0.12 ms per MB outside the lock and the registration 0.03 ms per MB.  On a machine without a usable CUDA
+// device (the host-side unit tests) the memory stays unregistered; bm_host_free tells the kinds apart.
 static std::mutex g_plain_m;
-static std::set<void*> g_plain;
+static std::map<void*, std::pair<size_t, bool>> g_plain;       // block -> (bytes, registered)
 
 void* bm_host_alloc(uint64_t bytes) {
     void* p = nullptr;
+    constexpr size_t kHuge = (size_t)2 << 20;
+    if (bytes >= 2 * kHuge) {
+        const size_t n = ((size_t)bytes + kHuge - 1) & ~(kHuge - 1);
+        if (posix_memalign(&p, kHuge, n) == 0) {
+            static const bool thp = !getenv("BM_HOST_THP") || atoi(getenv("BM_HOST_THP")) != 0;
+            if (thp) madvise(p, n, MADV_HUGEPAGE);
+            for (size_t i = 0; i < n; i += 4096) static_cast<volatile char*>(p)[i] = 0;
+            const bool reg = cudaHostRegister(p, n, cudaHostRegisterPortable) == cudaSuccess;
+            if (!reg) cudaGetLastError();
+            std::lock_guard<std::mutex> g(g_plain_m);
+            g_plain[p] = {n, reg};
+            return p;
+        }
+        p = nullptr;
+    }
     if (cudaMallocHost(&p, bytes ? bytes : 1) == cudaSuccess) return p;
     cudaGetLastError();
     if (posix_memalign(&p, 4096, bytes ? bytes : 1) != 0) return nullptr;
     std::lock_guard<std::mutex> g(g_plain_m);
-    g_plain.insert(p);
+    g_plain[p] = {(size_t)bytes, false};
     return p;
 }
 void bm_host_free(void* p) {
     if (!p) return;
     {
-        std::lock_guard<std::mutex> g(g_plain_m);
+        std::unique_lock<std::mutex> g(g_plain_m);
         auto it = g_plain.find(p);
-        if (it != g_plain.end()) { g_plain.erase(it); free(p); return; }
+        if (it != g_plain.end()) {
+            const bool reg = it->second.second;
+            g_plain.erase(it);
+            g.unlock();
+            if (reg) cudaHostUnregister(p);
+            free(p);
+            return;
+        }
     }
     cudaFreeHost(p);
 }

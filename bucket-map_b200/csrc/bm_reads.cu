@@ -16,6 +16,13 @@
 
 #include "bm_internal.cuh"
 
+#if defined(__SSE2__) && !defined(__CUDA_ARCH__)
+#include <emmintrin.h>
+#define BM_PACK_SSE2 1
+#else
+#define BM_PACK_SSE2 0
+#endif
+
 namespace {
 
 // seqan3 dna4 char_to_rank incl. the IUPAC first-base convention (see bm_rank_dna4): two 32-bit tables of 2-bit entries
@@ -138,12 +145,43 @@ static inline uint32_t pack_one(const uint8_t* lut, const uint8_t* s, const uint
         const uint32_t lim = n - 32 * c < 32 ? n - 32 * c : 32;
         uint32_t lo = 0, hi = 0;
         const uint8_t* t = s + 32 * c;
-        for (uint32_t i = 0; i < lim; i++) { const uint32_t v = lut[t[i]]; lo |= (v & 1u) << i; hi |= (v >> 1) << i; }
+        uint32_t i = 0;
+#if BM_PACK_SSE2
+        // 16 bases per step while they are plain A/C/G/T (either case): with c1, c2 = bits 1, 2 of the character the rank is
+        // (c2, c1 ^ c2), and a byte-mask move collects one bit of 16 characters.  Anything else takes the table below.
+        for (; i + 16 <= lim; i += 16) {
+            const __m128i x = _mm_loadu_si128(reinterpret_cast<const __m128i*>(t + i));
+            const __m128i u = _mm_and_si128(x, _mm_set1_epi8((char)0xDF));
+            const __m128i ok = _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(u, _mm_set1_epi8('A')), _mm_cmpeq_epi8(u, _mm_set1_epi8('C'))),
+                                            _mm_or_si128(_mm_cmpeq_epi8(u, _mm_set1_epi8('G')), _mm_cmpeq_epi8(u, _mm_set1_epi8('T'))));
+            if (_mm_movemask_epi8(ok) != 0xFFFF) break;
+            const uint32_t m1 = (uint32_t)_mm_movemask_epi8(_mm_slli_epi16(x, 6));      // bit 1 of every character
+            const uint32_t m2 = (uint32_t)_mm_movemask_epi8(_mm_slli_epi16(x, 5));      // bit 2
+            lo |= (m1 ^ m2) << i; hi |= m2 << i;
+        }
+#endif
+        for (; i < lim; i++) { const uint32_t v = lut[t[i]]; lo |= (v & 1u) << i; hi |= (v >> 1) << i; }
         out[c] = (uint64_t)lo | ((uint64_t)hi << 32);
     }
     if (!q) return 0;
     uint32_t mn = nq < n ? 0u : 0xFFFFFFFFu;
-    for (uint32_t i = 0; i < nq; i++) { const uint32_t v = (uint32_t)q[i] - 33u; mn = v < mn ? v : mn; }
+    {
+        uint32_t i = 0;
+#if BM_PACK_SSE2
+        // smallest quality character, 16 at a time; a character below '!' counts as a huge phred in the loop below (32-bit
+        // wrap), so a block that holds one is left to it
+        __m128i m = _mm_set1_epi8((char)0xFF);
+        uint32_t i16 = 0;
+        for (; i16 + 16 <= nq; i16 += 16) m = _mm_min_epu8(m, _mm_loadu_si128(reinterpret_cast<const __m128i*>(q + i16)));
+        if (i16) {
+            m = _mm_min_epu8(m, _mm_srli_si128(m, 8)); m = _mm_min_epu8(m, _mm_srli_si128(m, 4));
+            m = _mm_min_epu8(m, _mm_srli_si128(m, 2)); m = _mm_min_epu8(m, _mm_srli_si128(m, 1));
+            const uint32_t lowest = (uint32_t)_mm_cvtsi128_si32(m) & 0xFFu;
+            if (lowest >= 33u) { const uint32_t v = lowest - 33u; mn = v < mn ? v : mn; i = i16; }
+        }
+#endif
+        for (; i < nq; i++) { const uint32_t v = (uint32_t)q[i] - 33u; mn = v < mn ? v : mn; }
+    }
     const uint32_t nk = (n >= k) ? n - k + 1 : 0;
     if (mn >= b || nk == 0) {                                     // every window passes
         if (qo) for (uint32_t c = 0; c < nch; c++) {

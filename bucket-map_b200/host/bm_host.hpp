@@ -152,14 +152,18 @@ class fastq_reader {
 public:
     explicit fastq_reader(std::filesystem::path const& p);
     bool ok() const { return map_.ok(); }
-    // Next batch of up to max_reads reads (or max_bases bases): splits the records (one thread, memchr), then packs them
-    // for query seed length k and quality threshold b on the host threads.  false when the file is exhausted.
+    // Next batch of up to max_reads reads (or max_bases bases): splits the records (line ends found by the host threads, one
+    // window of the file at a time; the walk over the lines is serial and copies nothing), then packs them for query seed
+    // length k and quality threshold b on the host threads.  false when the file is exhausted.
     bool next(read_batch& b, uint32_t max_reads, uint64_t max_bases, uint32_t k, uint32_t bq);
 
 private:
     bool line(const char*& s, size_t& len);
+    void index_window();
     file_map map_;
     size_t pos_ = 0;
+    std::vector<uint64_t> nl_;      // positions of the line feeds in [.., win_hi_), ascending; nl_i_ = the next one to use
+    size_t nl_i_ = 0, win_hi_ = 0;
 };
 
 // FASTA parsed and bucketized once per (path, L, r); nullptr (after an [ERROR] line) if it cannot be read

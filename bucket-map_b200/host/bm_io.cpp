@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <chrono>
 #include <cstring>
 #include <ctime>
 #include <mutex>
@@ -245,21 +246,62 @@ void genome::bucketize(uint32_t bucket_len, uint32_t read_len) {
 fastq_reader::fastq_reader(std::filesystem::path const& p) { map_.open(p); }
 
 // next line as a view into the mapped file; false at end of file
+// Line feeds of the next window of the file, found by the host threads (each scans its own byte range with memchr, which also
+// spreads the first touch of the mapping's pages over the threads).  Called when every line feed known so far has been used,
+// so everything between pos_ and win_hi_ is the head of one line.
+static constexpr uint64_t kCrFlag = 1ull << 63;      // in an entry of the line-feed index: the line ends in "\r\n"
+
+void fastq_reader::index_window() {
+    constexpr size_t kWindow = (size_t)256 << 20;
+    const size_t end = map_.size();
+    const size_t lo = win_hi_, hi = end - lo > kWindow ? lo + kWindow : end;
+    unsigned T = host_threads();
+    if (hi - lo < ((size_t)1 << 20)) T = 1;
+    std::vector<std::vector<uint64_t>> found(T);
+    const char* d = map_.data();
+    parallel_parts(T, [&](unsigned t, unsigned parts) {
+        size_t i = lo + (size_t)((unsigned __int128)(hi - lo) * t / parts);
+        const size_t e = lo + (size_t)((unsigned __int128)(hi - lo) * (t + 1) / parts);
+        std::vector<uint64_t>& v = found[t];
+        v.reserve((e - i) / 96 + 16);
+        while (i < e) {
+            const char* nl = (const char*)memchr(d + i, '\n', e - i);
+            if (!nl) break;
+            const uint64_t at = (uint64_t)(nl - d);
+            v.push_back(at | ((at > 0 && nl[-1] == '\r') ? kCrFlag : 0ull));     // the walk over the lines reads no file byte
+            i = (size_t)at + 1;
+        }
+    });
+    size_t total = 0;
+    for (auto const& v : found) total += v.size();
+    nl_.resize(total);
+    size_t at = 0;
+    for (auto const& v : found) { if (!v.empty()) memcpy(nl_.data() + at, v.data(), v.size() * 8); at += v.size(); }
+    nl_i_ = 0;
+    win_hi_ = hi;
+}
+
 bool fastq_reader::line(const char*& s, size_t& len) {
     const size_t end = map_.size();
     if (pos_ >= end) return false;
+    while (nl_i_ == nl_.size() && win_hi_ < end) index_window();
     const char* b = map_.data() + pos_;
-    const char* nl = (const char*)memchr(b, '\n', end - pos_);
+    const bool has_nl = nl_i_ < nl_.size();
+    const uint64_t ent = has_nl ? nl_[nl_i_++] : (uint64_t)end;
+    const size_t e = (size_t)(ent & ~kCrFlag);
     s = b;
-    len = nl ? (size_t)(nl - b) : end - pos_;
-    pos_ += len + (nl ? 1 : 0);
-    if (len && s[len - 1] == '\r') len--;
+    len = e - pos_;
+    pos_ = e + (has_nl ? 1 : 0);
+    if (has_nl ? (ent & kCrFlag) != 0 && len : (len && s[len - 1] == '\r')) len--;
     return true;
 }
 
 bool fastq_reader::next(read_batch& b, uint32_t max_reads, uint64_t max_bases, uint32_t k, uint32_t bq) {
     b.clear();
     if (!map_.ok()) return false;
+    static const bool trace = std::getenv("BM_HOST_TRACE") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count(); };
     // 1. split the records (one thread: four memchr per record); the text is not copied
     const char *id, *s, *plus, *q;
     size_t nid, ns, np, nq;
@@ -276,6 +318,7 @@ bool fastq_reader::next(read_batch& b, uint32_t max_reads, uint64_t max_bases, u
     }
     const uint32_t n = b.size();
     if (!n) return false;
+    const double t_split = since();
     // 2. the device form, written by the host threads into pinned memory
     b.read_off.reserve((size_t)(n + 1) * 8);
     b.pl_off.reserve((size_t)(n + 1) * 4);
@@ -287,17 +330,28 @@ bool fastq_reader::next(read_batch& b, uint32_t max_reads, uint64_t max_bases, u
     }
     const size_t nch = plo[n];
     b.planes.reserve((nch + 1) * 8);
-    b.qk.reserve((nch + 1) * 4);
     unsigned T = host_threads();
     if (n < 4096) T = 1;
-    std::vector<uint32_t> low(T, 0);
-    parallel_parts(T, [&](unsigned t, unsigned parts) {
-        const uint32_t r0 = (uint32_t)((uint64_t)n * t / parts), r1 = (uint32_t)((uint64_t)n * (t + 1) / parts);
-        bm_pack_reads_v((const uint8_t* const*)b.seq.data(), (const uint8_t* const*)b.qual.data(), b.qual_len.data(),
-                        b.off.data(), plo, r0, r1, k, bq, b.planes.as<uint64_t>(), b.qk.as<uint32_t>(), &low[t]);
-    });
+    const double t_alloc = since();
+    // The quality plane is made (and its pinned buffer taken) only for a batch that needs it: the first pass packs the bases
+    // and reports whether any k-mer window fails -b; most batches of good reads stop there.
+    std::vector<uint32_t> low(T * 16, 0);
+    auto pack = [&](uint64_t* planes, uint32_t* qk) {
+        parallel_parts(T, [&](unsigned t, unsigned parts) {
+            const uint32_t r0 = (uint32_t)((uint64_t)n * t / parts), r1 = (uint32_t)((uint64_t)n * (t + 1) / parts);
+            bm_pack_reads_v((const uint8_t* const*)b.seq.data(), (const uint8_t* const*)b.qual.data(), b.qual_len.data(),
+                            b.off.data(), plo, r0, r1, k, bq, planes, qk, &low[t * 16]);
+        });
+    };
+    pack(b.planes.as<uint64_t>(), nullptr);
     b.all_pass = true;
-    for (uint32_t v : low) if (v) b.all_pass = false;
+    for (unsigned t = 0; t < T; t++) if (low[t * 16]) b.all_pass = false;
+    if (!b.all_pass) {
+        b.qk.reserve((nch + 1) * 4);
+        pack(b.planes.as<uint64_t>(), b.qk.as<uint32_t>());
+    }
+    if (trace) fprintf(stderr, "[host] fastq batch of %u reads: split %.2f  buffers %.2f  pack on %u threads %.2f ms\n", n, t_split,
+                       t_alloc - t_split, T, since() - t_alloc);
     return true;
 }
 

@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <condition_variable>
 #include <atomic>
@@ -19,6 +20,8 @@
 #include <thread>
 
 #include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <unistd.h>
 
 #include "bm_host.hpp"
@@ -87,6 +90,29 @@ inline void put_num(std::string& out, uint64_t v) {
     while (n) out += t[--n];
 }
 
+// the two sinks of the SAM renderer: the size of the text, and the text
+struct count_sink {
+    uint64_t n = 0;
+    void append(const char*, size_t len) { n += len; }
+    void push(char) { n++; }
+    void fill(size_t count, char) { n += count; }
+    void num(uint64_t v) { do { n++; v /= 10; } while (v); }
+    void bases(const uint8_t*, size_t len, const char*) { n += len; }
+};
+struct mem_sink {
+    char* p;
+    void append(const char* s, size_t len) { memcpy(p, s, len); p += len; }
+    void push(char c) { *p++ = c; }
+    void fill(size_t count, char c) { memset(p, c, count); p += count; }
+    void num(uint64_t v) {
+        char t[24];
+        int n = 0;
+        do { t[n++] = (char)('0' + v % 10); v /= 10; } while (v);
+        while (n) *p++ = t[--n];
+    }
+    void bases(const uint8_t* s, size_t len, const char* decode) { for (size_t x = 0; x < len; x++) p[x] = decode[s[x]]; p += len; }
+};
+
 // one batch on its way through the pipeline
 struct work {
     read_batch b;
@@ -144,15 +170,22 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
         if (want_lidx >= 0) bm_locator_index(c0, want_lidx);
         if (want_fine >= 0) bm_index_fine_table(c0, want_fine);
     }
-    int out_fd = ::open(sam_file.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    bool out_mappable = true;                     // regular file opened read-write: the SAM text is copied into a mapping
+    int out_fd = ::open(sam_file.c_str(), O_RDWR | O_CREAT | O_TRUNC, 0644);
+    if (out_fd < 0) { out_mappable = false; out_fd = ::open(sam_file.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644); }
     if (out_fd < 0) { std::cerr << "[ERROR]\t\tCannot write " << sam_file << ".\n"; return; }
+    {
+        struct stat st;
+        if (fstat(out_fd, &st) != 0 || !S_ISREG(st.st_mode) || std::getenv("BM_SAM_PWRITE")) out_mappable = false;
+    }
+    const bool host_trace = std::getenv("BM_HOST_TRACE") != nullptr;
 
     // ---- the parser starts on the first batch now; the device side gets ready meanwhile ----------------------------------
     struct dev { bm_ctx* c; std::unique_ptr<context> own; };
     std::vector<dev> devs;
     devs.push_back({c0, nullptr});
     const size_t n_dev = devices_.size() > 1 ? devices_.size() : 1;
-    const size_t depth = n_dev + 3;
+    const size_t depth = n_dev + 2;        // one batch being parsed, one per device, one being rendered
     std::vector<work> pool(depth);
     batch_queue<work*> free_q, parsed_q, done_q;
     for (auto& w : pool) free_q.push(&w);
@@ -260,8 +293,8 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
             bool done = false;
             if (!align) {
                 // one call: H2D chunks overlapped with the mapper.  The merged lists are almost always one record per
-                // read; if this batch needs more room than 4 per read the staged calls below size the buffer exactly.
-                w->loc_cap = (size_t)4 * n + 1024;
+                // read; if this batch needs more room than 2 per read the staged calls below size the buffer exactly.
+                w->loc_cap = (size_t)2 * n + 1024;
                 w->locs.reserve(w->loc_cap * sizeof(bm_loc));
                 int r1 = bm_map_locate_packed(c, &p, planes, qkp, plo, roff, n, 1, w->loc_off.as<uint32_t>(), w->locs.as<bm_loc>(),
                                               w->loc_cap, stats);
@@ -313,70 +346,106 @@ void bucket_locator::locate(fs::path const& sequence_file, fs::path const& index
         std::map<uint64_t, work*> waiting;
         uint64_t next_seq = 0;
         size_t ended = 0;
-        auto render = [&](work* w) {
-            const double t1 = now_s();
+        // The records of reads [r0, r1) into a sink: once into a counting sink (the exact size of every thread's piece, so that
+        // the pieces have their places in the file before a byte is written), once into memory -- the mapping of the file's new
+        // tail, or, for outputs that cannot be mapped, a buffer that pwrite sends.
+        auto emit = [&](auto& out, work* w, uint32_t r0, uint32_t r1) -> unsigned {
             const read_batch& b = w->b;
-            const uint32_t n = b.size();
             const uint32_t* loc_off = w->loc_off.as<uint32_t>();
             const bm_loc* locs = w->locs.as<bm_loc>();
+            unsigned records = 0;
+            for (uint32_t i = r0; i < r1; i++) {
+                if (loc_off[i] == loc_off[i + 1]) continue;
+                const size_t len = (size_t)(b.off[i + 1] - b.off[i]);
+                for (uint32_t j = loc_off[i]; j < loc_off[i + 1]; j++) {
+                    const bm_loc& l = locs[j];
+                    size_t map_qual, ref_offset;
+                    if (!align) {
+                        map_qual = std::min((unsigned int)60, 6 * l.votes);                  // :591
+                        ref_offset = (unsigned int)(bucket_offsets[l.bucket] + l.offset);    // :592
+                    } else {
+                        if (!w->aln[j].kept) continue;                                       // :571-573
+                        map_qual = (uint8_t)w->aln[j].map_qual;                              // mapq is a uint8_t field in SAM
+                        ref_offset = (unsigned int)(w->aln[j].begin + bucket_offsets[l.bucket] + l.offset);   // :576
+                    }
+                    out.append(b.id[i], b.id_len[i]); out.push('\t');
+                    out.num(l.is_original ? 0 : 16); out.push('\t');
+                    out.append(bucket_name[l.bucket].data(), bucket_name[l.bucket].size()); out.push('\t');
+                    out.num(ref_offset + 1); out.push('\t');
+                    out.num(map_qual); out.push('\t');
+                    if (align && w->aln[j].cigar_len) {
+                        for (uint32_t x = 0; x < w->aln[j].cigar_len; x++) {
+                            const uint32_t op = w->cigar[w->aln[j].cigar_off + x];
+                            out.num(op >> 4); out.push("MID"[op & 15u]);
+                        }
+                    } else out.push('*');
+                    out.append("\t*\t0\t0\t", 7);
+                    out.bases((const uint8_t*)b.seq[i], len, decode); out.push('\t');
+                    out.append(b.qual[i], b.qual_len[i]);
+                    if (b.qual_len[i] < len) out.fill(len - b.qual_len[i], '!');
+                    out.push('\n');
+                    records++;
+                }
+            }
+            return records;
+        };
+        auto render = [&](work* w) {
+            const double t1 = now_s();
+            const uint32_t n = w->b.size();
             unsigned T = host_threads();
             if (n < 2048) T = 1;
-            if (w->text.size() < T) w->text.resize(T);
+            std::vector<uint64_t> bytes(T, 0), at(T + 1, file_pos);
             std::vector<unsigned> cnt(T, 0);
+            auto range = [&](unsigned t, unsigned parts, uint32_t& r0, uint32_t& r1) {
+                r0 = (uint32_t)((uint64_t)n * t / parts); r1 = (uint32_t)((uint64_t)n * (t + 1) / parts);
+            };
             parallel_parts(T, [&](unsigned t, unsigned parts) {
-                std::string& out = w->text[t];
-                out.clear();
-                const uint32_t r0 = (uint32_t)((uint64_t)n * t / parts), r1 = (uint32_t)((uint64_t)n * (t + 1) / parts);
-                std::string seq_text;
-                for (uint32_t i = r0; i < r1; i++) {
-                    if (loc_off[i] == loc_off[i + 1]) continue;
-                    const size_t len = (size_t)(b.off[i + 1] - b.off[i]);
-                    seq_text.resize(len);
-                    const uint8_t* s = (const uint8_t*)b.seq[i];
-                    for (size_t x = 0; x < len; x++) seq_text[x] = decode[s[x]];
-                    for (uint32_t j = loc_off[i]; j < loc_off[i + 1]; j++) {
-                        const bm_loc& l = locs[j];
-                        size_t map_qual, ref_offset;
-                        if (!align) {
-                            map_qual = std::min((unsigned int)60, 6 * l.votes);                  // :591
-                            ref_offset = (unsigned int)(bucket_offsets[l.bucket] + l.offset);    // :592
-                        } else {
-                            if (!w->aln[j].kept) continue;                                       // :571-573
-                            map_qual = (uint8_t)w->aln[j].map_qual;                              // mapq is a uint8_t field in SAM
-                            ref_offset = (unsigned int)(w->aln[j].begin + bucket_offsets[l.bucket] + l.offset);   // :576
-                        }
-                        out.append(b.id[i], b.id_len[i]); out += '\t';
-                        put_num(out, l.is_original ? 0 : 16); out += '\t';
-                        out += bucket_name[l.bucket]; out += '\t';
-                        put_num(out, ref_offset + 1); out += '\t';
-                        put_num(out, map_qual); out += '\t';
-                        if (align && w->aln[j].cigar_len) {
-                            for (uint32_t x = 0; x < w->aln[j].cigar_len; x++) {
-                                const uint32_t op = w->cigar[w->aln[j].cigar_off + x];
-                                put_num(out, op >> 4); out += "MID"[op & 15u];
-                            }
-                        } else out += '*';
-                        out += "\t*\t0\t0\t";
-                        out += seq_text; out += '\t';
-                        out.append(b.qual[i], b.qual_len[i]);
-                        if (b.qual_len[i] < len) out.append(len - b.qual_len[i], '!');
-                        out += '\n';
-                        cnt[t]++;
+                uint32_t r0, r1;
+                range(t, parts, r0, r1);
+                count_sink c;
+                cnt[t] = emit(c, w, r0, r1);
+                bytes[t] = c.n;
+            });
+            for (unsigned t = 0; t < T; t++) { at[t + 1] = at[t] + bytes[t]; mapped_locations += cnt[t]; }
+            const double t_counted = now_s();
+            bool ok = true, mapped = false;
+            if (out_mappable && at[T] > file_pos) {
+                const uint64_t page = (uint64_t)sysconf(_SC_PAGESIZE);
+                const uint64_t a0 = file_pos & ~(page - 1);
+                void* m = MAP_FAILED;
+                if (::ftruncate(out_fd, (off_t)at[T]) == 0)
+                    m = ::mmap(nullptr, (size_t)(at[T] - a0), PROT_READ | PROT_WRITE, MAP_SHARED, out_fd, (off_t)a0);
+                if (m == MAP_FAILED) out_mappable = false;
+                else {
+                    parallel_parts(T, [&](unsigned t, unsigned parts) {
+                        uint32_t r0, r1;
+                        range(t, parts, r0, r1);
+                        mem_sink dst{(char*)m + (at[t] - a0)};
+                        emit(dst, w, r0, r1);
+                    });
+                    ::munmap(m, (size_t)(at[T] - a0));
+                    mapped = true;
+                }
+            }
+            if (!mapped) {
+                if (w->text.size() < T) w->text.resize(T);
+                parallel_parts(T, [&](unsigned t, unsigned parts) {
+                    uint32_t r0, r1;
+                    range(t, parts, r0, r1);
+                    std::string& buf = w->text[t];
+                    buf.resize((size_t)bytes[t]);
+                    mem_sink dst{buf.data()};
+                    emit(dst, w, r0, r1);
+                    size_t done = 0;
+                    while (done < buf.size()) {
+                        ssize_t k = ::pwrite(out_fd, buf.data() + done, buf.size() - done, (off_t)(at[t] + done));
+                        if (k <= 0) { ok = false; break; }
+                        done += (size_t)k;
                     }
-                }
-            });
-            std::vector<uint64_t> at(T + 1, file_pos);
-            for (unsigned t = 0; t < T; t++) { at[t + 1] = at[t] + w->text[t].size(); mapped_locations += cnt[t]; }
-            bool ok = true;
-            parallel_parts(T, [&](unsigned t, unsigned) {
-                const std::string& out = w->text[t];
-                size_t done = 0;
-                while (done < out.size()) {
-                    ssize_t k = ::pwrite(out_fd, out.data() + done, out.size() - done, (off_t)(at[t] + done));
-                    if (k <= 0) { ok = false; break; }
-                    done += (size_t)k;
-                }
-            });
+                });
+            }
+            if (host_trace) fprintf(stderr, "[host] SAM batch of %u reads: sizes %.2f  render + write (%s) %.2f ms\n", n,
+                                    (t_counted - t1) * 1e3, mapped ? "mapped" : "pwrite", (now_s() - t_counted) * 1e3);
             if (!ok) { std::cerr << "[ERROR]\t\tWriting " << sam_file << " failed.\n"; failed.store(true); }
             file_pos = at[T];
             read_id += n;

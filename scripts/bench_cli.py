@@ -45,7 +45,7 @@ common = ["-g", fa, "-L", "65536", "-f", "1", "--seed-x", "40503", "--seed-y", "
 t_index, log_x = run(["-x", "-i", "idx"] + common)
 t_map, log_m = run(["-i", "idx", "-q", fq, "-o", "out.sam"] + common)
 sam_bytes = os.path.getsize(os.path.join(d, "out.sam"))
-bench_lines = [l for l in log_m.splitlines() if l.startswith("[BENCHMARK]")]
+bench_lines = [l for l in log_m.splitlines() if l.startswith("[BENCHMARK]") or l.startswith("[pipe]") or l.startswith("[host]")]
 m = re.search(r"Total mapped locations: (\d+)", log_m)
 out = {"workload": "c2 through the command line: genome.fa %d bases, reads.fq %d x 300bp" % (a.bases, a.reads),
        "dir": d, "index_wall_s": t_index, "map_wall_s": t_map, "reads_per_s_map_wall": a.reads / t_map,

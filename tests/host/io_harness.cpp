@@ -40,7 +40,7 @@ int main(int argc, char** argv) {
             for (uint32_t i = 0; i < n; i++) { hid = fnv(b.id[i], b.id_len[i], hid); hq = fnv(b.qual[i], b.qual_len[i], hq); }
             printf("batch %u chunks %u all_pass %d planes %016llx qk %016llx off %016llx pl_off %016llx ids %016llx quals %016llx\n", n,
                    plo[n], b.all_pass ? 1 : 0, (unsigned long long)fnv(b.planes.data(), (size_t)plo[n] * 8),
-                   (unsigned long long)fnv(b.qk.data(), (size_t)plo[n] * 4),
+                   (unsigned long long)(b.all_pass ? 0ull : fnv(b.qk.data(), (size_t)plo[n] * 4)),   // no quality plane is made for a batch that passes
                    (unsigned long long)fnv(b.read_off.data(), (size_t)(n + 1) * 8), (unsigned long long)fnv(plo, (size_t)(n + 1) * 4),
                    (unsigned long long)hid, (unsigned long long)hq);
         }
