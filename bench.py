@@ -81,6 +81,9 @@ def parse():
     ap.add_argument("--frac", type=float, default=1.0, help="FracMinHash fraction (-f): 1 = the headline, 0.25 = the reference's default")
     ap.add_argument("--ftable", type=int, default=1, choices=[0, 1], help="full-resolution k-mer table for the exact recount")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (0: as --steps)")
+    ap.add_argument("--e2e-lanes", type=int, default=0, choices=[0, 1, 2],
+                    help="host threads (calls in flight) per GPU in the end-to-end steps: 2 = the context and a lane; 0 = 2 on one "
+                         "GPU, 1 on several (there the host's PCIe fabric is the bound and a second call in flight gains nothing)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--lanes", type=int, default=0,
@@ -562,39 +565,95 @@ def main():
     olocs = ctx.pinned(max(4 * n_reads * (world if rank == 0 else 1), 1024), bm.LOC_DTYPE)   # merged best locations: ~1 per read
     h2d_packed = int(pl_off[-1]) * 8 + (int(pl_off[-1]) * 4 if n_low else 0) + hplo.nbytes + hoff.nbytes
     d2h = 0
-    e2e = e2e_ascii = None
+    e2e = e2e_ascii = e2e_one = None
     if not align:
-        def step_e2e():
+        import threading
+
+        def step_e2e(c, oo, ol):
             if world == 1:
-                n_locs, _ = ctx.map_locate_packed_into(P, hpl, hqk, hplo, hoff, ooff, olocs, True)
-                return ooff.nbytes + n_locs * bm.LOC_DTYPE.itemsize
+                n_locs, _ = c.map_locate_packed_into(P, hpl, hqk, hplo, hoff, oo, ol, True)
+                return oo.nbytes + n_locs * bm.LOC_DTYPE.itemsize
             # N > 1: every rank maps its shard from its host buffers; the records go to rank 0's HOST through the gather
-            ctx.map_locate_packed_into(P, hpl, hqk, hplo, hoff, None, None, True)
+            c.map_locate_packed_into(P, hpl, hqk, hplo, hoff, None, None, True)
             if rank == 0:
-                nr, nl = ctx.gather_results(ooff, olocs)
+                nr, nl = c.gather_results(oo, ol)
                 return (nr + 1) * 4 + nl * bm.LOC_DTYPE.itemsize
-            ctx.gather_results()
+            c.gather_results()
             return 0
+
+        def run_e2e(lanes):
+            """lanes: [(context, out offsets, out records)], one host thread each; every step is one call with its own H2D + D2H"""
+            def sync_all():
+                for c, _, _ in lanes:
+                    c.sync()
+                    if world > 1:
+                        c.gather_sync()
+                torch.cuda.synchronize()
+                if world > 1:
+                    dist.barrier()
+            per_lane = (e2e_steps + len(lanes) - 1) // len(lanes)
+            got = [0] * len(lanes)
+            errs = []
+
+            def drive(i, steps):
+                try:
+                    for _ in range(steps):
+                        got[i] = step_e2e(*lanes[i])
+                except Exception as e:               # noqa: BLE001 -- re-raised by the main thread
+                    errs.append(e)
+            for i in range(len(lanes)):
+                drive(i, max(1, min(a.warmup, 3)))
+            sync_all()
+            te = time.perf_counter()
+            if len(lanes) == 1:
+                drive(0, per_lane)
+            else:
+                th = [threading.Thread(target=drive, args=(i, per_lane)) for i in range(len(lanes))]
+                for t in th:
+                    t.start()
+                for t in th:
+                    t.join()
+            sync_all()
+            secs = time.perf_counter() - te
+            if errs:
+                raise errs[0]
+            t2 = torch.tensor([secs], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+            return world * n_reads * per_lane * len(lanes) / float(t2.item()), per_lane * len(lanes), got[0]
 
         if world > 1 and rank == 0:
             ctx.gather_host_async(True)          # the gathered records reach rank 0's host under the next step
-        for _ in range(max(1, min(a.warmup, 3))):
-            step_e2e()
-        barrier()
-        te = time.perf_counter()
-        for _ in range(e2e_steps):
-            d2h = step_e2e()
-        barrier()
-        e2e_s = time.perf_counter() - te
-        t2 = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * n_reads * e2e_steps / float(t2.item()), "unit": unit,
-               "h2d_bytes_per_step": int(h2d_packed) * world, "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-               "api": "bm_map_locate_packed (pinned host buffers in the FASTQ parser's packed form: 2-bit base planes" +
-                      (", k-mer quality plane" if n_low else ", no quality plane: no read has a base below -b") +
-                      "; host records out; H2D chunks pipelined against the mapper inside the call)" +
-                      ("; N > 1: + bm_gather_results into rank 0's host memory" if world > 1 else "")}
+        api = ("bm_map_locate_packed (pinned host buffers in the FASTQ parser's packed form: 2-bit base planes" +
+               (", k-mer quality plane" if n_low else ", no quality plane: no read has a base below -b") +
+               "; host records out; H2D chunks pipelined against the mapper inside the call)" +
+               ("; N > 1: + bm_gather_results into rank 0's host memory" if world > 1 else ""))
+        v1, s1, d2h = run_e2e([(ctx, ooff, olocs)])
+        e2e_one = {"value": v1, "unit": unit, "h2d_bytes_per_step": int(h2d_packed) * world, "d2h_bytes_per_step": int(d2h),
+                   "steps": s1, "api": api + "; one call at a time"}
+        e2e = e2e_one
+        if a.e2e_lanes == 2 or (a.e2e_lanes == 0 and world == 1):
+            # two batches in flight per GPU: the context and a lane (bm_ctx_create_lane: views the index, owns streams and
+            # batch buffers), one host thread each; at N > 1 the lanes of all ranks form a second gather group
+            lane = ctx.create_lane(P)
+            ooff2 = ctx.pinned(len(ooff), np.uint32)
+            olocs2 = ctx.pinned(len(olocs), bm.LOC_DTYPE)
+            if world > 1:
+                hs2 = [None] * world
+                dist.all_gather_object(hs2, lane.gather_open(rank, world, 0, n_reads, 4 * n_reads + 4096))
+                lane.gather_connect(hs2)
+                if rank == 0:
+                    lane.gather_host_async(True)
+            v2, s2, d2h2 = run_e2e([(ctx, ooff, olocs), (lane, ooff2, olocs2)])
+            same = bool(np.array_equal(ooff, ooff2) and np.array_equal(olocs[:int(ooff[-1])], olocs2[:int(ooff2[-1])])) if rank == 0 else None
+            e2e = {"value": v2, "unit": unit, "h2d_bytes_per_step": int(h2d_packed) * world, "d2h_bytes_per_step": int(d2h2),
+                   "steps": s2, "lanes_give_the_same_records": same,
+                   "api": api + "; two calls in flight per GPU: the context and a lane (bm_ctx_create_lane), one host thread each"}
+            if world > 1:
+                lane.gather_sync()
+                lane.gather_close()
+                dist.barrier()
+            lane.close()
         if world == 1:
             hseq = ctx.pinned(len(seq), np.uint8); hseq[:] = seq
             hqual = ctx.pinned(len(qual), np.uint8); hqual[:] = qual
@@ -715,7 +774,7 @@ def main():
                    "step": ("bm_map_device + bm_locate_device(filter_best=1)" if not align else
                             "bm_map_device + bm_locate_device(filter_best=0) + bm_align_device") +
                            (" + bm_gather_results (records into rank 0's device memory)" if world > 1 else "")},
-        "e2e": e2e, "e2e_ascii": e2e_ascii,
+        "e2e": e2e, "e2e_one_call_at_a_time": e2e_one, "e2e_ascii": e2e_ascii,
         "gpu_launches": launches,
         "clocks": clk,
         "roofline": roof,
