@@ -36,6 +36,7 @@ struct FusedArgs {
     uint32_t P; uint16_t* sidx; uint32_t* shash;
     uint32_t ldmode, pf_lines, pf_inv;
     uint32_t fm[9];                           // bit planes of the hits a group needs: S - F + 1
+    uint32_t all_distok;                      // every q-gram is indexed and passes -d: no distinguishability look-ups needed
     uint32_t all_indexed;                     // every q-gram has a row (-f 1): no kmer_to_index look-ups needed for the counter
     uint32_t max_pass; int32_t* rowidx; uint32_t* over_list; uint32_t* n_over;   // hand-over to K2 (repeats)
 };
@@ -179,7 +180,11 @@ k_map_fused(const FusedArgs a) {
     }
     __syncwarp();
     // ---- 1b. one distinguishability bit per q-gram start (q_gram_mapper.h:189-196, one table bit per q-gram) ---------------
-    {
+    if (a.all_distok) {
+        // every one of the 4^q table bits is set (the usual case at -f 1): the bits of positions past the last q-gram start are
+        // never looked at (k-mer p < nk reads q-gram bits p .. p+k-q <= n-q), so whole words of ones do
+        for (uint32_t c = lane; c <= nqch; c += 32) Dq[c] = 0xFFFFFFFFu;
+    } else {
         uint2 p0 = pls[0];
         for (uint32_t c = 0; c < nqch; c += 4) {
             uint32_t bit[4];
@@ -476,6 +481,8 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
         for (int i = 0; i < 9; i++) a.fm[i] = ((need >> i) & 1u) ? 0xFFFFFFFFu : 0u;
     }
     a.all_indexed = (c->n_rows == (1u << (2 * c->q))) ? 1u : 0u;
+    // dist_valid counts the rows with MORE zeros than the threshold (the logged counter); the table bit asks for >=
+    a.all_distok = (a.all_indexed && c->dist_valid == c->n_rows && !getenv("BM_K2F_NO_ALLDIST")) ? 1u : 0u;
     a.pf_lines = (a.Wc * 4u + 127u) / 128u;
     a.pf_inv = 65535u / a.pf_lines + 1u;              // exact for t < 65536 / lines; S * lines <= 256 * 64 stays far below
     if ((uint64_t)S * a.pf_lines * a.pf_lines >= 65536) { a.pf_lines = 0; a.pf_inv = 0; }   // (t * inv) >> 16 would be off: no prefetch
@@ -485,6 +492,7 @@ int bm_internal_map_fused(bm_ctx* c, const bm_params* p, uint32_t seg0, uint32_t
     const int minb = mbe ? atoi(mbe) : 0;
     if (NP == 4) {
         if (minb == 8) BM_FUSED(4, 8); else if (minb == 10) BM_FUSED(4, 10); else if (minb == 9) BM_FUSED(4, 9);
+        else if (minb == 14) BM_FUSED(4, 14);
         else BM_FUSED(4, 12);                          // 48 warps per SM at 40 registers: measured fastest (2.36 vs 2.55 ms at 9)
     } else if (NP == 6) BM_FUSED(6, 8); else BM_FUSED(9, 6);
 #undef BM_FUSED

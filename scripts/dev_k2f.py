@@ -24,11 +24,15 @@ seq, qual, off, _, _ = datagen.simulate_reads(packed, N, n_reads, 300, 0.002, 0.
 ctx.reads_upload(P, seq, qual, off)
 ctx.kernel_timing(True)
 ref = None
-for fine, minb, pfd in ((1, "12", "3"), (1, "12", "0"), (1, "10", "3"), (1, "12", "3")):
+for fine, minb, pfd, nod in ((1, "12", "3", "1"), (1, "12", "3", ""), (1, "14", "3", ""), (1, "12", "3", "1"), (1, "12", "3", "")):
     ctx.index_fine_table(fine)
     if True:
         os.environ["BM_K2F_MINB"] = minb
         os.environ["BM_K2F_LD"] = pfd
+        if nod:
+            os.environ["BM_K2F_NO_ALLDIST"] = "1"
+        else:
+            os.environ.pop("BM_K2F_NO_ALLDIST", None)
         for _ in range(2):
             ctx.map_device(P); ctx.locate_device(P, True)
         ctx.sync(); ctx.kernel_stats_reset()
@@ -40,6 +44,6 @@ for fine, minb, pfd in ((1, "12", "3"), (1, "12", "0"), (1, "10", "3"), (1, "12"
         if ref is None:
             ref = (off_.copy(), locs.copy())
         same = np.array_equal(ref[0], off_) and np.array_equal(ref[1], locs)
-        print(f"fine={fine} minb={minb} ld={pfd}: map {ks['map_vote'][0] / 5:.3f} ms  locate {ks['locate'][0] / 5:.3f}  aux {ks['aux'][0] / 5:.3f} "
+        print(f"fine={fine} minb={minb} ld={pfd} lookups={bool(nod)}: map {ks['map_vote'][0] / 5:.3f} ms  locate {ks['locate'][0] / 5:.3f}  aux {ks['aux'][0] / 5:.3f} "
               f"merge {ks['merge'][0] / 5:.3f}  same={same}", flush=True)
 ctx.close()
