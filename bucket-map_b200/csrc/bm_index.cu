@@ -290,7 +290,12 @@ static int kmer_table_choose(bm_ctx* c, const bm_params* p, uint32_t* logg_out) 
     const bool fine = c->ftable_mode != 0;
     double best = gather;
     uint32_t best_logg = 0xFF;
-    for (uint32_t logg = 3; logg <= 5 && need > 0; logg++) {
+    // A bit matrix that lives in L2 (small references: C1's is 1 MB) costs no DRAM bytes either way, and the byte model has
+    // nothing to say; there the fused kernel wins by being one pass instead of three (measured on C1 at -f 0.25: 0.33 ms
+    // against 0.61 ms for sampler + gather + locator sampler per 100 k reads).
+    const bool l2_resident = (uint64_t)c->n_rows * c->Wp <= ((uint64_t)32 << 20);
+    if (l2_resident && need > 0) { best = 0.0; best_logg = 4; }
+    for (uint32_t logg = 3; logg <= 5 && need > 0 && !l2_resident; logg++) {
         const double G = (double)(1u << logg);
         const double groups = std::ceil((double)c->NB / G);
         const double lines = std::ceil(std::ceil(groups / 8.0) / 128.0);

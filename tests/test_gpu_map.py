@@ -76,7 +76,9 @@ def test_map_matches_oracle(oracle, bm, ctx, kw, pk, ktable):
     if ktable == 1:                               # mode 1: 8 / 16 / 32 buckets per coarse bit, or no table when the gather is cheaper
         assert chosen in (0, 8, 16, 32) and 0.0 < density <= 1.0
         if kw.get("frac", 1.0) < 0.5:
-            assert chosen == 0                    # FracMinHash-sparse index: every coarse bit would be set
+            # FracMinHash-sparse index: every coarse bit would be set and the gather is cheaper (C2 at -f 0.25, bench.py) --
+            # unless the matrix is small enough to live in L2, as every matrix of this file is: then the fused kernel is kept
+            assert chosen == 16
     else:
         assert chosen == ktable
     have = chosen != 0
