@@ -364,6 +364,19 @@ class Context:
         self._ck(self.lib.bm_locate_download(self.h, _ptr(off), _ptr(locs), n.value), "bm_locate_download")
         return off, locs
 
+    def locate_download_into(self, off, locs):
+        """bm_locate_download into the caller's arrays (pinned ones make the copy asynchronous-speed); returns n_locs"""
+        n = C.c_uint64()
+        self._ck(self.lib.bm_locate_count(self.h, C.byref(n)), "bm_locate_count")
+        self._ck(self.lib.bm_locate_download(self.h, _ptr(off), _ptr(locs), len(locs)), "bm_locate_download")
+        return n.value
+
+    def align_download_into(self, aln, cig):
+        """bm_align_download into the caller's arrays; returns the number of CIGAR ops"""
+        used = C.c_uint64()
+        self._ck(self.lib.bm_align_download(self.h, _ptr(aln), _ptr(cig), len(cig), C.byref(used)), "bm_align_download")
+        return used.value
+
     def locate_device_buffers(self):
         """(loc_off device pointer, locs device pointer, n_locs) of the last locate_device"""
         a, b, n = _vp(), _vp(), C.c_uint64()
