@@ -453,21 +453,40 @@ def main():
     k2i, n_rows = fracminhash(q, FMH_X, FMH_Y, a.frac)
     ctx.ref_upload(packed, cfg["n_bases"], b_start, b_len, NB)
     ctx.kernel_timing(True)
+    sharded_ms = sharded_ok = None
+    if world > 1:
+        uid = [ctx.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], world, rank)               # ncclCommInitRank inside the library (dlopen'ed NCCL)
+        # K1 sharded by buckets + ncclAllReduce (bm_index_build_sharded), timed, then checked against the one-rank build that
+        # the broadcast below delivers: the per-row zero counts of both matrices must agree on every rank
+        torch.cuda.synchronize()
+        dist.barrier()
+        ctx.index_build_sharded(k2i, q, n_rows)          # the first collective also brings NCCL's channels up: not timed
+        torch.cuda.synchronize()
+        dist.barrier()
+        tb = time.perf_counter()
+        ctx.index_build_sharded(k2i, q, n_rows)
+        dist.barrier()
+        sharded_ms = (time.perf_counter() - tb) * 1e3
+        zeros_sharded = ctx.index_zeros(0.5)[0]
+        ctx.kernel_stats_reset()
     if rank == 0:
         ctx.index_build(k2i, q, n_rows, download=False)
         ctx.sync()
     index_ms = ctx.kernel_stats()["index_build"][0]
     bcast_ms = None
     if world > 1:
-        uid = [ctx.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        ctx.comm_init(uid[0], world, rank)               # ncclCommInitRank inside the library (dlopen'ed NCCL)
         torch.cuda.synchronize()
         dist.barrier()
         tb = time.perf_counter()
         ctx.bcast_index(0)                               # ncclBroadcast: geometry, kmer_to_index, bit matrix
         dist.barrier()
         bcast_ms = (time.perf_counter() - tb) * 1e3
+        ctx.n_rows = n_rows
+        okt = torch.tensor([1 if np.array_equal(zeros_sharded, ctx.index_zeros(0.5)[0]) else 0], device="cuda")
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        sharded_ok = bool(okt.item())
     W = (NB + 7) >> 3
 
     # ---- reads of this rank (its contiguous shard of the job's reads), in both host forms
@@ -836,7 +855,8 @@ def main():
         "roofline_qgram_path": alt,
         "kernels_ms_per_step": {k: v[0] / a.steps for k, v in kst.items() if v[1]},
         "index_build_ms": index_ms, "kmer_table_build_ms": ktable_ms, "locator_index_build_ms": lidx_ms,
-        "index_bcast_ms": bcast_ms, "setup_s": setup_s,
+        "index_bcast_ms": bcast_ms, "index_build_sharded_ms": sharded_ms, "index_build_sharded_verified": sharded_ok,
+        "setup_s": setup_s,
         "mapped": {"reads_with_candidate": int(mstats[0]), "cand_fwd": int(mstats[1]), "cand_rev": int(mstats[2]),
                    "lists_handed_to_full_width_gather": int(mstats[5]), "coarse_groups_recounted_per_read": int(mstats[6]) / max(1, n_reads),
                    "locator_candidates_to_bucket_scan": int(mstats[7])},

@@ -86,6 +86,7 @@ SIGNATURES = {
     "bm_pipeline_lanes": (C.c_int, [_vp, C.c_uint32]),
     "bm_align_noalloc": (C.c_int, [_vp, C.POINTER(Params)] + [C.c_void_p] * 6 + [C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                                                                    C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bm_index_build_sharded": (C.c_int, [_vp, C.c_void_p, C.c_uint32, C.c_uint32]),
     "bm_ctx_create_lane": (C.c_int, [_vp, C.POINTER(Params), C.POINTER(_vp)]),
     "bm_align_device": (C.c_int, [_vp, C.POINTER(Params)]),
     "bm_align_download": (C.c_int, [_vp, _vp, _vp, C.c_uint64, C.POINTER(C.c_uint64)]),
@@ -183,6 +184,12 @@ class Context:
         self._ck(self.lib.bm_align_noalloc(self.h, C.byref(P), d_packed, d_bstart, d_blen, d_planes, d_pl_off, d_read_off,
                                            n_reads, max_read_len, d_loc_off, d_locs, n_aln, d_aln, d_cigar, d_cigar_cnt),
                  "bm_align_noalloc")
+
+    def index_build_sharded(self, k2i, q, n_rows):
+        """collective: every rank indexes its share of the buckets, the matrices are summed over NCCL"""
+        k2i = np.ascontiguousarray(k2i, np.int32)
+        self._ck(self.lib.bm_index_build_sharded(self.h, _ptr(k2i), q, n_rows), "bm_index_build_sharded")
+        self.n_rows = n_rows
 
     def create_lane(self, P):
         """a second context on this GPU viewing this one's reference, index and tables (bm_ctx_create_lane): drive it from

@@ -39,6 +39,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
     bool ok = false;
 };
@@ -56,6 +57,7 @@ NcclApi& nccl() {
     api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
     api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
     api.Broadcast = (decltype(api.Broadcast))dlsym(h, "ncclBroadcast");
+    api.AllReduce = (decltype(api.AllReduce))dlsym(h, "ncclAllReduce");
     api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
     api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.Broadcast && api.GetErrorString;
     return api;
@@ -274,6 +276,32 @@ int bm_comm_destroy(bm_ctx* c) {
 }
 
 // geometry + kmer_to_index + bit matrix: root -> every rank
+// K1 sharded by buckets: rank r sets the bits of its contiguous share of the buckets in a zeroed matrix,
+// then the matrices are summed over NVLink.  A bit belongs to one bucket, so exactly one rank can have set it: the sum of the
+// 32-bit words is their OR, no carry can occur.  Every rank ends up with the whole matrix (what bm_index_build on one rank
+// followed by bm_bcast_index would give).  Collective: every rank of the communicator calls it with the same table.
+int bm_index_build_sharded(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows) {
+    if (!c) return BM_E_ARG;
+    if (!c->comm) BM_FAIL(c, BM_E_ARG, "bm_index_build_sharded: bm_comm_init first");
+    if (!nccl().AllReduce) BM_FAIL(c, BM_E_CUDA, "bm_index_build_sharded: this NCCL has no ncclAllReduce");
+    cudaSetDevice(c->device);
+    const uint32_t nr = (uint32_t)c->comm_nranks, rk = (uint32_t)c->comm_rank;
+    const uint32_t b0 = (uint32_t)((uint64_t)c->n_emit * rk / nr), b1 = (uint32_t)((uint64_t)c->n_emit * (rk + 1) / nr);
+    int r = bm_internal_index_build_range(c, k2i, q, n_rows, b0, b1);
+    if (r) return r;
+    ncclComm_t comm = (ncclComm_t)c->comm;
+    const size_t words = ((size_t)n_rows * c->Wp + 64) / 4;
+    const size_t chunk = (size_t)1 << 28;                    // 1 GB of words per call
+    for (size_t o = 0; o < words; o += chunk) {
+        const size_t n = words - o < chunk ? words - o : chunk;
+        uint32_t* p = c->d_rows.as<uint32_t>() + o;
+        BM_NCCL(c, nccl().AllReduce(p, p, n, ncclUint32, ncclSum, comm, c->stream));
+    }
+    BM_CK(c, cudaStreamSynchronize(c->stream));
+    c->have_index = true;
+    return BM_OK;
+}
+
 int bm_bcast_index(bm_ctx* c, int root) {
     if (!c) return BM_E_ARG;
     if (!c->comm) BM_FAIL(c, BM_E_ARG, "bm_bcast_index: bm_comm_init first");

@@ -17,8 +17,8 @@ namespace {
 // Consecutive CTAs touch the same 32-B sector column of the matrix, which keeps the read-modify-write traffic in L2.
 __global__ void __launch_bounds__(256)
 k_index_build(const uint8_t* __restrict__ packed, const uint64_t* __restrict__ bstart, const uint32_t* __restrict__ blen,
-              const int32_t* __restrict__ k2i, uint32_t q, uint32_t* __restrict__ rows32, uint32_t Wp32) {
-    const uint32_t b = blockIdx.x;
+              const int32_t* __restrict__ k2i, uint32_t q, uint32_t* __restrict__ rows32, uint32_t Wp32, uint32_t b0) {
+    const uint32_t b = b0 + blockIdx.x;       // b0: first bucket of this launch (a rank's share in the sharded build)
     const uint64_t start = bstart[b];
     const uint32_t len = blen[b];
     if (len < q) return;
@@ -444,7 +444,7 @@ int bm_index_build(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, u
         KScope ks(c, BM_K_INDEX);
         k_index_build<<<c->n_emit, 256, 0, c->stream>>>(c->d_packed.as<uint8_t>(), c->d_bstart.as<uint64_t>(),
                                                         c->d_blen.as<uint32_t>(), c->d_k2i.as<int32_t>(), q,
-                                                        c->d_rows.as<uint32_t>(), c->Wp / 4);
+                                                        c->d_rows.as<uint32_t>(), c->Wp / 4, 0u);
     }
     BM_CK(c, cudaGetLastError());
     BM_CK(c, cudaStreamSynchronize(c->stream));
@@ -452,6 +452,31 @@ int bm_index_build(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, u
     if (out_rows) return bm_index_download(c, out_rows);
     return BM_OK;
 }
+
+}  // extern "C"
+
+// K1 over the buckets [b0, b1) only, into a zeroed matrix: one rank's share of bm_index_build_sharded (bm_comm.cu), which
+// sums the ranks' matrices afterwards.  Enqueued on c->stream, not waited for; have_index stays false until the sum is in.
+int bm_internal_index_build_range(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t b0, uint32_t b1) {
+    if (!k2i) BM_FAIL(c, BM_E_ARG, "bm_index_build_sharded: kmer_to_index is null");
+    if (c->NB == 0 || !c->d_packed.p) BM_FAIL(c, BM_E_ARG, "bm_index_build_sharded: bm_ref_upload / bm_bcast_ref first");
+    if (b0 > b1 || b1 > c->n_emit) BM_FAIL(c, BM_E_ARG, "bm_index_build_sharded: bad bucket range");
+    cudaSetDevice(c->device);
+    int r = set_table(c, k2i, q, n_rows, c->NB);
+    if (r) return r;
+    c->have_index = false;
+    BM_CK(c, cudaMemsetAsync(c->d_rows.p, 0, (size_t)n_rows * c->Wp + 64, c->stream));
+    if (b1 > b0 && n_rows) {
+        KScope ks(c, BM_K_INDEX);
+        k_index_build<<<b1 - b0, 256, 0, c->stream>>>(c->d_packed.as<uint8_t>(), c->d_bstart.as<uint64_t>(),
+                                                      c->d_blen.as<uint32_t>(), c->d_k2i.as<int32_t>(), q,
+                                                      c->d_rows.as<uint32_t>(), c->Wp / 4, b0);
+    }
+    BM_CK(c, cudaGetLastError());
+    return BM_OK;
+}
+
+extern "C" {
 
 int bm_index_load(bm_ctx* c, const int32_t* k2i, uint32_t q, const uint8_t* rows, uint32_t n_rows, uint32_t NB) {
     if (!c) return BM_E_ARG;

@@ -216,6 +216,7 @@ int bm_internal_locate_idx(bm_ctx* c, const bm_params* p, uint32_t n, uint32_t* 
 int bm_internal_exclusive_scan(bm_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, uint32_t n);
 int bm_internal_h2d(bm_ctx* c, void* dst, const void* src, size_t bytes);   // large copy from possibly pageable memory
 // reads: size the batch buffers (host tables + device), then append the segment table of reads [r0, r1)
+int bm_internal_index_build_range(bm_ctx* c, const int32_t* k2i, uint32_t q, uint32_t n_rows, uint32_t b0, uint32_t b1);
 int bm_internal_reads_begin(bm_ctx* c, const bm_params* p, const uint64_t* read_off, uint32_t n_reads, const uint32_t* pl_off,
                             bool lazy = false);
 // k_pack_reads over reads [r0, r1) of the resident ASCII batch (d_seq, d_qual, d_read_off, d_pl_off) on c->stream

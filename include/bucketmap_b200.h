@@ -247,6 +247,10 @@ int bm_comm_destroy(bm_ctx* ctx);
  * from `root` into every rank's context; derived tables are rebuilt locally (cheaper than moving them).  Collective. */
 int bm_bcast_index(bm_ctx* ctx, int root);
 int bm_bcast_ref(bm_ctx* ctx, int root);
+/* bm_index_build (indexer/bucket_indexer.h:171-216, the loop over the buckets) sharded over the ranks: every rank, holding the
+ * reference (bm_ref_upload / bm_bcast_ref), indexes its contiguous share of the buckets; ncclAllReduce sums the matrices (a bit
+ * belongs to one bucket, so the sum is the OR).  Every rank ends up with the whole index.  Collective, same table everywhere. */
+int bm_index_build_sharded(bm_ctx* ctx, const int32_t* kmer_to_index, uint32_t q, uint32_t n_rows);
 /* Gather of the location records to `root`, in rank order = read order (contiguous shards).  Not an NCCL call: each rank's
  * records are written into the root's memory over NVLink (peer mapping) behind its locator pass, flagged, and packed by
  * the root -- no host synchronisation on any rank, two batches in flight.

@@ -120,3 +120,35 @@ def test_nccl_broadcast_of_index_and_reference(oracle):
     finally:
         for c in ctxs:
             c.close()
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs (NCCL refuses two ranks on one device)")
+def test_sharded_index_build_equals_the_oracle_on_every_rank(oracle):
+    """bm_index_build_sharded: each rank indexes its share of the buckets, ncclAllReduce sums the matrices"""
+    d = dataset(read_len=150, n_reads=100, n_bases=3_000_000, L=8192, rec_split=3)
+    k2i, n_rows = oracle.fracminhash(d.q, X, Y, d.frac)
+    rows = oracle.index_build(d.packed, d.b_start, d.b_len, d.NB, d.q, k2i, n_rows)
+    world = 2
+    ctxs = [bm.Context(r) for r in range(world)]
+    try:
+        ctxs[0].ref_upload(d.packed, d.n_bases, d.b_start, d.b_len, d.NB)
+        uid = ctxs[0].comm_unique_id()
+        errs = []
+
+        def run(r):
+            try:
+                ctxs[r].comm_init(uid, world, r)
+                ctxs[r].bcast_ref(0)
+                ctxs[r].index_build_sharded(k2i, d.q, n_rows)
+            except Exception as e:      # noqa: BLE001
+                errs.append(e)
+        ts = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        assert not errs, errs
+        for c in ctxs:
+            c.NB, c.n_rows = d.NB, n_rows
+            assert np.array_equal(c.index_download(), rows)
+    finally:
+        for c in ctxs:
+            c.close()
