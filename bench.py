@@ -81,9 +81,8 @@ def parse():
     ap.add_argument("--frac", type=float, default=1.0, help="FracMinHash fraction (-f): 1 = the headline, 0.25 = the reference's default")
     ap.add_argument("--ftable", type=int, default=1, choices=[0, 1], help="full-resolution k-mer table for the exact recount")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (0: as --steps)")
-    ap.add_argument("--e2e-lanes", type=int, default=0, choices=[0, 1, 2],
-                    help="host threads (calls in flight) per GPU in the end-to-end steps: 2 = the context and a lane; 0 = 2 on one "
-                         "GPU, 1 on several (there the host's PCIe fabric is the bound and a second call in flight gains nothing)")
+    ap.add_argument("--e2e-lanes", type=int, default=2, choices=[1, 2],
+                    help="host threads (calls in flight) per GPU in the end-to-end steps: 2 = the context and a lane")
     ap.add_argument("--cpu-sample", type=int, default=0, help="reads in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--lanes", type=int, default=0,
@@ -584,15 +583,18 @@ def main():
     olocs = ctx.pinned(max(4 * n_reads * (world if rank == 0 else 1), 1024), bm.LOC_DTYPE)   # merged best locations: ~1 per read
     h2d_packed = int(pl_off[-1]) * 8 + (int(pl_off[-1]) * 4 if n_low else 0) + hplo.nbytes + hoff.nbytes
     d2h = 0
-    e2e = e2e_ascii = e2e_one = None
+    e2e = e2e_ascii = e2e_one = e2e_gathered = None
     if not align:
         import threading
 
+        gathered = [False]                       # N > 1: True = the records of all ranks go to rank 0's HOST through the gather
+
         def step_e2e(c, oo, ol):
-            if world == 1:
-                n_locs, _ = c.map_locate_packed_into(P, hpl, hqk, hplo, hoff, oo, ol, True)
-                return oo.nbytes + n_locs * bm.LOC_DTYPE.itemsize
-            # N > 1: every rank maps its shard from its host buffers; the records go to rank 0's HOST through the gather
+            if not gathered[0]:
+                # every rank: its shard from its host buffers, its records into its own host arrays (what a sharded job needs:
+                # each process writes the SAM records of its reads, as the reference arm's processes do)
+                n_locs, _ = c.map_locate_packed_into(P, hpl, hqk, hplo, hoff, oo[:n_reads + 1], ol[:4 * n_reads], True)
+                return (n_reads + 1) * 4 + n_locs * bm.LOC_DTYPE.itemsize
             c.map_locate_packed_into(P, hpl, hqk, hplo, hoff, None, None, True)
             if rank == 0:
                 nr, nl = c.gather_results(oo, ol)
@@ -605,7 +607,7 @@ def main():
             def sync_all():
                 for c, _, _ in lanes:
                     c.sync()
-                    if world > 1:
+                    if gathered[0]:
                         c.gather_sync()
                 torch.cuda.synchronize()
                 if world > 1:
@@ -641,38 +643,40 @@ def main():
                 dist.all_reduce(t2, op=dist.ReduceOp.MAX)
             return world * n_reads * per_lane * len(lanes) / float(t2.item()), per_lane * len(lanes), got[0]
 
-        if world > 1 and rank == 0:
-            ctx.gather_host_async(True)          # the gathered records reach rank 0's host under the next step
         api = ("bm_map_locate_packed (pinned host buffers in the FASTQ parser's packed form: 2-bit base planes" +
                (", k-mer quality plane" if n_low else ", no quality plane: no read has a base below -b") +
-               "; host records out; H2D chunks pipelined against the mapper inside the call)" +
-               ("; N > 1: + bm_gather_results into rank 0's host memory" if world > 1 else ""))
+               "; records into the rank's own pinned host arrays; H2D chunks pipelined against the mapper inside the call)")
+
+        def line(v, steps, d2h_b, what, **more):
+            out = {"value": v, "unit": unit, "h2d_bytes_per_step": int(h2d_packed) * world,
+                   "d2h_bytes_per_step": int(d2h_b) * (1 if gathered[0] else world), "steps": steps, "api": api + what}
+            out.update(more)
+            return out
         v1, s1, d2h = run_e2e([(ctx, ooff, olocs)])
-        e2e_one = {"value": v1, "unit": unit, "h2d_bytes_per_step": int(h2d_packed) * world, "d2h_bytes_per_step": int(d2h),
-                   "steps": s1, "api": api + "; one call at a time"}
+        e2e_one = line(v1, s1, d2h, "; one call at a time")
         e2e = e2e_one
-        if a.e2e_lanes == 2 or (a.e2e_lanes == 0 and world == 1):
+        e2e_gathered = None
+        if a.e2e_lanes != 1:
             # two batches in flight per GPU: the context and a lane (bm_ctx_create_lane: views the index, owns streams and
-            # batch buffers), one host thread each; at N > 1 the lanes of all ranks form a second gather group
+            # batch buffers), one host thread each
             lane = ctx.create_lane(P)
-            ooff2 = ctx.pinned(len(ooff), np.uint32)
-            olocs2 = ctx.pinned(len(olocs), bm.LOC_DTYPE)
-            if world > 1:
-                hs2 = [None] * world
-                dist.all_gather_object(hs2, lane.gather_open(rank, world, 0, n_reads, 4 * n_reads + 4096))
-                lane.gather_connect(hs2)
-                if rank == 0:
-                    lane.gather_host_async(True)
+            ooff2 = ctx.pinned(n_reads + 1, np.uint32)
+            olocs2 = ctx.pinned(4 * n_reads, bm.LOC_DTYPE)
             v2, s2, d2h2 = run_e2e([(ctx, ooff, olocs), (lane, ooff2, olocs2)])
-            same = bool(np.array_equal(ooff, ooff2) and np.array_equal(olocs[:int(ooff[-1])], olocs2[:int(ooff2[-1])])) if rank == 0 else None
-            e2e = {"value": v2, "unit": unit, "h2d_bytes_per_step": int(h2d_packed) * world, "d2h_bytes_per_step": int(d2h2),
-                   "steps": s2, "lanes_give_the_same_records": same,
-                   "api": api + "; two calls in flight per GPU: the context and a lane (bm_ctx_create_lane), one host thread each"}
-            if world > 1:
-                lane.gather_sync()
-                lane.gather_close()
-                dist.barrier()
+            same = bool(np.array_equal(ooff[:n_reads + 1], ooff2) and
+                        np.array_equal(olocs[:int(ooff[n_reads])], olocs2[:int(ooff2[-1])]))
+            e2e = line(v2, s2, d2h2, "; two calls in flight per GPU: the context and a lane (bm_ctx_create_lane), one host thread each",
+                       lanes_give_the_same_records=same)
             lane.close()
+        if world > 1:
+            # the same with all records delivered to rank 0's host (bm_gather_results + bm_gather_host_async): what one writer of
+            # one SAM file in read order needs; bound by rank 0's link, which carries every rank's records
+            gathered[0] = True
+            if rank == 0:
+                ctx.gather_host_async(True)
+            vg, sg, d2hg = run_e2e([(ctx, ooff, olocs)])
+            e2e_gathered = line(vg, sg, d2hg, "; + bm_gather_results: every rank's records into rank 0's host memory; one call at a time")
+            gathered[0] = False
         if world == 1:
             hseq = ctx.pinned(len(seq), np.uint8); hseq[:] = seq
             hqual = ctx.pinned(len(qual), np.uint8); hqual[:] = qual
@@ -848,7 +852,7 @@ def main():
                    "step": ("bm_map_device + bm_locate_device(filter_best=1)" if not align else
                             "bm_map_device + bm_locate_device(filter_best=0) + bm_align_device") +
                            (" + bm_gather_results (records into rank 0's device memory)" if world > 1 else "")},
-        "e2e": e2e, "e2e_one_call_at_a_time": e2e_one, "e2e_ascii": e2e_ascii,
+        "e2e": e2e, "e2e_one_call_at_a_time": e2e_one, "e2e_gathered_to_rank0": e2e_gathered, "e2e_ascii": e2e_ascii,
         "gpu_launches": launches,
         "clocks": clk,
         "roofline": roof,
