@@ -4,6 +4,10 @@ torch.distributed is used exactly twice on the path: one broadcast of the q-gram
 or loaded on rank 0, and one variable-length gather of the fixed-size location records to rank 0.  No collective sits
 inside the per-read work, so there is nothing to fuse.  Works with the nccl backend (device tensors that alias the
 library's buffers) and with gloo (CPU tensors; used by the world_size-2 CPU tests).
+
+Since round 2 the library itself replicates the index and gathers the records (csrc/bm_comm.cu: bm_bcast_index, bm_bcast_ref,
+bm_index_build_sharded, bm_gather_results) and bench.py uses those; this module stays as the torch.distributed form of the
+same plumbing for callers that already run a process group, and as what the gloo tests exercise on machines without a GPU.
 """
 import contextlib
 import os
