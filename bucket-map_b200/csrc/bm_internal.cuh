@@ -91,6 +91,7 @@ struct bm_ctx {
     // mode 1 chooses the buckets per coarse bit (8 / 16 / 32) -- or no table at all -- from a cost model fed with the measured
     // density of the k-mer rows (bm_index.cu: kmer_table_choose); modes 8 / 16 / 32 force a group size
     bool ktable_auto = true;
+    float auto_d = -1.f;                                      // ... and the -d it was made for
     uint32_t auto_k = 0, auto_S = 0, auto_F = 0, auto_logg = 4;   // the decision and what it was made for (auto_logg 0xFF: no table)
     double auto_density = 0.0;
     uint64_t ktable_max_bytes = 0;   // 0: half of the free device memory at build time
